@@ -1,0 +1,250 @@
+"""TEST INFRASTRUCTURE ONLY — never imported by the product package.
+
+Runs the reference's own Python code (GT-RIPL/AugCL, mounted read-only at
+/root/reference) on CPU so that (1) the restatement in ``augcl_oracle.py`` can
+be pinned against it and (2) golden vectors can be generated for
+``tests/golden/`` (``make_golden.py``).  The reference cannot travel to the GPU
+box, so nothing here is used by ``-m gpu`` tests, ``smoke()`` or ``bench.py``.
+
+The reference does not import in this container as-is:
+  * ``src/augmentations.py:6`` imports kornia (absent, unpinned) -> stub module;
+  * ``src/utils.py:238-239`` uses ``np.array(copy=False)`` (raises on numpy 2);
+  * ``.cuda()`` / ``is_cuda`` / ``get_device()`` are hard-coded
+    (``src/utils.py:208-212``, ``src/augmentations.py:86,280-282,390``).
+The shims below neutralise exactly those three things and nothing else; all
+arithmetic executed is the reference's.  Determinism is injected by replacing
+the random draws (kornia RandomCrop parameters, ``torch.randn`` in
+``random_conv``, the background batch) with supplied tensors.
+"""
+from __future__ import annotations
+
+import contextlib
+import math
+import os
+import sys
+import types
+
+import numpy as np
+import torch
+
+REF_SRC = "/root/reference/src"
+
+
+def available() -> bool:
+    return os.path.isfile(os.path.join(REF_SRC, "augmentations.py"))
+
+
+# --------------------------------------------------------------------------
+# kornia stand-in.  kornia is a third-party dependency absent from
+# /root/reference (setup/conda.yaml:22, unpinned; the contemporaries torch==1.7.1 /
+# numpy==1.19.5 resolve to a 0.5.x release).  The two call sites are restated
+# from the published algorithm.  "parity unpinned":
+# the reference holds no test vectors at this boundary.
+# --------------------------------------------------------------------------
+HSV_EPS = 1e-6  # kornia 0.5.x rgb_to_hsv default
+
+
+def kornia_rgb_to_hsv(image: torch.Tensor, eps: float = HSV_EPS) -> torch.Tensor:
+    maxc, _ = image.max(-3)
+    maxc_mask = image == maxc.unsqueeze(-3)
+    _, max_indices = ((maxc_mask.cumsum(-3) == 1) & maxc_mask).max(-3)
+    minc = image.min(-3)[0]
+    v = maxc
+    deltac = maxc - minc
+    s = deltac / (v + eps)
+    deltac = torch.where(deltac == 0, torch.ones_like(deltac), deltac)
+    maxc_tmp = maxc.unsqueeze(-3) - image
+    rc, gc, bc = maxc_tmp[..., 0, :, :], maxc_tmp[..., 1, :, :], maxc_tmp[..., 2, :, :]
+    h = torch.stack([bc - gc, 2.0 * deltac + rc - bc, 4.0 * deltac + gc - rc], dim=-3)
+    h = torch.gather(h, dim=-3, index=max_indices[..., None, :, :]).squeeze(-3)
+    h = h / deltac
+    h = (h / 6.0) % 1.0
+    h = 2 * math.pi * h
+    return torch.stack([h, s, v], dim=-3)
+
+
+class _RandomCrop:
+    """kornia.augmentation.RandomCrop((h, w)) with injected parameters.
+
+    ``_next_offsets`` (n,2) int (row, col) must be set by the harness before the
+    call; mode "slice" (kornia>=0.6 default) or "warp" (0.5.x: bilinear
+    warp_affine, align_corners=True)."""
+
+    _next_offsets = None
+    _mode = "slice"
+
+    def __init__(self, size):
+        self.size = size
+
+    def __call__(self, x):
+        h, w = self.size
+        off = type(self)._next_offsets
+        assert off is not None, "harness must inject crop offsets"
+        n = x.shape[0]
+        if type(self)._mode == "slice":
+            return torch.stack(
+                [x[i, :, int(off[i, 0]):int(off[i, 0]) + h, int(off[i, 1]):int(off[i, 1]) + w] for i in range(n)]
+            )
+        # warp mode: translation-only affine sampled with bilinear/zeros/align_corners=True
+        H, W = x.shape[-2:]
+        ys = torch.arange(h, dtype=torch.float32)
+        xs = torch.arange(w, dtype=torch.float32)
+        out = []
+        for i in range(n):
+            sy = ys + float(off[i, 0])
+            sx = xs + float(off[i, 1])
+            gy = sy * 2.0 / (H - 1) - 1.0
+            gx = sx * 2.0 / (W - 1) - 1.0
+            grid = torch.stack(torch.meshgrid(gx, gy, indexing="xy"), dim=-1)[None]
+            out.append(torch.nn.functional.grid_sample(
+                x[i:i + 1], grid, mode="bilinear", padding_mode="zeros", align_corners=True))
+        return torch.cat(out)
+
+
+def _install_kornia_stub():
+    if "kornia" in sys.modules and not getattr(sys.modules["kornia"], "_augcl_stub", False):
+        return
+    k = types.ModuleType("kornia")
+    k._augcl_stub = True
+    k.color = types.ModuleType("kornia.color")
+    k.color.rgb_to_hsv = kornia_rgb_to_hsv
+    k.augmentation = types.ModuleType("kornia.augmentation")
+    k.augmentation.RandomCrop = _RandomCrop
+    sys.modules["kornia"] = k
+    sys.modules["kornia.color"] = k.color
+    sys.modules["kornia.augmentation"] = k.augmentation
+
+
+_ref_mods = None
+
+
+def load_reference():
+    """Import the reference's ``augmentations`` and ``utils`` modules (cached)."""
+    global _ref_mods
+    if _ref_mods is not None:
+        return _ref_mods
+    if not available():
+        raise RuntimeError("/root/reference is not present on this machine")
+    _install_kornia_stub()
+    saved = {k: sys.modules.pop(k) for k in ("augmentations", "utils") if k in sys.modules}
+    sys.path.insert(0, REF_SRC)
+    try:
+        import augmentations as ref_aug  # noqa: E402
+        import utils as ref_utils  # noqa: E402
+    finally:
+        sys.path.remove(REF_SRC)
+        # keep the reference modules out of the global namespace
+        sys.modules.pop("augmentations", None)
+        sys.modules.pop("utils", None)
+        sys.modules.update(saved)
+    _ref_mods = (ref_aug, ref_utils)
+    return _ref_mods
+
+
+@contextlib.contextmanager
+def cpu_shims():
+    """Neutralise .cuda()/is_cuda/get_device() and numpy-2 ``copy=False``."""
+    orig_cuda = torch.Tensor.cuda
+    orig_get_device = torch.Tensor.get_device
+    orig_is_cuda = torch.Tensor.is_cuda
+    orig_np_array = np.array
+
+    def np_array(obj, *a, copy=True, **kw):
+        if copy is False:
+            return np.asarray(obj, *a, **kw)
+        return orig_np_array(obj, *a, copy=copy, **kw)
+
+    torch.Tensor.cuda = lambda self, *a, **k: self
+    torch.Tensor.get_device = lambda self: "cpu"
+    torch.Tensor.is_cuda = property(lambda self: True)
+    np.array = np_array
+    try:
+        yield
+    finally:
+        torch.Tensor.cuda = orig_cuda
+        torch.Tensor.get_device = orig_get_device
+        torch.Tensor.is_cuda = orig_is_cuda
+        np.array = orig_np_array
+
+
+# -------------------------- reference entry points --------------------------
+
+def ref_random_shift(x: torch.Tensor, offsets, pad: int = 4, mode: str = "slice") -> torch.Tensor:
+    """src/augmentations.py:378-382 with kornia's draw replaced by ``offsets`` (n,2)=(row,col)."""
+    aug, _ = load_reference()
+    _RandomCrop._next_offsets = np.asarray(offsets)
+    _RandomCrop._mode = mode
+    try:
+        with cpu_shims():
+            return aug.random_shift(x, pad)
+    finally:
+        _RandomCrop._next_offsets = None
+
+
+def ref_random_crop(x: torch.Tensor, size: int, w1, h1) -> torch.Tensor:
+    """src/augmentations.py:385-413 with supplied offsets (w1 indexes rows)."""
+    aug, _ = load_reference()
+    with cpu_shims():
+        return aug.random_crop(x, size, w1=torch.as_tensor(w1).long(), h1=torch.as_tensor(h1).long())
+
+
+def ref_random_conv(x: torch.Tensor, weights: torch.Tensor) -> torch.Tensor:
+    """src/augmentations.py:265-274 with ``torch.randn(3,3,3,3)`` replaced by weights[i]."""
+    aug, _ = load_reference()
+    it = iter(weights)
+    orig = aug.torch.randn
+    aug.torch.randn = lambda *shape, **kw: next(it).clone()
+    try:
+        with cpu_shims():
+            return aug.random_conv(x)
+    finally:
+        aug.torch.randn = orig
+
+
+@contextlib.contextmanager
+def _bank_batch(aug, imgs):
+    orig_load, orig_get = aug.load_dataloader, aug._get_data_batch
+    aug.load_dataloader = lambda *a, **k: None
+    aug._get_data_batch = lambda batch_size: imgs.clone()
+    try:
+        yield
+    finally:
+        aug.load_dataloader, aug._get_data_batch = orig_load, orig_get
+
+
+def ref_random_overlay(x: torch.Tensor, imgs: torch.Tensor) -> torch.Tensor:
+    """src/augmentations.py:253-262; ``imgs`` (n,3,h,w) f32 in [0,1] replaces the Places/COCO batch."""
+    aug, _ = load_reference()
+    with cpu_shims(), _bank_batch(aug, imgs):
+        return aug.random_overlay(x)
+
+
+def ref_splice(x, imgs, hue_thres=0, sat_thres=0, val_thres=0.6) -> torch.Tensor:
+    """src/augmentations.py:295-306 (+277-284)."""
+    aug, _ = load_reference()
+    with cpu_shims(), _bank_batch(aug, imgs):
+        return aug.splice(x.clone(), hue_thres=hue_thres, sat_thres=sat_thres, val_thres=val_thres)
+
+
+def ref_cs_splice(x, imgs, hue_thres=3.5, sat_thres=0, val_thres=0) -> torch.Tensor:
+    """src/augmentations.py:309-324."""
+    aug, _ = load_reference()
+    with cpu_shims(), _bank_batch(aug, imgs):
+        return aug.CS_splice(x.clone(), hue_thres=hue_thres, sat_thres=sat_thres, val_thres=val_thres)
+
+
+def ref_replay_buffer(obs_shape, action_shape, capacity, batch_size):
+    """A reference ``utils.ReplayBuffer`` (src/utils.py:136-154), prefill off."""
+    _, ref_utils = load_reference()
+    return ref_utils.ReplayBuffer(obs_shape, action_shape, capacity, batch_size, prefill=False)
+
+
+def ref_lazy_frames(frames):
+    _, ref_utils = load_reference()
+    return ref_utils.LazyFrames(list(frames))
+
+
+def ref_sample(buf, idxs):
+    """src/utils.py:272-280 with explicit idxs, run on CPU."""
+    with cpu_shims():
+        return buf.sample(idxs=np.asarray(idxs))
