@@ -1,0 +1,494 @@
+// Stand-alone augmentation kernels on f32 NCHW batches (sm_100a).
+//
+// Reference functions replaced (all under /root/reference/src/augmentations.py):
+//   random_shift :378-382   random_crop :385-433   random_conv :265-274
+//   random_overlay :253-262   splice :295-306 + create_hsv_mask :277-284   CS_splice :309-324
+//
+// All of them are HBM-bound streaming kernels (read S32 [+ bank], write S32 per sample); none is a
+// dense contraction, so no tensor cores.  This translation unit is compiled with --fmad=false: every
+// multiply/add below is rounded separately, exactly like the reference's chain of torch elementwise
+// ops, and FMAs appear only where written explicitly (the conv accumulation).
+#include "common.cuh"
+
+namespace augcl {
+
+// ---------------------------------------------------------------------------------------------
+// window copy: out[i,ch,r,q] = in[i,ch,clamp(r+dy_i,0,H-1),clamp(q+dx_i,0,W-1)]
+//   random_shift INT: (dy,dx) = offsets[i] - pad      random_crop: (dy,dx) = offsets[i]
+// One CTA walks (sample, channel) planes; a thread emits one float4 from four source floats (the
+// source window is mis-aligned by dx floats, so the loads are scalar and coalesce in L1).
+// ---------------------------------------------------------------------------------------------
+template <int WQ>
+__global__ void __launch_bounds__(256) window_copy_vec_kernel(const float* __restrict__ in, float* __restrict__ out,
+                                                              int planes, int c, int H, int W, int Ho, int Wo,
+                                                              const int32_t* __restrict__ offsets, int pad) {
+  const int wq = WQ ? WQ : (Wo >> 2);
+  const int nvec = Ho * wq;
+  for (int plane = blockIdx.x; plane < planes; plane += gridDim.x) {
+    const int i = plane / c;
+    const int dy = offsets[2 * i] - pad, dx = offsets[2 * i + 1] - pad;
+    const float* src = in + (int64_t)plane * H * W;
+    float4* dst = reinterpret_cast<float4*>(out + (int64_t)plane * Ho * Wo);
+    for (int v = threadIdx.x; v < nvec; v += blockDim.x) {
+      const int r = v / wq, q4 = v - r * wq;
+      const float* row = src + (int64_t)clampi(r + dy, 0, H - 1) * W;
+      const int c0 = q4 * 4 + dx;
+      float4 o;
+      if (c0 >= 0 && c0 + 3 < W) {
+        o = make_float4(__ldg(row + c0), __ldg(row + c0 + 1), __ldg(row + c0 + 2), __ldg(row + c0 + 3));
+      } else {
+        o = make_float4(__ldg(row + clampi(c0, 0, W - 1)), __ldg(row + clampi(c0 + 1, 0, W - 1)),
+                        __ldg(row + clampi(c0 + 2, 0, W - 1)), __ldg(row + clampi(c0 + 3, 0, W - 1)));
+      }
+      dst[v] = o;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) window_copy_generic_kernel(const float* __restrict__ in, float* __restrict__ out,
+                                                                  int64_t total, int c, int H, int W, int Ho, int Wo,
+                                                                  const int32_t* __restrict__ offsets, int pad) {
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+    const int q = (int)(e % Wo);
+    int64_t rest = e / Wo;
+    const int r = (int)(rest % Ho);
+    const int64_t plane = rest / Ho;
+    const int i = (int)(plane / c);
+    const int rr = clampi(r + offsets[2 * i] - pad, 0, H - 1), cc = clampi(q + offsets[2 * i + 1] - pad, 0, W - 1);
+    out[e] = in[(plane * H + rr) * W + cc];
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// bilinear shift, DrQ-v2 formulation: F.grid_sample(replicate_pad(x), base_grid + shift,
+// padding_mode='zeros', align_corners=False).  The fp32 sequence below restates ATen's CPU
+// grid_sampler_2d (the oracle of record): unnormalise ((g+1)*size-1)/2 -> floor -> four corner
+// weights as products of distances -> weighted sum in nw,ne,sw,se order; corners outside the padded
+// image contribute zero.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) shift_bilinear_kernel(const float* __restrict__ in, float* __restrict__ out,
+                                                             int64_t total, int c, int h, int w, int pad,
+                                                             const int32_t* __restrict__ offsets,
+                                                             const float* __restrict__ base) {
+  const int Hp = h + 2 * pad, Wp = w + 2 * pad;
+  const float sc = (float)(2.0 / (double)Hp);   // python: shift *= 2.0 / (h + 2*pad)  (h == w)
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+    const int q = (int)(e % w);
+    int64_t rest = e / w;
+    const int r = (int)(rest % h);
+    const int64_t plane = rest / h;
+    const int i = (int)(plane / c);
+    const float gx = base[q] + (float)offsets[2 * i + 1] * sc;
+    const float gy = base[r] + (float)offsets[2 * i] * sc;
+    const float ix = ((gx + 1.0f) * (float)Wp - 1.0f) / 2.0f;
+    const float iy = ((gy + 1.0f) * (float)Hp - 1.0f) / 2.0f;
+    const float fx = floorf(ix), fy = floorf(iy);
+    const int x0 = (int)fx, y0 = (int)fy, x1 = x0 + 1, y1 = y0 + 1;
+    const float tx = ix - fx, ty = iy - fy;      // distance to the west / north corner
+    const float ex = 1.0f - tx, ey = 1.0f - ty;
+    const float* src = in + plane * h * w;
+    auto tap = [&](int y, int x) -> float {
+      if (x < 0 || y < 0 || x >= Wp || y >= Hp) return 0.0f;
+      return __ldg(src + (int64_t)clampi(y - pad, 0, h - 1) * w + clampi(x - pad, 0, w - 1));
+    };
+    const float nw = tap(y0, x0) * (ex * ey), ne = tap(y0, x1) * (tx * ey);
+    const float sw = tap(y1, x0) * (ex * ty), se = tap(y1, x1) * (tx * ty);
+    out[e] = ((nw + ne) + sw) + se;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// random_conv: CTA = one RGB frame x one band of kBand rows.  The band (+1-row/col replicate halo),
+// already divided by 255, is staged in shared memory; the 81 weights of the sample sit in shared
+// memory as [27][4] so one broadcast LDS.128 feeds the three output channels of a tap.  Each thread
+// produces a 1x4 strip for all three output channels: 324 explicit FMAs, then sigmoid and *255.
+// ---------------------------------------------------------------------------------------------
+constexpr int kBand = 12;
+
+__device__ __forceinline__ float sigmoid255(float v) {
+  return __fdividef(1.0f, 1.0f + __expf(-v)) * 255.0f;
+}
+
+__global__ void __launch_bounds__(256, 3) random_conv_kernel(const float* __restrict__ in, float* __restrict__ out,
+                                                          int frames, int k, int h, int w,
+                                                          const float* __restrict__ weights, int bands, int RS) {
+  extern __shared__ __align__(16) float csm[];
+  float* wsm = csm;              // [27][4]
+  float* tile = csm + 27 * 4;    // [3][kBand+2][RS]
+  const int tid = threadIdx.x;
+  const int wq = (w + 3) >> 2;
+  for (int work = blockIdx.x; work < frames * bands; work += gridDim.x) {
+    const int frame = work / bands, band = work - frame * bands;
+    const int sample = frame / k;
+    const int r0 = band * kBand;
+    const int rows = min(kBand, h - r0);
+    const float* src = in + (int64_t)frame * 3 * h * w;
+    __syncthreads();  // previous work item fully consumed
+    if (tid < 81) {
+      // weights[sample][co][ci][ky][kx] -> wsm[(ci*9 + ky*3 + kx)*4 + co]
+      const int co = tid / 27, tap = tid - co * 27;
+      wsm[tap * 4 + co] = weights[(int64_t)sample * 81 + tid];
+    }
+    const int trows = rows + 2;
+    for (int e = tid; e < 3 * trows * RS; e += blockDim.x) {
+      const int pc = e % RS;
+      const int t2 = e / RS;
+      const int pr = t2 % trows, ch = t2 / trows;
+      const int rr = clampi(r0 + pr - 1, 0, h - 1), cc = clampi(pc - 1, 0, w - 1);
+      tile[(ch * (kBand + 2) + pr) * RS + pc] = __fdiv_rn(__ldg(src + ((int64_t)ch * h + rr) * w + cc), 255.0f);
+    }
+    __syncthreads();
+    for (int v = tid; v < rows * wq; v += blockDim.x) {
+      const int r = v / wq, q4 = v - r * wq;
+      float acc[3][4];
+#pragma unroll
+      for (int co = 0; co < 3; ++co)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[co][j] = 0.0f;
+#pragma unroll 1
+      for (int ci = 0; ci < 3; ++ci) {
+#pragma unroll
+        for (int ky = 0; ky < 3; ++ky) {
+          const float* trow = tile + (ci * (kBand + 2) + r + ky) * RS + q4 * 4;
+          const float4 a = *reinterpret_cast<const float4*>(trow);
+          const float2 b = *reinterpret_cast<const float2*>(trow + 4);
+          const float x[6] = {a.x, a.y, a.z, a.w, b.x, b.y};
+#pragma unroll
+          for (int kx = 0; kx < 3; ++kx) {
+            const float4 wv = *reinterpret_cast<const float4*>(wsm + (ci * 9 + ky * 3 + kx) * 4);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              acc[0][j] = fmaf(x[j + kx], wv.x, acc[0][j]);
+              acc[1][j] = fmaf(x[j + kx], wv.y, acc[1][j]);
+              acc[2][j] = fmaf(x[j + kx], wv.z, acc[2][j]);
+            }
+          }
+        }
+      }
+      const int col = q4 * 4;
+#pragma unroll
+      for (int co = 0; co < 3; ++co) {
+        float* dst = out + (((int64_t)frame * 3 + co) * h + (r0 + r)) * w + col;
+        const float4 o = make_float4(sigmoid255(acc[co][0]), sigmoid255(acc[co][1]), sigmoid255(acc[co][2]),
+                                     sigmoid255(acc[co][3]));
+        if ((w & 3) == 0) {
+          *reinterpret_cast<float4*>(dst) = o;
+        } else {
+          const float ov[4] = {o.x, o.y, o.z, o.w};
+          for (int j = 0; j < 4 && col + j < w; ++j) dst[j] = ov[j];
+        }
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// overlay / splice: streaming elementwise kernels.  Background rows come from a device-resident bank
+// ([M][3][h][w], u8 or f32 in [0,1]); a u8 pixel is divided by 255 like torchvision's ToTensor.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ float overlay_px(float x, float img, float oma, float alpha) {
+  // ((1 - alpha) * (x / 255.0) + alpha * imgs) * 255.0     (src/augmentations.py:262)
+  return (oma * __fdiv_rn(x, 255.0f) + alpha * img) * 255.0f;
+}
+
+template <bool BANK_U8>
+__global__ void __launch_bounds__(256) overlay_vec_kernel(const float4* __restrict__ in, float4* __restrict__ out,
+                                                          int64_t nvec, int c, int hw4, const void* __restrict__ bank,
+                                                          int64_t bank_len, const int64_t* __restrict__ bank_idx,
+                                                          float oma, float alpha) {
+  for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t plane = v / hw4;
+    const int p4 = (int)(v - plane * hw4);
+    const int i = (int)(plane / c), ch = (int)(plane - (int64_t)i * c);
+    int64_t row = bank_idx[i];
+    row = row < 0 ? 0 : (row >= bank_len ? bank_len - 1 : row);
+    const int64_t boff = (row * 3 + (ch % 3)) * (int64_t)hw4 + p4;
+    float4 g;
+    if (BANK_U8) {
+      const float4 t = bytes_to_float4(__ldg(reinterpret_cast<const uint32_t*>(bank) + boff));
+      g = make_float4(__fdiv_rn(t.x, 255.0f), __fdiv_rn(t.y, 255.0f), __fdiv_rn(t.z, 255.0f), __fdiv_rn(t.w, 255.0f));
+    } else {
+      g = __ldg(reinterpret_cast<const float4*>(bank) + boff);
+    }
+    const float4 x = __ldg(in + v);
+    out[v] = make_float4(overlay_px(x.x, g.x, oma, alpha), overlay_px(x.y, g.y, oma, alpha),
+                         overlay_px(x.z, g.z, oma, alpha), overlay_px(x.w, g.w, oma, alpha));
+  }
+}
+
+template <bool BANK_U8>
+__global__ void __launch_bounds__(256) overlay_generic_kernel(const float* __restrict__ in, float* __restrict__ out,
+                                                              int64_t total, int c, int hw, const void* __restrict__ bank,
+                                                              int64_t bank_len, const int64_t* __restrict__ bank_idx,
+                                                              float oma, float alpha) {
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t plane = e / hw;
+    const int px = (int)(e - plane * hw);
+    const int i = (int)(plane / c), ch = (int)(plane - (int64_t)i * c);
+    int64_t row = bank_idx[i];
+    row = row < 0 ? 0 : (row >= bank_len ? bank_len - 1 : row);
+    const int64_t boff = (row * 3 + (ch % 3)) * (int64_t)hw + px;
+    const float g = BANK_U8 ? __fdiv_rn((float)reinterpret_cast<const uint8_t*>(bank)[boff], 255.0f)
+                            : reinterpret_cast<const float*>(bank)[boff];
+    out[e] = overlay_px(in[e], g, oma, alpha);
+  }
+}
+
+struct SpliceThr {
+  float hue, sat, val;
+  int variant;
+};
+
+// kornia.color.rgb_to_hsv (0.5.x, eps=1e-6) + the threshold test of create_hsv_mask, per pixel.
+__device__ __forceinline__ bool hsv_gt(float r, float g, float b, float ht, float st, float vt) {
+  const float maxc = fmaxf(fmaxf(r, g), b);
+  const float minc = fminf(fminf(r, g), b);
+  const float delta = maxc - minc;
+  const float s = __fdiv_rn(delta, maxc + 1e-6f);
+  const float d = (delta == 0.0f) ? 1.0f : delta;
+  const float rc = maxc - r, gc = maxc - g, bc = maxc - b;
+  const float hsel = (r == maxc) ? (bc - gc) : ((g == maxc) ? ((2.0f * d + rc) - bc) : ((4.0f * d + gc) - rc));
+  float hh = __fdiv_rn(__fdiv_rn(hsel, d), 6.0f);
+  if (hh < 0.0f) hh = hh + 1.0f;                 // torch.remainder(., 1.0) for |.| < 1
+  const float hue = 6.2831854820251465f * hh;    // float32(2*pi)
+  return (hue > ht) && (s > st) && (maxc > vt);
+}
+
+__device__ __forceinline__ void splice_px(float xr, float xg, float xb, float gr, float gg, float gb,
+                                          const SpliceThr& t, float& o_r, float& o_g, float& o_b) {
+  const float r = __fdiv_rn(xr, 255.0f), g = __fdiv_rn(xg, 255.0f), b = __fdiv_rn(xb, 255.0f);
+  bool keep = hsv_gt(r, g, b, t.hue, t.sat, t.val);
+  if (t.variant == AUGCL_CS_SPLICE) {
+    // overlay[mask2] = x[mask2]; overlay[~mask] = x[~mask]   (src/augmentations.py:318-323)
+    const bool mask2 = hsv_gt(r, g, b, 0.0f, t.sat, 0.6f);
+    keep = mask2 || !keep;
+  }
+  o_r = (keep ? r : gr) * 255.0f;
+  o_g = (keep ? g : gg) * 255.0f;
+  o_b = (keep ? b : gb) * 255.0f;
+}
+
+template <bool BANK_U8>
+__device__ __forceinline__ float4 bank_vec(const void* bank, int64_t off4) {
+  if (BANK_U8) {
+    const float4 t = bytes_to_float4(__ldg(reinterpret_cast<const uint32_t*>(bank) + off4));
+    return make_float4(__fdiv_rn(t.x, 255.0f), __fdiv_rn(t.y, 255.0f), __fdiv_rn(t.z, 255.0f), __fdiv_rn(t.w, 255.0f));
+  }
+  return __ldg(reinterpret_cast<const float4*>(bank) + off4);
+}
+
+template <bool BANK_U8>
+__global__ void __launch_bounds__(256) splice_vec_kernel(const float4* __restrict__ in, float4* __restrict__ out,
+                                                         int64_t nwork, int n, int hw4, const void* __restrict__ bank,
+                                                         int64_t bank_len, const int64_t* __restrict__ bank_idx,
+                                                         SpliceThr thr) {
+  for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nwork; v += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t frame = v / hw4;          // row j of x.reshape(n*k, 3, h, w)
+    const int p4 = (int)(v - frame * hw4);
+    int64_t row = bank_idx[frame % n];      // overlay = batch.repeat(k,1,1,1): row j <- background j mod n
+    row = row < 0 ? 0 : (row >= bank_len ? bank_len - 1 : row);
+    const int64_t xo = frame * 3 * hw4 + p4, bo = row * 3 * hw4 + p4;
+    const float4 xr = __ldg(in + xo), xg = __ldg(in + xo + hw4), xb = __ldg(in + xo + 2 * (int64_t)hw4);
+    const float4 gr = bank_vec<BANK_U8>(bank, bo), gg = bank_vec<BANK_U8>(bank, bo + hw4),
+                 gb = bank_vec<BANK_U8>(bank, bo + 2 * (int64_t)hw4);
+    float4 o_r, o_g, o_b;
+    splice_px(xr.x, xg.x, xb.x, gr.x, gg.x, gb.x, thr, o_r.x, o_g.x, o_b.x);
+    splice_px(xr.y, xg.y, xb.y, gr.y, gg.y, gb.y, thr, o_r.y, o_g.y, o_b.y);
+    splice_px(xr.z, xg.z, xb.z, gr.z, gg.z, gb.z, thr, o_r.z, o_g.z, o_b.z);
+    splice_px(xr.w, xg.w, xb.w, gr.w, gg.w, gb.w, thr, o_r.w, o_g.w, o_b.w);
+    out[xo] = o_r;
+    out[xo + hw4] = o_g;
+    out[xo + 2 * (int64_t)hw4] = o_b;
+  }
+}
+
+template <bool BANK_U8>
+__global__ void __launch_bounds__(256) splice_generic_kernel(const float* __restrict__ in, float* __restrict__ out,
+                                                             int64_t nwork, int n, int hw, const void* __restrict__ bank,
+                                                             int64_t bank_len, const int64_t* __restrict__ bank_idx,
+                                                             SpliceThr thr) {
+  for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nwork; v += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t frame = v / hw;
+    const int px = (int)(v - frame * hw);
+    int64_t row = bank_idx[frame % n];
+    row = row < 0 ? 0 : (row >= bank_len ? bank_len - 1 : row);
+    const int64_t xo = frame * 3 * hw + px, bo = row * 3 * hw + px;
+    float g[3];
+    for (int j = 0; j < 3; ++j)
+      g[j] = BANK_U8 ? __fdiv_rn((float)reinterpret_cast<const uint8_t*>(bank)[bo + (int64_t)j * hw], 255.0f)
+                     : reinterpret_cast<const float*>(bank)[bo + (int64_t)j * hw];
+    float o_r, o_g, o_b;
+    splice_px(in[xo], in[xo + hw], in[xo + 2 * (int64_t)hw], g[0], g[1], g[2], thr, o_r, o_g, o_b);
+    out[xo] = o_r;
+    out[xo + hw] = o_g;
+    out[xo + 2 * (int64_t)hw] = o_b;
+  }
+}
+
+static inline int grid_for(int64_t work_items, int threads, int max_ctas_per_sm) {
+  int64_t blocks = (work_items + threads - 1) / threads;
+  const int64_t cap = (int64_t)kNumSMs * max_ctas_per_sm;
+  return (int)(blocks < 1 ? 1 : (blocks > cap ? cap : blocks));
+}
+
+static int check_image_args(const char* who, const float* in, float* out, int n, int c, int h, int w) {
+  AUGCL_REQUIRE(in && out, "%s: in/out is NULL", who);
+  AUGCL_REQUIRE(in != out, "%s: in and out must not alias", who);
+  AUGCL_REQUIRE(n > 0 && c > 0 && h > 0 && w > 0, "%s: n, c, h, w must be positive (got %d,%d,%d,%d)", who, n, c, h, w);
+  AUGCL_REQUIRE((int64_t)n * c < (1ll << 31) && (int64_t)h * w < (1ll << 28), "%s: shape too large", who);
+  if (!aligned(in, 4) || !aligned(out, 4)) AUGCL_FAIL(AUGCL_ERR_BAD_ALIGN, "%s: pointers must be 4-byte aligned", who);
+  return AUGCL_OK;
+}
+
+static int launch_window_copy(const float* in, float* out, int n, int c, int H, int W, int Ho, int Wo,
+                              const int32_t* offsets, int pad, cudaStream_t st) {
+  const int planes = n * c;
+  if (g_staging.load() == 0 && (Wo & 3) == 0 && aligned(out, 16)) {
+    const int grid = planes < kNumSMs * 8 ? planes : kNumSMs * 8;
+    if (Wo == 84)
+      window_copy_vec_kernel<21><<<grid, 256, 0, st>>>(in, out, planes, c, H, W, Ho, Wo, offsets, pad);
+    else
+      window_copy_vec_kernel<0><<<grid, 256, 0, st>>>(in, out, planes, c, H, W, Ho, Wo, offsets, pad);
+  } else {
+    const int64_t total = (int64_t)planes * Ho * Wo;
+    window_copy_generic_kernel<<<grid_for(total, 256, 16), 256, 0, st>>>(in, out, total, c, H, W, Ho, Wo, offsets, pad);
+  }
+  AUGCL_LAUNCHED();
+  return AUGCL_OK;
+}
+
+}  // namespace augcl
+
+using namespace augcl;
+
+extern "C" {
+
+int augcl_drq_base_grid(int h, int pad, float* out_host) {
+  AUGCL_REQUIRE(out_host && h > 0 && pad >= 0, "augcl_drq_base_grid: bad arguments");
+  // torch.linspace(-1+eps, 1-eps, steps, dtype=float32)[:h]: fp32 start/end/step, symmetric evaluation
+  // (first half start + step*i, second half end - step*(steps-1-i)).
+  const int steps = h + 2 * pad;
+  const double eps = 1.0 / (double)steps;
+  const float start = (float)(-1.0 + eps), end = (float)(1.0 - eps);
+  const float step = steps > 1 ? (end - start) / (float)(steps - 1) : 0.0f;
+  const int halfway = steps / 2;
+  for (int i = 0; i < h; ++i)
+    out_host[i] = i < halfway ? start + step * (float)i : end - step * (float)(steps - i - 1);
+  return AUGCL_OK;
+}
+
+int augcl_random_shift(const float* in, float* out, int n, int c, int h, int w, int pad, const int32_t* offsets,
+                       int mode, const float* base, augcl_stream stream) {
+  if (int rc = check_image_args("augcl_random_shift", in, out, n, c, h, w)) return rc;
+  AUGCL_REQUIRE(offsets, "augcl_random_shift: offsets is NULL");
+  AUGCL_REQUIRE(pad >= 0 && pad < (1 << 15), "augcl_random_shift: bad pad %d", pad);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (mode == AUGCL_SHIFT_INT) return launch_window_copy(in, out, n, c, h, w, h, w, offsets, pad, st);
+  AUGCL_REQUIRE(mode == AUGCL_SHIFT_BILINEAR, "augcl_random_shift: unknown mode %d", mode);
+  AUGCL_REQUIRE(base, "augcl_random_shift: BILINEAR needs the base grid");
+  if (h != w) AUGCL_FAIL(AUGCL_ERR_UNSUPPORTED, "augcl_random_shift: BILINEAR (DrQ-v2 grid) requires h == w");
+  const int64_t total = (int64_t)n * c * h * w;
+  shift_bilinear_kernel<<<grid_for(total, 256, 16), 256, 0, st>>>(in, out, total, c, h, w, pad, offsets, base);
+  AUGCL_LAUNCHED();
+  return AUGCL_OK;
+}
+
+int augcl_random_crop(const float* in, float* out, int n, int c, int H, int W, int size, const int32_t* offsets,
+                      augcl_stream stream) {
+  if (int rc = check_image_args("augcl_random_crop", in, out, n, c, H, W)) return rc;
+  AUGCL_REQUIRE(offsets, "augcl_random_crop: offsets is NULL");
+  AUGCL_REQUIRE(size > 0 && size <= H && size <= W, "augcl_random_crop: size %d does not fit %dx%d", size, H, W);
+  return launch_window_copy(in, out, n, c, H, W, size, size, offsets, 0, (cudaStream_t)stream);
+}
+
+int augcl_random_conv(const float* in, float* out, int n, int c, int h, int w, const float* weights,
+                      augcl_stream stream) {
+  if (int rc = check_image_args("augcl_random_conv", in, out, n, c, h, w)) return rc;
+  AUGCL_REQUIRE(weights, "augcl_random_conv: weights is NULL");
+  AUGCL_REQUIRE(c % 3 == 0, "augcl_random_conv: c=%d is not a multiple of 3", c);
+  const int k = c / 3, frames = n * k;
+  const int bands = (h + kBand - 1) / kBand;
+  const int RS = ((w + 2 + 3) & ~3) + 4;  // padded row stride: multiple of 4 floats, room for the float2 tail
+  const size_t smem = (27 * 4 + 3 * (kBand + 2) * (size_t)RS) * sizeof(float);
+  if (smem > 200 * 1024) AUGCL_FAIL(AUGCL_ERR_UNSUPPORTED, "augcl_random_conv: width %d too large", w);
+  static std::atomic<bool> configured{false};
+  if (!configured.exchange(true))
+    AUGCL_CUDA(cudaFuncSetAttribute(random_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  const int64_t work = (int64_t)frames * bands;
+  const int grid = (int)(work < kNumSMs * 8 ? work : kNumSMs * 8);
+  random_conv_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(in, out, frames, k, h, w, weights, bands, RS);
+  AUGCL_LAUNCHED();
+  return AUGCL_OK;
+}
+
+static int check_bank(const char* who, const void* bank, int bank_dtype, int64_t bank_len, const int64_t* bank_idx) {
+  AUGCL_REQUIRE(bank && bank_idx, "%s: bank/bank_idx is NULL", who);
+  AUGCL_REQUIRE(bank_len > 0, "%s: bank_len must be positive", who);
+  AUGCL_REQUIRE(bank_dtype == AUGCL_BANK_U8 || bank_dtype == AUGCL_BANK_F32, "%s: unknown bank_dtype %d", who, bank_dtype);
+  return AUGCL_OK;
+}
+
+int augcl_random_overlay(const float* in, float* out, int n, int c, int h, int w, const void* bank, int bank_dtype,
+                         int64_t bank_len, const int64_t* bank_idx, float alpha, augcl_stream stream) {
+  if (int rc = check_image_args("augcl_random_overlay", in, out, n, c, h, w)) return rc;
+  if (int rc = check_bank("augcl_random_overlay", bank, bank_dtype, bank_len, bank_idx)) return rc;
+  AUGCL_REQUIRE(c % 3 == 0, "augcl_random_overlay: c=%d is not a multiple of 3", c);
+  cudaStream_t st = (cudaStream_t)stream;
+  const float oma = (float)(1.0 - (double)alpha);
+  const int hw = h * w;
+  const int64_t total = (int64_t)n * c * hw;
+  const bool u8 = bank_dtype == AUGCL_BANK_U8;
+  const bool vec = g_staging.load() == 0 && (hw & 3) == 0 && aligned(in, 16) && aligned(out, 16) &&
+                   aligned(bank, u8 ? 4 : 16);
+  if (vec) {
+    const int64_t nvec = total / 4;
+    const int grid = grid_for(nvec, 256, 8);
+    if (u8)
+      overlay_vec_kernel<true><<<grid, 256, 0, st>>>((const float4*)in, (float4*)out, nvec, c, hw / 4, bank, bank_len, bank_idx, oma, alpha);
+    else
+      overlay_vec_kernel<false><<<grid, 256, 0, st>>>((const float4*)in, (float4*)out, nvec, c, hw / 4, bank, bank_len, bank_idx, oma, alpha);
+  } else {
+    const int grid = grid_for(total, 256, 16);
+    if (u8)
+      overlay_generic_kernel<true><<<grid, 256, 0, st>>>(in, out, total, c, hw, bank, bank_len, bank_idx, oma, alpha);
+    else
+      overlay_generic_kernel<false><<<grid, 256, 0, st>>>(in, out, total, c, hw, bank, bank_len, bank_idx, oma, alpha);
+  }
+  AUGCL_LAUNCHED();
+  return AUGCL_OK;
+}
+
+int augcl_splice(const float* in, float* out, int n, int c, int h, int w, const void* bank, int bank_dtype,
+                 int64_t bank_len, const int64_t* bank_idx, float hue_thres, float sat_thres, float val_thres,
+                 int variant, augcl_stream stream) {
+  if (int rc = check_image_args("augcl_splice", in, out, n, c, h, w)) return rc;
+  if (int rc = check_bank("augcl_splice", bank, bank_dtype, bank_len, bank_idx)) return rc;
+  AUGCL_REQUIRE(c % 3 == 0, "augcl_splice: c=%d is not a multiple of 3", c);
+  AUGCL_REQUIRE(variant == AUGCL_SPLICE || variant == AUGCL_CS_SPLICE, "augcl_splice: unknown variant %d", variant);
+  cudaStream_t st = (cudaStream_t)stream;
+  const SpliceThr thr{hue_thres, sat_thres, val_thres, variant};
+  const int hw = h * w;
+  const int64_t frames = (int64_t)n * (c / 3);
+  const bool u8 = bank_dtype == AUGCL_BANK_U8;
+  const bool vec = g_staging.load() == 0 && (hw & 3) == 0 && aligned(in, 16) && aligned(out, 16) &&
+                   aligned(bank, u8 ? 4 : 16);
+  if (vec) {
+    const int64_t nwork = frames * (hw / 4);
+    const int grid = grid_for(nwork, 256, 8);
+    if (u8)
+      splice_vec_kernel<true><<<grid, 256, 0, st>>>((const float4*)in, (float4*)out, nwork, n, hw / 4, bank, bank_len, bank_idx, thr);
+    else
+      splice_vec_kernel<false><<<grid, 256, 0, st>>>((const float4*)in, (float4*)out, nwork, n, hw / 4, bank, bank_len, bank_idx, thr);
+  } else {
+    const int64_t nwork = frames * hw;
+    const int grid = grid_for(nwork, 256, 16);
+    if (u8)
+      splice_generic_kernel<true><<<grid, 256, 0, st>>>(in, out, nwork, n, hw, bank, bank_len, bank_idx, thr);
+    else
+      splice_generic_kernel<false><<<grid, 256, 0, st>>>(in, out, nwork, n, hw, bank, bank_len, bank_idx, thr);
+  }
+  AUGCL_LAUNCHED();
+  return AUGCL_OK;
+}
+
+}  // extern "C"

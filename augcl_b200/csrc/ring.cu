@@ -1,0 +1,399 @@
+// Device-resident replay ring + the fused minibatch gather / u8->f32 / shift|crop kernel.
+//
+// Replaces the host storage and sampling of utils.ReplayBuffer
+// (/root/reference/src/utils.py:139-154 storage, :216-227 add, :206-214 + :234-240 gather/H2D/cast,
+//  :242-280 sample*), optionally fused with random_shift / random_crop
+// (/root/reference/src/augmentations.py:378-382, 385-413).
+//
+// HBM layout ("v1"): obs[cap][C][H][W] u8 | next[cap][C][H][W] u8 | act[cap][A] f32 | rew[cap] | nd[cap].
+//
+// Sample kernel (TMA staging): work item = one u8 plane (H*W bytes, 7 056 B at 84x84) of one
+// (sample, tensor).  Persistent CTAs walk items round-robin; an elected thread streams the next
+// planes global->shared with cp.async.bulk (1-D TMA, completion on an mbarrier, kStages deep) while
+// all threads expand the current plane: each thread builds one float4 of output from 4 source bytes
+// (two aligned LDS.32 + funnel shift for the interior, clamped byte loads at the replicate border),
+// converts with PRMT+FADD and stores 16 B coalesced.  Algorithmic traffic per sample:
+// 2*C*H*W (u8 read) + 2*4*C*Ho*Wo (f32 write) = 635 040 B at C=9, 84x84.
+#include "common.cuh"
+
+namespace augcl {
+extern std::atomic<int> g_sample_stages;
+extern std::atomic<int> g_sample_ctas_per_sm;
+}
+
+struct augcl_ring {
+  int device;
+  int64_t capacity;
+  int k, cpf, C, H, W, A;
+  int64_t stack_bytes;  // C*H*W
+  uint8_t* obs;
+  uint8_t* next;
+  float* act;
+  float* rew;
+  float* nd;
+  int64_t bytes;
+};
+
+namespace augcl {
+
+struct SampleParams {
+  const uint8_t* store[2];
+  float* out[2];
+  const int32_t* off[2];
+  const int64_t* idx;
+  const float* act;
+  const float* rew;
+  const float* nd;
+  float* out_act;
+  float* out_rew;
+  float* out_nd;
+  int64_t capacity;
+  int B, C, H, W, Ho, Wo, A;
+  int pad;        // SHIFT: pad; NONE/CROP: 0.  source coord = clamp(out coord + off - pad)
+  int normalize;
+  int nt;         // number of tensors written (1 or 2); slot s -> tensor tmap[s]
+  int tmap[2];
+  int stage_bytes;
+  int stages;
+};
+
+__device__ __forceinline__ int64_t clamp_idx(int64_t i, int64_t cap) {
+  return i < 0 ? 0 : (i >= cap ? cap - 1 : i);
+}
+
+__device__ __forceinline__ void gather_scalars(const SampleParams& p) {
+  // actions / rewards / not_dones rows (src/utils.py:210-212): a few hundred floats, done by a grid-stride loop
+  const int per = p.A + 2;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < p.B * per; i += gridDim.x * blockDim.x) {
+    const int b = i / per, j = i - b * per;
+    const int64_t s = clamp_idx(p.idx[b], p.capacity);
+    if (j < p.A) {
+      if (p.out_act) p.out_act[(int64_t)b * p.A + j] = p.act[s * p.A + j];
+    } else if (j == p.A) {
+      if (p.out_rew) p.out_rew[b] = p.rew[s];
+    } else {
+      if (p.out_nd) p.out_nd[b] = p.nd[s];
+    }
+  }
+}
+
+__device__ __forceinline__ float4 finish(uint32_t w, int normalize) {
+  float4 o = bytes_to_float4(w);
+  if (normalize) {
+    o.x = __fdiv_rn(o.x, 255.0f); o.y = __fdiv_rn(o.y, 255.0f);
+    o.z = __fdiv_rn(o.z, 255.0f); o.w = __fdiv_rn(o.w, 255.0f);
+  }
+  return o;
+}
+
+struct ItemMeta {
+  int lead;  // byte offset of the plane inside its stage buffer (source aligned down to 16 B)
+  int dy, dx;
+  int pad_;
+};
+
+// WQ = Wo/4 as a compile-time constant (0 = runtime) so the row/column split is a multiply-shift.
+template <int WQ>
+__global__ void __launch_bounds__(256) ring_sample_tma_kernel(const SampleParams p) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  const int S = p.stages;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem);                       // S mbarriers
+  ItemMeta* meta = reinterpret_cast<ItemMeta*>(smem + 64);                   // S metas (S <= 8 -> 128 B)
+  uint8_t* bufs = smem + 64 + 128;                                           // S stage buffers, 16-B aligned
+  const int tid = threadIdx.x;
+  const int P = p.H * p.W;
+  const int total = p.B * p.nt * p.C;
+  const int wq = WQ ? WQ : (p.Wo >> 2);
+  const int nvec = p.Ho * wq;
+
+  if (tid == 0) {
+    for (int s = 0; s < S; ++s) mbar_init(&bars[s], 1);
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  auto issue = [&](int item, int s) {   // tid 0 only
+    const int ch = item % p.C;
+    const int bt = item / p.C;
+    const int slot = bt % p.nt, b = bt / p.nt;
+    const int t = p.tmap[slot];
+    const int64_t row = clamp_idx(p.idx[b], p.capacity);
+    const uint8_t* src = p.store[t] + (row * p.C + ch) * (int64_t)P;
+    const uintptr_t a = reinterpret_cast<uintptr_t>(src);
+    const int lead = (int)(a & 15);
+    const uint32_t bytes = (uint32_t)((lead + P + 15) & ~15);
+    int dy = -p.pad, dx = -p.pad;
+    if (p.off[t]) { dy += p.off[t][2 * b]; dx += p.off[t][2 * b + 1]; } else { dy = 0; dx = 0; }
+    meta[s] = ItemMeta{lead, dy, dx, 0};
+    mbar_expect_tx(&bars[s], bytes);
+    bulk_g2s(bufs + (size_t)s * p.stage_bytes, src - lead, bytes, &bars[s]);
+  };
+
+  if (tid == 0) {
+    for (int j = 0; j < S; ++j) {
+      const int item = blockIdx.x + j * gridDim.x;
+      if (item < total) issue(item, j);
+    }
+  }
+
+  gather_scalars(p);
+
+  int s = 0;
+  uint32_t phase = 0;
+  for (int item = blockIdx.x; item < total; item += gridDim.x) {
+    mbar_wait(&bars[s], phase);
+    const ItemMeta m = meta[s];
+    const uint8_t* sb = bufs + (size_t)s * p.stage_bytes;
+    const uint32_t* sw = reinterpret_cast<const uint32_t*>(sb);
+    const int ch = item % p.C;
+    const int bt = item / p.C;
+    const int slot = bt % p.nt, b = bt / p.nt;
+    float4* outp = reinterpret_cast<float4*>(p.out[p.tmap[slot]] + ((int64_t)b * p.C + ch) * (int64_t)(p.Ho * p.Wo));
+    for (int v = tid; v < nvec; v += blockDim.x) {
+      const int r = v / wq, q4 = v - r * wq;
+      const int rr = clampi(r + m.dy, 0, p.H - 1);
+      const int c0 = q4 * 4 + m.dx;
+      const int base = m.lead + rr * p.W;
+      uint32_t w;
+      if (c0 >= 0 && c0 + 3 < p.W) {
+        const int a = base + c0;
+        w = __funnelshift_r(sw[a >> 2], sw[(a >> 2) + 1], (a & 3) * 8);
+      } else {
+        const uint32_t b0 = sb[base + clampi(c0, 0, p.W - 1)], b1 = sb[base + clampi(c0 + 1, 0, p.W - 1)];
+        const uint32_t b2 = sb[base + clampi(c0 + 2, 0, p.W - 1)], b3 = sb[base + clampi(c0 + 3, 0, p.W - 1)];
+        w = b0 | (b1 << 8) | (b2 << 16) | (b3 << 24);
+      }
+      outp[v] = finish(w, p.normalize);
+    }
+    __syncthreads();  // every thread is done reading stage s -> it may be refilled
+    if (tid == 0) {
+      const int nxt = item + S * gridDim.x;
+      if (nxt < total) issue(nxt, s);
+    }
+    if (++s == S) { s = 0; phase ^= 1; }
+  }
+}
+
+// No staging, any shape: one thread per output element.  Fallback for Wo % 4 != 0 and the
+// "generic" arm of the staging A/B switch.
+__global__ void __launch_bounds__(256) ring_sample_generic_kernel(const SampleParams p) {
+  gather_scalars(p);
+  const int64_t plane_o = (int64_t)p.Ho * p.Wo;
+  const int64_t total = (int64_t)p.B * p.nt * p.C * plane_o;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int q = (int)(i % p.Wo);
+    int64_t rest = i / p.Wo;
+    const int r = (int)(rest % p.Ho); rest /= p.Ho;
+    const int ch = (int)(rest % p.C); rest /= p.C;
+    const int slot = (int)(rest % p.nt);
+    const int b = (int)(rest / p.nt);
+    const int t = p.tmap[slot];
+    int dy = 0, dx = 0;
+    if (p.off[t]) { dy = p.off[t][2 * b] - p.pad; dx = p.off[t][2 * b + 1] - p.pad; }
+    const int rr = clampi(r + dy, 0, p.H - 1), cc = clampi(q + dx, 0, p.W - 1);
+    const int64_t row = clamp_idx(p.idx[b], p.capacity);
+    float v = (float)p.store[t][((row * p.C + ch) * p.H + rr) * (int64_t)p.W + cc];
+    if (p.normalize) v = __fdiv_rn(v, 255.0f);
+    p.out[t][(((int64_t)b * p.C + ch) * p.Ho + r) * p.Wo + q] = v;
+  }
+}
+
+// Synthetic content: byte j of a store = byte (j % 16) of Philox block j / 16 (little-endian words).
+__global__ void __launch_bounds__(256) fill_bytes_kernel(uint4* dst, int64_t nblk, uint64_t seed, uint64_t subseq) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nblk; i += (int64_t)gridDim.x * blockDim.x)
+    dst[i] = philox4x32_10((uint64_t)i, subseq, seed);
+}
+
+__global__ void __launch_bounds__(256) fill_scalars_kernel(float* act, float* rew, float* nd, int64_t count, int A,
+                                                           uint64_t seed) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (int64_t)gridDim.x * blockDim.x) {
+    const uint4 r = philox4x32_10((uint64_t)i, 3, seed);
+    rew[i] = (float)(r.x >> 8) * (1.0f / 16777216.0f);            // [0,1)
+    nd[i] = (r.y & 15u) ? 1.0f : 0.0f;                            // ~6 % terminal transitions
+    for (int j = 0; j < A; ++j) {
+      const uint4 a = philox4x32_10((uint64_t)(i * A + j), 2, seed);
+      act[i * A + j] = (float)(a.x >> 8) * (2.0f / 16777216.0f) - 1.0f;  // [-1,1)
+    }
+  }
+}
+
+}  // namespace augcl
+
+using namespace augcl;
+
+extern "C" {
+
+int augcl_ring_create(augcl_ring** out, int device, int64_t capacity, int k, int c_per_frame, int H, int W,
+                      int action_dim) {
+  AUGCL_REQUIRE(out, "augcl_ring_create: out is NULL");
+  *out = nullptr;
+  AUGCL_REQUIRE(capacity > 0 && k > 0 && c_per_frame > 0 && H > 0 && W > 0 && action_dim > 0,
+                "augcl_ring_create: capacity, k, c_per_frame, H, W, action_dim must be positive");
+  AUGCL_REQUIRE((int64_t)H * W < (1 << 24), "augcl_ring_create: frame plane too large");
+  int ndev = 0;
+  AUGCL_CUDA(cudaGetDeviceCount(&ndev));
+  AUGCL_REQUIRE(device >= 0 && device < ndev, "augcl_ring_create: device %d out of range (%d devices)", device, ndev);
+  DeviceGuard g(device);
+  AUGCL_CUDA(g.err);
+  augcl_ring* r = new augcl_ring();
+  r->device = device; r->capacity = capacity; r->k = k; r->cpf = c_per_frame;
+  r->C = k * c_per_frame; r->H = H; r->W = W; r->A = action_dim;
+  r->stack_bytes = (int64_t)r->C * H * W;
+  const int64_t store = ((capacity * r->stack_bytes + 255) / 256) * 256 + 256;  // slack: bulk copies round up to 16 B
+  const int64_t fbytes = capacity * (int64_t)sizeof(float);
+  r->bytes = 2 * store + fbytes * (action_dim + 2);
+  cudaError_t e = cudaMalloc(&r->obs, store);
+  if (e == cudaSuccess) e = cudaMalloc(&r->next, store);
+  if (e == cudaSuccess) e = cudaMalloc(&r->act, fbytes * action_dim);
+  if (e == cudaSuccess) e = cudaMalloc(&r->rew, fbytes);
+  if (e == cudaSuccess) e = cudaMalloc(&r->nd, fbytes);
+  if (e != cudaSuccess) {
+    cudaFree(r->obs); cudaFree(r->next); cudaFree(r->act); cudaFree(r->rew); cudaFree(r->nd);
+    delete r;
+    cudaGetLastError();
+    AUGCL_FAIL(AUGCL_ERR_OOM, "augcl_ring_create: cudaMalloc of %lld bytes failed: %s", (long long)(2 * store),
+               cudaGetErrorString(e));
+  }
+  *out = r;
+  return AUGCL_OK;
+}
+
+int augcl_ring_destroy(augcl_ring* r) {
+  if (!r) return AUGCL_OK;
+  DeviceGuard g(r->device);
+  cudaFree(r->obs); cudaFree(r->next); cudaFree(r->act); cudaFree(r->rew); cudaFree(r->nd);
+  delete r;
+  return AUGCL_OK;
+}
+
+int64_t augcl_ring_bytes(const augcl_ring* r) { return r ? r->bytes : 0; }
+
+static int ring_copy(augcl_ring* r, int64_t slot0, int64_t count, bool put, uint8_t* obs, uint8_t* next, float* act,
+                     float* rew, float* nd, cudaStream_t st, const char* who) {
+  AUGCL_REQUIRE(r, "%s: ring is NULL", who);
+  AUGCL_REQUIRE(slot0 >= 0 && count >= 0 && slot0 + count <= r->capacity,
+                "%s: slots [%lld, %lld) outside capacity %lld", who, (long long)slot0, (long long)(slot0 + count),
+                (long long)r->capacity);
+  if (count == 0) return AUGCL_OK;
+  DeviceGuard g(r->device);
+  AUGCL_CUDA(g.err);
+  auto cp = [&](void* ring_ptr, void* user, size_t bytes) -> cudaError_t {
+    if (!user) return cudaSuccess;
+    return put ? cudaMemcpyAsync(ring_ptr, user, bytes, cudaMemcpyDefault, st)
+               : cudaMemcpyAsync(user, ring_ptr, bytes, cudaMemcpyDefault, st);
+  };
+  AUGCL_CUDA(cp(r->obs + slot0 * r->stack_bytes, obs, (size_t)(count * r->stack_bytes)));
+  AUGCL_CUDA(cp(r->next + slot0 * r->stack_bytes, next, (size_t)(count * r->stack_bytes)));
+  AUGCL_CUDA(cp(r->act + slot0 * r->A, act, (size_t)(count * r->A) * sizeof(float)));
+  AUGCL_CUDA(cp(r->rew + slot0, rew, (size_t)count * sizeof(float)));
+  AUGCL_CUDA(cp(r->nd + slot0, nd, (size_t)count * sizeof(float)));
+  return AUGCL_OK;
+}
+
+int augcl_ring_put(augcl_ring* r, int64_t slot0, int64_t count, const uint8_t* obs, const uint8_t* next_obs,
+                   const float* actions, const float* rewards, const float* not_dones, augcl_stream stream) {
+  return ring_copy(r, slot0, count, true, const_cast<uint8_t*>(obs), const_cast<uint8_t*>(next_obs),
+                   const_cast<float*>(actions), const_cast<float*>(rewards), const_cast<float*>(not_dones),
+                   (cudaStream_t)stream, "augcl_ring_put");
+}
+
+int augcl_ring_get(augcl_ring* r, int64_t slot0, int64_t count, uint8_t* obs, uint8_t* next_obs, float* actions,
+                   float* rewards, float* not_dones, augcl_stream stream) {
+  return ring_copy(r, slot0, count, false, obs, next_obs, actions, rewards, not_dones, (cudaStream_t)stream,
+                   "augcl_ring_get");
+}
+
+int augcl_ring_fill_synthetic(augcl_ring* r, int64_t count, uint64_t seed, augcl_stream stream) {
+  AUGCL_REQUIRE(r, "augcl_ring_fill_synthetic: ring is NULL");
+  AUGCL_REQUIRE(count >= 0 && count <= r->capacity, "augcl_ring_fill_synthetic: count out of range");
+  if (count == 0) return AUGCL_OK;
+  DeviceGuard g(r->device);
+  AUGCL_CUDA(g.err);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int64_t nblk = (count * r->stack_bytes + 15) / 16;  // store has >= 256 B of slack
+  fill_bytes_kernel<<<kNumSMs * 8, 256, 0, st>>>(reinterpret_cast<uint4*>(r->obs), nblk, seed, 0);
+  AUGCL_LAUNCHED();
+  fill_bytes_kernel<<<kNumSMs * 8, 256, 0, st>>>(reinterpret_cast<uint4*>(r->next), nblk, seed, 1);
+  AUGCL_LAUNCHED();
+  fill_scalars_kernel<<<kNumSMs * 2, 256, 0, st>>>(r->act, r->rew, r->nd, count, r->A, seed);
+  AUGCL_LAUNCHED();
+  return AUGCL_OK;
+}
+
+int augcl_ring_sample(augcl_ring* r, const int64_t* idx, int B, float* out_obs, float* out_next, float* out_act,
+                      float* out_rew, float* out_nd, int aug_mode, const int32_t* off_obs, const int32_t* off_next,
+                      int pad_or_size, int normalize, augcl_stream stream) {
+  AUGCL_REQUIRE(r, "augcl_ring_sample: ring is NULL");
+  AUGCL_REQUIRE(idx, "augcl_ring_sample: idx is NULL");
+  AUGCL_REQUIRE(B > 0, "augcl_ring_sample: B must be positive (got %d)", B);
+  AUGCL_REQUIRE(out_obs || out_next, "augcl_ring_sample: both image outputs are NULL");
+  AUGCL_REQUIRE(aug_mode == AUGCL_AUG_NONE || aug_mode == AUGCL_AUG_SHIFT || aug_mode == AUGCL_AUG_CROP,
+                "augcl_ring_sample: unknown aug_mode %d", aug_mode);
+  SampleParams p{};
+  p.store[0] = r->obs; p.store[1] = r->next;
+  p.out[0] = out_obs; p.out[1] = out_next;
+  p.off[0] = off_obs; p.off[1] = off_next;
+  p.idx = idx; p.act = r->act; p.rew = r->rew; p.nd = r->nd;
+  p.out_act = out_act; p.out_rew = out_rew; p.out_nd = out_nd;
+  p.capacity = r->capacity;
+  p.B = B; p.C = r->C; p.H = r->H; p.W = r->W; p.A = r->A;
+  p.Ho = r->H; p.Wo = r->W; p.pad = 0; p.normalize = normalize ? 1 : 0;
+  if (aug_mode == AUGCL_AUG_SHIFT) {
+    AUGCL_REQUIRE(pad_or_size >= 0 && pad_or_size < (1 << 15), "augcl_ring_sample: bad pad %d", pad_or_size);
+    p.pad = pad_or_size;
+  } else if (aug_mode == AUGCL_AUG_CROP) {
+    AUGCL_REQUIRE(pad_or_size > 0 && pad_or_size <= r->H && pad_or_size <= r->W,
+                  "augcl_ring_sample: crop size %d does not fit %dx%d", pad_or_size, r->H, r->W);
+    AUGCL_REQUIRE((!out_obs || off_obs) && (!out_next || off_next),
+                  "augcl_ring_sample: CROP needs offsets for every tensor that is written");
+    p.Ho = p.Wo = pad_or_size;
+  } else {
+    p.off[0] = p.off[1] = nullptr;
+  }
+  p.nt = 0;
+  if (out_obs) p.tmap[p.nt++] = 0;
+  if (out_next) p.tmap[p.nt++] = 1;
+  AUGCL_REQUIRE((int64_t)B * p.nt * p.C < (1ll << 31), "augcl_ring_sample: batch too large");
+  DeviceGuard g(r->device);
+  AUGCL_CUDA(g.err);
+  cudaStream_t st = (cudaStream_t)stream;
+
+  const int kMaxSmem = 227 * 1024;
+  const int P = p.H * p.W;
+  p.stage_bytes = ((P + 15) & ~15) + 32;
+  const bool vec_ok = (p.Wo % 4 == 0) && aligned(out_obs, 16) && aligned(out_next, 16) &&
+                      64 + 128 + p.stage_bytes <= kMaxSmem;
+  if (g_staging.load() == 0 && vec_ok) {
+    int stages = g_sample_stages.load();
+    int ctas_per_sm = g_sample_ctas_per_sm.load();
+    while (stages > 1 && 64 + 128 + stages * p.stage_bytes > kMaxSmem) --stages;
+    const int smem = 64 + 128 + stages * p.stage_bytes;
+    p.stages = stages;
+    const int fit = (228 * 1024) / (smem + 1024);
+    if (ctas_per_sm > fit) ctas_per_sm = fit < 1 ? 1 : fit;
+    const int total = B * p.nt * p.C;
+    int grid = kNumSMs * ctas_per_sm;
+    if (grid > total) grid = total;
+    auto launch = [&](auto kern) -> int {
+      static std::atomic<uint64_t> configured{0};   // one bit per device, per kernel instantiation
+      if (!(configured.load() >> (r->device & 63) & 1)) {
+        AUGCL_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem));
+        configured.fetch_or(1ull << (r->device & 63));
+      }
+      kern<<<grid, 256, smem, st>>>(p);
+      AUGCL_LAUNCHED();
+      return AUGCL_OK;
+    };
+    if (p.Wo == 84) return launch(ring_sample_tma_kernel<21>);
+    if (p.Wo == 100) return launch(ring_sample_tma_kernel<25>);
+    return launch(ring_sample_tma_kernel<0>);
+  }
+  const int64_t total = (int64_t)B * p.nt * p.C * p.Ho * p.Wo;
+  int64_t blocks = (total + 255) / 256;
+  if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
+  ring_sample_generic_kernel<<<(int)blocks, 256, 0, st>>>(p);
+  AUGCL_LAUNCHED();
+  return AUGCL_OK;
+}
+
+}  // extern "C"

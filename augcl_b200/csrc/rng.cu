@@ -1,0 +1,85 @@
+// Device RNG fills (Philox4x32-10).  Stand in for the reference's host draws:
+//   np.random.randint            /root/reference/src/utils.py:232          -> augcl_rng_fill_indices
+//   LongTensor(n).random_(0, m)  /root/reference/src/augmentations.py:404   -> augcl_rng_fill_offsets
+//   kornia RandomCrop parameters /root/reference/src/augmentations.py:382   -> augcl_rng_fill_offsets
+//   torch.randn(3,3,3,3)         /root/reference/src/augmentations.py:269   -> augcl_rng_fill_normal
+// Element e of a fill uses 32-bit word e of the stream (block e/4 = counter (e/4, subsequence), key = seed).
+#include "common.cuh"
+
+namespace augcl {
+
+template <typename T>
+__global__ void __launch_bounds__(256) fill_randint_kernel(T* out, int64_t count, int64_t lo, uint64_t range,
+                                                           uint64_t seed, uint64_t subseq) {
+  const int64_t nblk = (count + 3) / 4;
+  for (int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; b < nblk; b += (int64_t)gridDim.x * blockDim.x) {
+    const uint4 r = philox4x32_10((uint64_t)b, subseq, seed);
+    const uint32_t wds[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int64_t e = b * 4 + j;
+      if (e < count) out[e] = (T)(lo + (int64_t)(((uint64_t)wds[j] * range) >> 32));
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) fill_normal_kernel(float* out, int64_t count, uint64_t seed, uint64_t subseq) {
+  const int64_t nblk = (count + 3) / 4;
+  for (int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; b < nblk; b += (int64_t)gridDim.x * blockDim.x) {
+    const uint4 r = philox4x32_10((uint64_t)b, subseq, seed);
+    const uint32_t wds[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      // Box-Muller on an exactly representable pair: u1 in (0,1], u2 in [0,1)
+      const float u1 = (float)((wds[2 * j] >> 8) + 1u) * (1.0f / 16777216.0f);
+      const float u2 = (float)(wds[2 * j + 1] >> 8) * (1.0f / 16777216.0f);
+      const float rad = sqrtf(-2.0f * logf(u1));
+      float sn, cs;
+      sincospif(2.0f * u2, &sn, &cs);
+      const int64_t e = b * 4 + 2 * j;
+      if (e < count) out[e] = rad * cs;
+      if (e + 1 < count) out[e + 1] = rad * sn;
+    }
+  }
+}
+
+static inline int rng_grid(int64_t count) {
+  int64_t blocks = ((count + 3) / 4 + 255) / 256;
+  return (int)(blocks < 1 ? 1 : (blocks > kNumSMs * 8 ? kNumSMs * 8 : blocks));
+}
+
+}  // namespace augcl
+
+using namespace augcl;
+
+extern "C" {
+
+int augcl_rng_fill_offsets(int32_t* out, int64_t count, int32_t lo, int32_t hi, uint64_t seed, uint64_t subsequence,
+                           augcl_stream stream) {
+  AUGCL_REQUIRE(out && count > 0, "augcl_rng_fill_offsets: out is NULL or count <= 0");
+  AUGCL_REQUIRE(hi > lo, "augcl_rng_fill_offsets: empty range [%d, %d)", lo, hi);
+  fill_randint_kernel<int32_t><<<rng_grid(count), 256, 0, (cudaStream_t)stream>>>(out, count, lo, (uint64_t)((int64_t)hi - lo), seed,
+                                                                                  subsequence);
+  AUGCL_LAUNCHED();
+  return AUGCL_OK;
+}
+
+int augcl_rng_fill_indices(int64_t* out, int64_t count, int64_t lo, int64_t hi, uint64_t seed, uint64_t subsequence,
+                           augcl_stream stream) {
+  AUGCL_REQUIRE(out && count > 0, "augcl_rng_fill_indices: out is NULL or count <= 0");
+  AUGCL_REQUIRE(hi > lo && hi - lo <= (1ll << 32), "augcl_rng_fill_indices: range [%lld, %lld) empty or wider than 2^32",
+                (long long)lo, (long long)hi);
+  fill_randint_kernel<int64_t><<<rng_grid(count), 256, 0, (cudaStream_t)stream>>>(out, count, lo, (uint64_t)(hi - lo), seed,
+                                                                                  subsequence);
+  AUGCL_LAUNCHED();
+  return AUGCL_OK;
+}
+
+int augcl_rng_fill_normal(float* out, int64_t count, uint64_t seed, uint64_t subsequence, augcl_stream stream) {
+  AUGCL_REQUIRE(out && count > 0, "augcl_rng_fill_normal: out is NULL or count <= 0");
+  fill_normal_kernel<<<rng_grid(count), 256, 0, (cudaStream_t)stream>>>(out, count, seed, subsequence);
+  AUGCL_LAUNCHED();
+  return AUGCL_OK;
+}
+
+}  // extern "C"

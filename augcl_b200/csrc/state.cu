@@ -1,0 +1,42 @@
+// Process-wide state of the library: last error (per thread), launch counter, runtime options.
+#include <cstring>
+
+#include "common.cuh"
+
+namespace augcl {
+std::atomic<int64_t> g_launches{0};
+std::atomic<int> g_staging{0};
+std::atomic<int> g_sample_stages{3};
+std::atomic<int> g_sample_ctas_per_sm{6};
+static thread_local std::string t_error;
+void set_error(const std::string& msg) { t_error = msg; }
+}  // namespace augcl
+
+extern "C" {
+
+const char* augcl_version(void) { return "augcl_b200 0.1.0 (sm_100a)"; }
+const char* augcl_last_error(void) { return augcl::t_error.c_str(); }
+int64_t augcl_launch_count(void) { return augcl::g_launches.load(); }
+
+int augcl_set_option(const char* key, const char* value) {
+  using namespace augcl;
+  AUGCL_REQUIRE(key && value, "augcl_set_option: null key/value");
+  if (!strcmp(key, "staging")) {
+    if (!strcmp(value, "tma")) { g_staging = 0; return AUGCL_OK; }
+    if (!strcmp(value, "generic")) { g_staging = 1; return AUGCL_OK; }
+    AUGCL_FAIL(AUGCL_ERR_BAD_ARG, "augcl_set_option: staging must be tma|generic, got '%s'", value);
+  }
+  if (!strcmp(key, "sample_stages")) {
+    int v = atoi(value);
+    AUGCL_REQUIRE(v >= 1 && v <= 8, "sample_stages must be in [1,8]");
+    g_sample_stages = v; return AUGCL_OK;
+  }
+  if (!strcmp(key, "sample_ctas_per_sm")) {
+    int v = atoi(value);
+    AUGCL_REQUIRE(v >= 1 && v <= 16, "sample_ctas_per_sm must be in [1,16]");
+    g_sample_ctas_per_sm = v; return AUGCL_OK;
+  }
+  AUGCL_FAIL(AUGCL_ERR_BAD_ARG, "augcl_set_option: unknown key '%s'", key);
+}
+
+}  // extern "C"

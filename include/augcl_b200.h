@@ -1,0 +1,170 @@
+/*
+ * augcl_b200 — C ABI of the B200-native replay-gather + image-augmentation hot path.
+ *
+ * The reference (GT-RIPL/AugCL) exposes this path as Python functions, not as an FFI
+ * (SURVEY.md §8b).  Each entry point below names the reference interface it replaces
+ * (file:line under /root/reference); the Python modules augcl_b200/augmentations.py and
+ * augcl_b200/utils.py mirror those interfaces 1:1 and bind this library through ctypes
+ * (INTEGRATION.md shows the stub a reference maintainer would add).
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no torch / C++ types cross the boundary.
+ *   - every function returns 0 (AUGCL_OK) or a negative augcl_status; the message of
+ *     the last failure on the calling thread is returned by augcl_last_error().
+ *   - functions never throw, never allocate outputs and never synchronise the device:
+ *     work is enqueued on `stream` (a cudaStream_t passed as void*; NULL = legacy default
+ *     stream).  The caller owns every buffer; the library owns only a ring's storage.
+ *   - image tensors are contiguous NCHW.  Pixels are f32 in 0..255 exactly like the
+ *     reference's augmentations (the /255 lives in its encoder, src/algorithms/modules.py:85-90);
+ *     `normalize != 0` fuses that division into the kernel (out = v / 255.0f, IEEE-rounded).
+ *   - random draws are always *inputs* (indices, offsets, conv weights, background rows) so
+ *     results are comparable with the reference "given identical draws"; the augcl_rng_*
+ *     functions generate such draws on the device (Philox4x32-10) when the caller has none.
+ *   - device pointers must belong to the calling thread's current CUDA device, except ring
+ *     calls, which switch to the ring's device for the duration of the call.
+ */
+#ifndef AUGCL_B200_H_
+#define AUGCL_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct augcl_ring augcl_ring;   /* opaque: device-resident replay ring  */
+typedef void* augcl_stream;             /* cudaStream_t                          */
+
+typedef enum augcl_status {
+  AUGCL_OK = 0,
+  AUGCL_ERR_BAD_ARG = -1,    /* null pointer, non-positive size, value out of range    */
+  AUGCL_ERR_BAD_ALIGN = -2,  /* pointer not aligned as the entry point requires         */
+  AUGCL_ERR_CUDA = -3,       /* a CUDA runtime call failed; see augcl_last_error()      */
+  AUGCL_ERR_OOM = -4,        /* device allocation for a ring failed                     */
+  AUGCL_ERR_UNSUPPORTED = -5 /* shape outside what the kernels handle                   */
+} augcl_status;
+
+/* aug_mode of augcl_ring_sample */
+enum { AUGCL_AUG_NONE = 0, AUGCL_AUG_SHIFT = 1, AUGCL_AUG_CROP = 2 };
+/* mode of augcl_random_shift */
+enum { AUGCL_SHIFT_INT = 0, AUGCL_SHIFT_BILINEAR = 1 };
+/* bank_dtype of overlay / splice */
+enum { AUGCL_BANK_U8 = 0, AUGCL_BANK_F32 = 1 };
+/* variant of augcl_splice */
+enum { AUGCL_SPLICE = 0, AUGCL_CS_SPLICE = 1 };
+
+const char* augcl_version(void);
+const char* augcl_last_error(void);
+/* Number of kernel launches this library has enqueued from the calling process so far
+ * (bench.py's "gpu_launches" evidence). */
+int64_t augcl_launch_count(void);
+/* Runtime switches, for A/B measurement: "staging" = "tma" (default; cp.async.bulk + mbarrier
+ * pipeline through shared memory) | "generic" (one thread per output element, no staging). */
+int augcl_set_option(const char* key, const char* value);
+
+/* ------------------------------------------------------------------------------------------
+ * Device-resident replay ring.
+ * Replaces the host storage of utils.ReplayBuffer (src/utils.py:139-154): the Python list
+ * `_obses` of (LazyFrames, LazyFrames) and the numpy `actions/rewards/not_dones` arrays.
+ * Layout in HBM ("v1", full stacks):  obs[capacity][k*cpf][H][W] u8, next_obs[...] same,
+ * actions[capacity][action_dim] f32, rewards[capacity] f32, not_dones[capacity] f32.
+ * The write cursor (`idx`, `full`) stays in the caller (utils.ReplayBuffer keeps the
+ * reference's attributes of those names, which src/train.py reads and writes).
+ * ------------------------------------------------------------------------------------------ */
+int augcl_ring_create(augcl_ring** out, int device, int64_t capacity, int k, int c_per_frame,
+                      int H, int W, int action_dim);
+int augcl_ring_destroy(augcl_ring* ring);
+/* bytes of HBM the ring holds */
+int64_t augcl_ring_bytes(const augcl_ring* ring);
+
+/* Store `count` transitions at slots [slot0, slot0+count) (no wrap: slot0+count <= capacity).
+ * Replaces ReplayBuffer.add (src/utils.py:216-227) for count==1 and the chunk re-load of
+ * ReplayBuffer.load (src/utils.py:177-204) for count>1.  Source pointers may be host or device
+ * memory (cudaMemcpyDefault); obs/next are count*k*cpf*H*W bytes, actions count*action_dim f32,
+ * rewards / not_dones count f32.  Any source pointer may be NULL to leave that field untouched. */
+int augcl_ring_put(augcl_ring* ring, int64_t slot0, int64_t count, const uint8_t* obs,
+                   const uint8_t* next_obs, const float* actions, const float* rewards,
+                   const float* not_dones, augcl_stream stream);
+/* Inverse of put (drain for ReplayBuffer.save, src/utils.py:156-170).  NULL pointers are skipped. */
+int augcl_ring_get(augcl_ring* ring, int64_t slot0, int64_t count, uint8_t* obs, uint8_t* next_obs,
+                   float* actions, float* rewards, float* not_dones, augcl_stream stream);
+/* Fill slots [0, count) with Philox bytes / normals (benchmarks and tests; no reference analogue). */
+int augcl_ring_fill_synthetic(augcl_ring* ring, int64_t count, uint64_t seed, augcl_stream stream);
+
+/* Minibatch gather + u8->f32 (+ fused random_shift or random_crop).
+ * Replaces ReplayBuffer._encode_obses + tensor_buffer_samples (src/utils.py:206-214,234-240),
+ * i.e. the body of sample / sample_obs / sample_curl / sample_drq (src/utils.py:242-280), and,
+ * when aug_mode != NONE, the random_shift / random_crop call that follows it
+ * (src/augmentations.py:378-382, 385-413).
+ *   idx        device int64[B], each in [0, capacity)  (clamped for memory safety)
+ *   out_obs / out_next   device f32 [B, k*cpf, S, S'] with (S,S') = (H,W) for NONE/SHIFT and
+ *              (size,size) for CROP; either may be NULL to skip that tensor (sample_obs)
+ *   out_act [B,action_dim], out_rew [B], out_nd [B]  device f32, each may be NULL
+ *   off_obs / off_next   device int32[B,2] = (row, col) offsets.  SHIFT: in [0, 2*pad], the crop
+ *              origin inside the replicate-padded image (pad,pad == identity); NULL = identity for
+ *              that tensor.  CROP: (w1, h1) of the reference (w1 indexes rows), in [0, H-size] x
+ *              [0, W-size]; must not be NULL for a tensor that is written.
+ *   pad_or_size  pad (SHIFT) or size (CROP); ignored for NONE. */
+int augcl_ring_sample(augcl_ring* ring, const int64_t* idx, int B, float* out_obs, float* out_next,
+                      float* out_act, float* out_rew, float* out_nd, int aug_mode,
+                      const int32_t* off_obs, const int32_t* off_next, int pad_or_size,
+                      int normalize, augcl_stream stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Stand-alone augmentations on f32 NCHW batches (in and out must not alias).
+ * ------------------------------------------------------------------------------------------ */
+
+/* random_shift (src/augmentations.py:378-382): replicate-pad by `pad`, crop (h,w) at offsets[i].
+ *   mode INT:      offsets int32[n,2] = (row, col) in [0, 2*pad]; exact copy (kornia slice crop).
+ *   mode BILINEAR: DrQ-v2 grid_sample formulation named by the north star: offsets = (row, col)
+ *                  integer shifts; `base` = device f32[h] holding linspace(-1+1/(h+2p), 1-1/(h+2p),
+ *                  h+2p)[:h] (augcl_drq_base_grid); requires h == w. */
+int augcl_random_shift(const float* in, float* out, int n, int c, int h, int w, int pad,
+                       const int32_t* offsets, int mode, const float* base, augcl_stream stream);
+/* Host helper: writes the h base-grid values of the DrQ-v2 formulation (fp32, torch.linspace order). */
+int augcl_drq_base_grid(int h, int pad, float* out_host);
+
+/* random_crop (src/augmentations.py:385-433): out[i] = in[i, :, r:r+size, q:q+size] with
+ * (r, q) = offsets[i] = (w1_i, h1_i).  in [n,c,H,W] -> out [n,c,size,size]. */
+int augcl_random_crop(const float* in, float* out, int n, int c, int H, int W, int size,
+                      const int32_t* offsets, augcl_stream stream);
+
+/* random_conv (src/augmentations.py:265-274): per sample i, for each of its c/3 RGB frames,
+ * out = sigmoid(conv2d(replicate_pad1(x/255), weights[i])) * 255, weights f32 [n,3(out),3(in),3,3]. */
+int augcl_random_conv(const float* in, float* out, int n, int c, int h, int w, const float* weights,
+                      augcl_stream stream);
+
+/* random_overlay (src/augmentations.py:253-262): out = ((1-alpha)*(x/255) + alpha*img)*255 where
+ * img = bank[bank_idx[i]] ([3,h,w]; u8 rows are divided by 255 like torchvision ToTensor, f32 rows
+ * are used as they are), the same row for every frame of sample i (channel ch uses img[ch % 3]).
+ * bank_idx device int64[n] in [0, bank_len). */
+int augcl_random_overlay(const float* in, float* out, int n, int c, int h, int w, const void* bank,
+                         int bank_dtype, int64_t bank_len, const int64_t* bank_idx, float alpha,
+                         augcl_stream stream);
+
+/* splice / CS_splice (src/augmentations.py:295-306, 309-324, mask 277-284): per RGB frame, keep the
+ * pixels whose HSV (kornia.color.rgb_to_hsv of x/255) exceeds (hue,sat,val), replace the others by the
+ * background pixel; output (.)*255.  Frame f of sample s (row j = s*(c/3)+f of the reshaped batch)
+ * takes background bank[bank_idx[j mod n]] — the reference's batch-tiling (fact 7 of SURVEY.md). */
+int augcl_splice(const float* in, float* out, int n, int c, int h, int w, const void* bank,
+                 int bank_dtype, int64_t bank_len, const int64_t* bank_idx, float hue_thres,
+                 float sat_thres, float val_thres, int variant, augcl_stream stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Device RNG (Philox4x32-10, counter = (block_lo, block_hi, subseq_lo, subseq_hi), key = seed).
+ * Stand in for the reference's host draws: np.random.randint (src/utils.py:232),
+ * LongTensor.random_ (src/augmentations.py:404-405), kornia's crop parameters (:382),
+ * torch.randn(3,3,3,3) (:269).  Values: lo + ((u32 * (hi-lo)) >> 32).
+ * ------------------------------------------------------------------------------------------ */
+int augcl_rng_fill_offsets(int32_t* out, int64_t count, int32_t lo, int32_t hi, uint64_t seed,
+                           uint64_t subsequence, augcl_stream stream);
+int augcl_rng_fill_indices(int64_t* out, int64_t count, int64_t lo, int64_t hi, uint64_t seed,
+                           uint64_t subsequence, augcl_stream stream);
+int augcl_rng_fill_normal(float* out, int64_t count, uint64_t seed, uint64_t subsequence,
+                          augcl_stream stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AUGCL_B200_H_ */
