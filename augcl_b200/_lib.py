@@ -1,0 +1,92 @@
+"""ctypes binding of libaugcl_b200.so (the C ABI declared in include/augcl_b200.h).
+
+The product path has NO CPU fallback: if the shared library is missing or a call fails,
+an exception is raised.  Nothing under ``oracle/`` is ever imported from here.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libaugcl_b200.so")
+
+# enums of include/augcl_b200.h
+AUG_NONE, AUG_SHIFT, AUG_CROP = 0, 1, 2
+SHIFT_INT, SHIFT_BILINEAR = 0, 1
+BANK_U8, BANK_F32 = 0, 1
+SPLICE, CS_SPLICE = 0, 1
+
+_p, _i, _i64, _u64, _f = C.c_void_p, C.c_int, C.c_int64, C.c_uint64, C.c_float
+
+# name -> (restype, argtypes); every symbol include/augcl_b200.h declares
+SIGNATURES = {
+    "augcl_version": (C.c_char_p, []),
+    "augcl_last_error": (C.c_char_p, []),
+    "augcl_launch_count": (_i64, []),
+    "augcl_set_option": (_i, [C.c_char_p, C.c_char_p]),
+    "augcl_ring_create": (_i, [C.POINTER(_p), _i, _i64, _i, _i, _i, _i, _i]),
+    "augcl_ring_destroy": (_i, [_p]),
+    "augcl_ring_bytes": (_i64, [_p]),
+    "augcl_ring_put": (_i, [_p, _i64, _i64, _p, _p, _p, _p, _p, _p]),
+    "augcl_ring_get": (_i, [_p, _i64, _i64, _p, _p, _p, _p, _p, _p]),
+    "augcl_ring_fill_synthetic": (_i, [_p, _i64, _u64, _p]),
+    "augcl_ring_sample": (_i, [_p, _p, _i, _p, _p, _p, _p, _p, _i, _p, _p, _i, _i, _p]),
+    "augcl_random_shift": (_i, [_p, _p, _i, _i, _i, _i, _i, _p, _i, _p, _p]),
+    "augcl_drq_base_grid": (_i, [_i, _i, C.POINTER(_f)]),
+    "augcl_random_crop": (_i, [_p, _p, _i, _i, _i, _i, _i, _p, _p]),
+    "augcl_random_conv": (_i, [_p, _p, _i, _i, _i, _i, _p, _p]),
+    "augcl_random_overlay": (_i, [_p, _p, _i, _i, _i, _i, _p, _i, _i64, _p, _f, _p]),
+    "augcl_splice": (_i, [_p, _p, _i, _i, _i, _i, _p, _i, _i64, _p, _f, _f, _f, _i, _p]),
+    "augcl_rng_fill_offsets": (_i, [_p, _i64, C.c_int32, C.c_int32, _u64, _u64, _p]),
+    "augcl_rng_fill_indices": (_i, [_p, _i64, _i64, _i64, _u64, _u64, _p]),
+    "augcl_rng_fill_normal": (_i, [_p, _i64, _u64, _u64, _p]),
+    "augcl_rng_fill_bytes": (_i, [_p, _i64, _u64, _u64, _p]),
+}
+
+
+class AugclError(RuntimeError):
+    """A C-ABI call returned a negative augcl_status."""
+
+    def __init__(self, fn: str, status: int, msg: str):
+        super().__init__(f"{fn} failed with status {status}: {msg}")
+        self.status = status
+
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """Loads the library once; raises (never falls back) when it is absent."""
+    global _lib
+    if _lib is None:
+        if not os.path.isfile(LIB_PATH):
+            raise ImportError(
+                f"{LIB_PATH} not found: build it with `python -m augcl_b200.build` "
+                "(augcl_b200 has no CPU fallback)")
+        h = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(h, name)
+            fn.restype, fn.argtypes = res, args
+        _lib = h
+    return _lib
+
+
+def call(name: str, *args) -> None:
+    """Invoke a status-returning entry point; raise AugclError on a negative status."""
+    h = lib()
+    rc = getattr(h, name)(*args)
+    if rc != 0:
+        raise AugclError(name, rc, h.augcl_last_error().decode(errors="replace"))
+
+
+def launch_count() -> int:
+    return int(lib().augcl_launch_count())
+
+
+def set_option(key: str, value: str) -> None:
+    call("augcl_set_option", key.encode(), value.encode())
+
+
+def version() -> str:
+    return lib().augcl_version().decode()

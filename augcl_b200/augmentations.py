@@ -1,0 +1,291 @@
+"""Drop-in for the reference's ``augmentations`` module (/root/reference/src/augmentations.py).
+
+Same function names, positional arguments and error behaviour as the reference, so
+``src/algorithms/*`` and ``RAD.apply_aug`` (src/algorithms/rad.py:9-22) call it unchanged:
+tensors in, tensors out, CUDA f32 NCHW in the 0..255 range, inputs never mutated.
+Every function enqueues ONE hand-written sm_100a kernel through the C ABI
+(include/augcl_b200.h) on torch's current stream.  There is no CPU path.
+
+Random draws.  The reference draws on the host (kornia crop parameters :382,
+``LongTensor.random_`` :404-405, ``torch.randn`` :269, the DataLoader's shuffled batch :76-86).
+Here every draw can be SUPPLIED through a keyword-only argument (``offsets=``, ``weights=``,
+``bank_idx=``) — that is how parity "given identical draws" is tested — and otherwise comes from
+the device Philox stream (seed with :func:`seed`; stream = (seed, call counter)).
+
+Backgrounds.  Places365 / COCO are not available offline; ``random_overlay`` / ``splice`` read a
+device-resident background bank ([M,3,h,w] u8 or f32-in-[0,1]) registered with
+:func:`set_background_bank`.  ``load_dataloader`` keeps the reference's name and dataset check
+(:240-250) and, when no bank has been registered, creates a synthetic one.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib as L
+
+__all__ = ["random_shift", "random_crop", "random_conv", "random_overlay", "splice", "CS_splice",
+           "identity", "aug_to_func", "seed", "set_background_bank", "load_dataloader"]
+
+# --------------------------------------------------------------------------------------------
+# process-global state (the reference keeps `dataloader` / `data_iter` globals, :11-12)
+# --------------------------------------------------------------------------------------------
+_bank = None            # device tensor [M,3,h,w], uint8 or float32 in [0,1]
+_seed = 0
+_calls = 0              # Philox subsequence of the next draw
+_base_grids = {}        # (h, pad, device) -> DrQ-v2 base grid on the device
+SYNTHETIC_BANK_LEN = 4096
+
+
+def seed(s: int) -> None:
+    """Seed the device draws of this module (the reference uses torch/numpy global RNGs)."""
+    global _seed, _calls
+    _seed, _calls = int(s) & (2**64 - 1), 0
+
+
+def _next_subsequence() -> int:
+    global _calls
+    _calls += 1
+    return _calls - 1
+
+
+def _stream(t: torch.Tensor) -> int:
+    return torch.cuda.current_stream(t.device).cuda_stream
+
+
+def _prep(x: torch.Tensor, who: str) -> torch.Tensor:
+    if not isinstance(x, torch.Tensor) or not x.is_cuda:
+        raise AssertionError(f"{who}: input must be a CUDA tensor (augcl_b200 has no CPU path)")
+    if x.dim() != 4:
+        raise ValueError(f"{who}: expected (n,c,h,w), got {tuple(x.shape)}")
+    if x.dtype != torch.float32:
+        x = x.float()
+    return x.contiguous()
+
+
+def _dev_i32(v, n: int, device, who: str) -> torch.Tensor:
+    t = torch.as_tensor(v)
+    if t.shape != (n, 2):
+        raise ValueError(f"{who}: offsets must have shape ({n}, 2), got {tuple(t.shape)}")
+    return t.to(device=device, dtype=torch.int32, non_blocking=True).contiguous()
+
+
+def _draw_offsets(n: int, lo: int, hi: int, device) -> torch.Tensor:
+    out = torch.empty((n, 2), dtype=torch.int32, device=device)
+    L.call("augcl_rng_fill_offsets", out.data_ptr(), 2 * n, lo, hi, _seed, _next_subsequence(), _stream(out))
+    return out
+
+
+def identity(x):
+    """src/augmentations.py:374."""
+    return x
+
+
+# --------------------------------------------------------------------------------------------
+# random_shift  (src/augmentations.py:378-382)
+# --------------------------------------------------------------------------------------------
+def random_shift(imgs, pad=4, *, offsets=None, mode="int"):
+    """Replicate-pad by ``pad`` and crop back to (h,w) at a per-sample random origin.
+
+    offsets: optional (n,2) integers (row, col) in [0, 2*pad] (the kornia RandomCrop draw).
+    mode "int" = exact integer crop (bit-exact); "bilinear" = the DrQ-v2 grid_sample formulation.
+    """
+    x = _prep(imgs, "random_shift")
+    n, c, h, w = x.shape
+    with torch.cuda.device(x.device):
+        off = _draw_offsets(n, 0, 2 * pad + 1, x.device) if offsets is None else _dev_i32(offsets, n, x.device, "random_shift")
+        out = torch.empty_like(x)
+        if mode == "int":
+            L.call("augcl_random_shift", x.data_ptr(), out.data_ptr(), n, c, h, w, int(pad), off.data_ptr(),
+                   L.SHIFT_INT, None, _stream(x))
+        elif mode == "bilinear":
+            L.call("augcl_random_shift", x.data_ptr(), out.data_ptr(), n, c, h, w, int(pad), off.data_ptr(),
+                   L.SHIFT_BILINEAR, _base_grid(h, int(pad), x.device).data_ptr(), _stream(x))
+        else:
+            raise ValueError(f"random_shift: unknown mode {mode!r}")
+    return out
+
+
+def _base_grid(h: int, pad: int, device) -> torch.Tensor:
+    key = (h, pad, str(device))
+    g = _base_grids.get(key)
+    if g is None:
+        buf = (C.c_float * h)()
+        L.call("augcl_drq_base_grid", h, pad, buf)
+        g = torch.tensor(list(buf), dtype=torch.float32).to(device)
+        _base_grids[key] = g
+    return g
+
+
+# --------------------------------------------------------------------------------------------
+# random_crop  (src/augmentations.py:385-413)
+# --------------------------------------------------------------------------------------------
+def random_crop(x, size=84, w1=None, h1=None, return_w1_h1=False):
+    """Vectorized CUDA implementation of random crop; ``w1`` indexes rows (reference quirk)."""
+    assert (w1 is None and h1 is None) or (w1 is not None and h1 is not None), \
+        "must either specify both w1 and h1 or neither of them"
+    assert isinstance(x, torch.Tensor) and x.is_cuda, "input must be cuda tensor"
+    xin = x
+    x = _prep(x, "random_crop")
+    n, c, H, W = x.shape
+    crop_max = W - size
+    if crop_max <= 0:                      # :396-399 passthrough
+        return (xin, None, None) if return_w1_h1 else xin
+    with torch.cuda.device(x.device):
+        if w1 is None:
+            off = _draw_offsets(n, 0, crop_max, x.device)       # random_(0, crop_max): upper bound exclusive
+        else:
+            off = torch.stack([torch.as_tensor(w1).reshape(n), torch.as_tensor(h1).reshape(n)], dim=1)
+            off = off.to(device=x.device, dtype=torch.int32).contiguous()
+        out = torch.empty((n, c, size, size), dtype=torch.float32, device=x.device)
+        L.call("augcl_random_crop", x.data_ptr(), out.data_ptr(), n, c, H, W, int(size), off.data_ptr(), _stream(x))
+    if return_w1_h1:
+        return out, off[:, 0].long(), off[:, 1].long()
+    return out
+
+
+# --------------------------------------------------------------------------------------------
+# random_conv  (src/augmentations.py:265-274)
+# --------------------------------------------------------------------------------------------
+def random_conv(x, *, weights=None):
+    """Per-sample random 3x3 conv (3->3 channels) on replicate-padded x/255, sigmoid, *255.
+
+    weights: optional (n,3,3,3,3) f32 = the reference's per-sample ``torch.randn(3,3,3,3)``."""
+    x = _prep(x, "random_conv")
+    n, c, h, w = x.shape
+    with torch.cuda.device(x.device):
+        if weights is None:
+            wt = torch.empty((n, 3, 3, 3, 3), dtype=torch.float32, device=x.device)
+            L.call("augcl_rng_fill_normal", wt.data_ptr(), wt.numel(), _seed, _next_subsequence(), _stream(x))
+        else:
+            wt = torch.as_tensor(weights).to(device=x.device, dtype=torch.float32).contiguous()
+            if wt.shape != (n, 3, 3, 3, 3):
+                raise ValueError(f"random_conv: weights must be ({n},3,3,3,3), got {tuple(wt.shape)}")
+        out = torch.empty_like(x)
+        L.call("augcl_random_conv", x.data_ptr(), out.data_ptr(), n, c, h, w, wt.data_ptr(), _stream(x))
+    return out
+
+
+# --------------------------------------------------------------------------------------------
+# background bank (stands in for the Places365 / COCO DataLoader, src/augmentations.py:19-86)
+# --------------------------------------------------------------------------------------------
+def set_background_bank(bank) -> None:
+    """Register the device-resident background bank: [M,3,h,w] uint8, or float32 in [0,1]."""
+    global _bank
+    if bank is None:
+        _bank = None
+        return
+    if not (isinstance(bank, torch.Tensor) and bank.is_cuda and bank.dim() == 4 and bank.shape[1] == 3):
+        raise ValueError("background bank must be a CUDA tensor of shape [M,3,h,w]")
+    if bank.dtype not in (torch.uint8, torch.float32):
+        raise ValueError("background bank must be uint8 or float32")
+    _bank = bank.contiguous()
+
+
+def get_background_bank():
+    return _bank
+
+
+def load_dataloader(batch_size, image_size, dataset="coco", *, device=None):
+    """Reference name and dataset check (src/augmentations.py:240-250).  The image folders are not
+    available offline: when no bank is registered, a synthetic u8 bank of SYNTHETIC_BANK_LEN rows is
+    generated on the device (Philox bytes)."""
+    global _bank
+    if dataset not in ("places365_standard", "coco"):
+        raise NotImplementedError(f'overlay has not been implemented for dataset "{dataset}"')
+    if _bank is None:
+        device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        bank = torch.empty((SYNTHETIC_BANK_LEN, 3, image_size, image_size), dtype=torch.uint8, device=device)
+        with torch.cuda.device(device):
+            L.call("augcl_rng_fill_bytes", bank.data_ptr(), bank.numel(), _seed ^ 0xBA4C, 0, _stream(bank))
+        _bank = bank
+
+
+def _bank_for(x: torch.Tensor, who: str, dataset: str):
+    n, c, h, w = x.shape
+    load_dataloader(batch_size=n, image_size=h, dataset=dataset, device=x.device)
+    b = _bank
+    if b.device != x.device:
+        raise ValueError(f"{who}: background bank lives on {b.device}, input on {x.device}")
+    if tuple(b.shape[2:]) != (h, w):
+        raise ValueError(f"{who}: background bank is {tuple(b.shape[2:])}, input images are {(h, w)}")
+    return b, (L.BANK_U8 if b.dtype == torch.uint8 else L.BANK_F32)
+
+
+def _bank_rows(n: int, bank_len: int, bank_idx, device) -> torch.Tensor:
+    if bank_idx is None:
+        out = torch.empty(n, dtype=torch.int64, device=device)
+        L.call("augcl_rng_fill_indices", out.data_ptr(), n, 0, bank_len, _seed, _next_subsequence(), _stream(out))
+        return out
+    t = torch.as_tensor(bank_idx).reshape(-1).to(device=device, dtype=torch.int64).contiguous()
+    if t.numel() != n:
+        raise ValueError(f"bank_idx must have {n} entries, got {t.numel()}")
+    return t
+
+
+# --------------------------------------------------------------------------------------------
+# random_overlay  (src/augmentations.py:253-262)
+# --------------------------------------------------------------------------------------------
+def random_overlay(x, dataset="coco", *, bank_idx=None, alpha=0.5):
+    """((1-alpha)*(x/255) + alpha*img)*255 with img = bank[bank_idx[i]], same image for every frame."""
+    x = _prep(x, "random_overlay")
+    n, c, h, w = x.shape
+    with torch.cuda.device(x.device):
+        bank, bdt = _bank_for(x, "random_overlay", dataset)
+        rows = _bank_rows(n, bank.shape[0], bank_idx, x.device)
+        out = torch.empty_like(x)
+        L.call("augcl_random_overlay", x.data_ptr(), out.data_ptr(), n, c, h, w, bank.data_ptr(), bdt,
+               bank.shape[0], rows.data_ptr(), float(alpha), _stream(x))
+    return out
+
+
+# --------------------------------------------------------------------------------------------
+# splice / CS_splice  (src/augmentations.py:295-306, 309-324; mask :277-284)
+# --------------------------------------------------------------------------------------------
+def _splice(x, thr, variant, who, bank_idx, dataset):
+    x = _prep(x, who)
+    n, c, h, w = x.shape
+    with torch.cuda.device(x.device):
+        bank, bdt = _bank_for(x, who, dataset)
+        rows = _bank_rows(n, bank.shape[0], bank_idx, x.device)
+        out = torch.empty_like(x)
+        L.call("augcl_splice", x.data_ptr(), out.data_ptr(), n, c, h, w, bank.data_ptr(), bdt, bank.shape[0],
+               rows.data_ptr(), float(thr[0]), float(thr[1]), float(thr[2]), variant, _stream(x))
+    return out
+
+
+def splice(x, hue_thres=0, sat_thres=0, val_thres=0.6, *, bank_idx=None, dataset="coco"):
+    """Keep pixels whose HSV exceeds the thresholds, replace the rest by the background;
+    frame f of sample s takes background row (s*k+f) mod n (the reference's batch tiling)."""
+    return _splice(x, (hue_thres, sat_thres, val_thres), L.SPLICE, "splice", bank_idx, dataset)
+
+
+def CS_splice(x, hue_thres=3.5, sat_thres=0, val_thres=0, *, bank_idx=None, dataset="coco"):
+    return _splice(x, (hue_thres, sat_thres, val_thres), L.CS_SPLICE, "CS_splice", bank_idx, dataset)
+
+
+def _not_native(name):
+    def fn(*a, **k):
+        raise NotImplementedError(
+            f"augcl_b200: '{name}' is outside the replay-gather + augmentation hot path (SURVEY.md §8f-3) "
+            "and has no native kernel yet")
+    fn.__name__ = name
+    return fn
+
+
+# same 12 keys as src/augmentations.py:436-449
+aug_to_func = {
+    "grayscale": _not_native("random_grayscale"),
+    "flip": _not_native("random_flip"),
+    "rotate": _not_native("random_rotation"),
+    "conv": random_conv,
+    "shift": random_shift,
+    "color_jitter": _not_native("color_jitter"),
+    "identity": identity,
+    "splice": splice,
+    "crop": random_crop,
+    "cutout_color": _not_native("random_cutout_color"),
+    "CS_splice": CS_splice,
+    "overlay": random_overlay,
+}

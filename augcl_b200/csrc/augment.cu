@@ -366,14 +366,14 @@ extern "C" {
 int augcl_drq_base_grid(int h, int pad, float* out_host) {
   AUGCL_REQUIRE(out_host && h > 0 && pad >= 0, "augcl_drq_base_grid: bad arguments");
   // torch.linspace(-1+eps, 1-eps, steps, dtype=float32)[:h]: fp32 start/end/step, symmetric evaluation
-  // (first half start + step*i, second half end - step*(steps-1-i)).
+  // (first half fma(step, i, start), second half fma(-step, steps-1-i, end): ATen's vectorised CPU kernel fuses).
   const int steps = h + 2 * pad;
   const double eps = 1.0 / (double)steps;
   const float start = (float)(-1.0 + eps), end = (float)(1.0 - eps);
   const float step = steps > 1 ? (end - start) / (float)(steps - 1) : 0.0f;
   const int halfway = steps / 2;
   for (int i = 0; i < h; ++i)
-    out_host[i] = i < halfway ? start + step * (float)i : end - step * (float)(steps - i - 1);
+    out_host[i] = i < halfway ? fmaf(step, (float)i, start) : fmaf(-step, (float)(steps - i - 1), end);
   return AUGCL_OK;
 }
 

@@ -43,6 +43,21 @@ __global__ void __launch_bounds__(256) fill_normal_kernel(float* out, int64_t co
   }
 }
 
+// byte e of a fill = byte (e % 16) of Philox block e / 16 (little-endian words)
+__global__ void __launch_bounds__(256) fill_u8_kernel(uint8_t* out, int64_t count, uint64_t seed, uint64_t subseq) {
+  const int64_t nblk = (count + 15) / 16;
+  const bool vec = (reinterpret_cast<uintptr_t>(out) & 15) == 0;
+  for (int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; b < nblk; b += (int64_t)gridDim.x * blockDim.x) {
+    const uint4 r = philox4x32_10((uint64_t)b, subseq, seed);
+    if (vec && b * 16 + 16 <= count) {
+      reinterpret_cast<uint4*>(out)[b] = r;
+    } else {
+      const uint32_t wds[4] = {r.x, r.y, r.z, r.w};
+      for (int j = 0; j < 16 && b * 16 + j < count; ++j) out[b * 16 + j] = (uint8_t)(wds[j >> 2] >> (8 * (j & 3)));
+    }
+  }
+}
+
 static inline int rng_grid(int64_t count) {
   int64_t blocks = ((count + 3) / 4 + 255) / 256;
   return (int)(blocks < 1 ? 1 : (blocks > kNumSMs * 8 ? kNumSMs * 8 : blocks));
@@ -71,6 +86,13 @@ int augcl_rng_fill_indices(int64_t* out, int64_t count, int64_t lo, int64_t hi, 
                 (long long)lo, (long long)hi);
   fill_randint_kernel<int64_t><<<rng_grid(count), 256, 0, (cudaStream_t)stream>>>(out, count, lo, (uint64_t)(hi - lo), seed,
                                                                                   subsequence);
+  AUGCL_LAUNCHED();
+  return AUGCL_OK;
+}
+
+int augcl_rng_fill_bytes(uint8_t* out, int64_t count, uint64_t seed, uint64_t subsequence, augcl_stream stream) {
+  AUGCL_REQUIRE(out && count > 0, "augcl_rng_fill_bytes: out is NULL or count <= 0");
+  fill_u8_kernel<<<rng_grid((count + 3) / 4), 256, 0, (cudaStream_t)stream>>>(out, count, seed, subsequence);
   AUGCL_LAUNCHED();
   return AUGCL_OK;
 }

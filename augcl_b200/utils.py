@@ -1,0 +1,263 @@
+"""Drop-in for the replay-buffer half of the reference's ``utils`` module
+(/root/reference/src/utils.py:127-322): ``ReplayBuffer`` with the same constructor, attributes
+(``capacity, batch_size, idx, full, last_save, actions, rewards, not_dones``) and methods
+(``add, sample, sample_obs, sample_curl, sample_drq, save, load``) that ``src/train.py`` and
+``src/algorithms/*`` use, and ``LazyFrames``.
+
+The Python list of (LazyFrames, LazyFrames) becomes a device-resident uint8 ring
+(include/augcl_b200.h, "v1" full-stack layout); every ``sample*`` is ONE fused CUDA kernel that
+gathers obs + next_obs by index, casts u8->f32 and (sample_drq / sample_curl) applies the random
+shift / crop on the way out.  No CPU path: the CUDA library is required.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+import torch
+
+from . import _lib as L
+from . import augmentations
+
+
+class LazyFrames(object):
+    """k frames concatenated along channels on demand (src/utils.py:283-322)."""
+
+    def __init__(self, frames, extremely_lazy=True):
+        self._frames = frames
+        self._extremely_lazy = extremely_lazy
+        self._out = None
+
+    @property
+    def frames(self):
+        return self._frames
+
+    def _force(self):
+        if self._extremely_lazy:
+            return np.concatenate(self._frames, axis=0)
+        if self._out is None:
+            self._out = np.concatenate(self._frames, axis=0)
+            self._frames = None
+        return self._out
+
+    def __array__(self, dtype=None, copy=None):
+        out = self._force()
+        return out if dtype is None else out.astype(dtype)
+
+    def __len__(self):
+        return len(self._frames) if self._extremely_lazy else len(self._force())
+
+    def __getitem__(self, i):
+        return self._force()[i]
+
+    def count(self):
+        return len(self._frames) if self._extremely_lazy else self._force().shape[0] // 3
+
+    def frame(self, i):
+        return self._force()[i * 3:(i + 1) * 3]
+
+
+# chunks written by save() unpickle under the reference (its class lives in module ``utils``)
+LazyFrames.__module__ = "utils"
+
+
+class ReplayBuffer(object):
+    """Buffer to store environment transitions — device-resident (src/utils.py:136-280)."""
+
+    STAGE = 256  # transitions staged in pinned host memory between flushes to the ring
+
+    def __init__(self, obs_shape, action_shape, capacity, batch_size, prefill=True, *, device=None,
+                 frame_channels=3):
+        # `prefill` only reserved host memory in the reference (src/utils.py:127-133,143-145); the ring
+        # is allocated up front, so the flag is accepted and has nothing left to do.
+        if not torch.cuda.is_available():
+            raise RuntimeError("augcl_b200.utils.ReplayBuffer needs a CUDA device (no CPU path)")
+        self.capacity = int(capacity)
+        self.batch_size = batch_size
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        c, h, w = obs_shape
+        if c % frame_channels:
+            raise ValueError(f"obs channels {c} not a multiple of frame_channels {frame_channels}")
+        self.obs_shape = (int(c), int(h), int(w))
+        self.action_dim = int(np.prod(action_shape)) if len(action_shape) else 1
+        self.actions = np.empty((self.capacity, *action_shape), dtype=np.float32)
+        self.rewards = np.empty((self.capacity, 1), dtype=np.float32)
+        self.not_dones = np.empty((self.capacity, 1), dtype=np.float32)
+        self.idx = 0
+        self.last_save = 0
+        self.last_requeue_save = 0
+        self.full = False
+        self.refilled = False
+
+        h_ring = C.c_void_p()
+        L.call("augcl_ring_create", C.byref(h_ring), self.device.index or 0, self.capacity, c // frame_channels,
+               frame_channels, h, w, self.action_dim)
+        self._ring = h_ring
+        self._stack_bytes = c * h * w
+        n = min(self.STAGE, self.capacity)
+        self._st_obs = torch.empty((n, c, h, w), dtype=torch.uint8).pin_memory()
+        self._st_next = torch.empty((n, c, h, w), dtype=torch.uint8).pin_memory()
+        self._st_obs_np, self._st_next_np = self._st_obs.numpy(), self._st_next.numpy()
+        self._st_start = 0      # ring slot of staged transition 0
+        self._st_count = 0
+        self._st_event = None   # completion of the last flush (staging must not be overwritten before)
+
+    def __del__(self):
+        ring, self._ring = getattr(self, "_ring", None), None
+        if ring:
+            try:
+                L.lib().augcl_ring_destroy(ring)
+            except Exception:
+                pass
+
+    # ------------------------------------------------------------------ ingest
+    def add(self, obs, action, reward, next_obs, done):
+        """src/utils.py:216-227.  obs / next_obs: LazyFrames or (C,H,W) uint8 arrays."""
+        if self._st_count == 0:
+            if self._st_event is not None:
+                self._st_event.synchronize()
+                self._st_event = None
+            self._st_start = self.idx
+        j = self._st_count
+        self._st_obs_np[j] = np.asarray(obs)
+        self._st_next_np[j] = np.asarray(next_obs)
+        np.copyto(self.actions[self.idx], action)
+        np.copyto(self.rewards[self.idx], reward)
+        np.copyto(self.not_dones[self.idx], not done)
+        self._st_count += 1
+        self.idx = (self.idx + 1) % self.capacity
+        self.full = self.full or self.idx == 0
+        if self._st_count == self._st_obs.shape[0] or self.idx == 0:   # staging full, or about to wrap
+            self._flush()
+
+    def _stream(self):
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def _flush(self):
+        """Pending staged transitions -> ring (one async H2D per field)."""
+        n = self._st_count
+        if n == 0:
+            return
+        s0 = self._st_start
+        a = np.ascontiguousarray(self.actions[s0:s0 + n]).reshape(n, -1)
+        L.call("augcl_ring_put", self._ring, s0, n, self._st_obs.data_ptr(), self._st_next.data_ptr(),
+               a.ctypes.data, self.rewards[s0:s0 + n].ctypes.data, self.not_dones[s0:s0 + n].ctypes.data,
+               self._stream())
+        # the scalar sources are pageable (copied synchronously by the driver); the frame staging is pinned
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.device))
+        self._st_event = ev
+        self._st_count = 0
+
+    # ------------------------------------------------------------------ indices
+    def _get_idxs(self, n=None):
+        """src/utils.py:229-232 — same numpy global-RNG draw as the reference."""
+        if n is None:
+            n = self.batch_size
+        return np.random.randint(0, self.capacity if self.full else self.idx, size=n)
+
+    def _dev_idxs(self, idxs):
+        if isinstance(idxs, torch.Tensor):
+            return idxs.to(device=self.device, dtype=torch.int64).contiguous()
+        return torch.from_numpy(np.ascontiguousarray(idxs, dtype=np.int64)).to(self.device, non_blocking=True)
+
+    # ------------------------------------------------------------------ the fused sample kernel
+    def _sample(self, idxs, *, obs=True, next_obs=True, scalars=True, aug=L.AUG_NONE, off_obs=None,
+                off_next=None, pad_or_size=0, normalize=False):
+        """One augcl_ring_sample launch.  Returns (obs, actions, rewards, next_obs, not_dones); entries
+        that were not requested are None."""
+        self._flush()
+        with torch.cuda.device(self.device):
+            di = self._dev_idxs(idxs)
+            B = di.numel()
+            c, h, w = self.obs_shape
+            ho, wo = (pad_or_size, pad_or_size) if aug == L.AUG_CROP else (h, w)
+            dev = self.device
+            o = torch.empty((B, c, ho, wo), dtype=torch.float32, device=dev) if obs else None
+            no = torch.empty((B, c, ho, wo), dtype=torch.float32, device=dev) if next_obs else None
+            act = torch.empty((B,) + self.actions.shape[1:], dtype=torch.float32, device=dev) if scalars else None
+            rew = torch.empty((B, 1), dtype=torch.float32, device=dev) if scalars else None
+            nd = torch.empty((B, 1), dtype=torch.float32, device=dev) if scalars else None
+            p = lambda t: None if t is None else t.data_ptr()  # noqa: E731
+            L.call("augcl_ring_sample", self._ring, di.data_ptr(), B, p(o), p(no), p(act), p(rew), p(nd), aug,
+                   p(off_obs), p(off_next), int(pad_or_size), 1 if normalize else 0, self._stream())
+        return o, act, rew, no, nd
+
+    def _offsets(self, B, lo, hi, supplied):
+        if supplied is not None:
+            return augmentations._dev_i32(supplied, B, self.device, "ReplayBuffer")
+        with torch.cuda.device(self.device):
+            return augmentations._draw_offsets(B, lo, hi, self.device)
+
+    # ------------------------------------------------------------------ reference API
+    def tensor_buffer_samples(self, idxs):
+        """src/utils.py:206-214 (note the return order differs from sample())."""
+        obs, actions, rewards, next_obs, not_dones = self._sample(idxs)
+        return obs, next_obs, actions, rewards, not_dones
+
+    def sample(self, n=None, idxs=None):
+        """src/utils.py:272-280."""
+        if idxs is None:
+            idxs = self._get_idxs(n)
+        return self._sample(idxs)
+
+    def sample_obs(self, n=None):
+        """src/utils.py:242-245."""
+        return self._sample(self._get_idxs(n), next_obs=False, scalars=False)[0]
+
+    def sample_curl(self, n=None, *, idxs=None, size=84, offsets=None):
+        """src/utils.py:247-258: three independent random crops (pos, obs, next_obs), fused into the
+        gather.  offsets: optional dict {"pos","obs","next_obs"} -> (B,2) (w1,h1) draws."""
+        if idxs is None:
+            idxs = self._get_idxs(n)
+        B = len(idxs)
+        c, h, w = self.obs_shape
+        crop_max = w - size
+        if crop_max <= 0:   # random_crop passthrough (src/augmentations.py:396-399)
+            obs, actions, rewards, next_obs, not_dones = self._sample(idxs)
+            return obs, actions, rewards, next_obs, not_dones, obs.clone()
+        offsets = offsets or {}
+        o_pos = self._offsets(B, 0, crop_max, offsets.get("pos"))       # draw order of the reference
+        o_obs = self._offsets(B, 0, crop_max, offsets.get("obs"))
+        o_next = self._offsets(B, 0, crop_max, offsets.get("next_obs"))
+        obs, actions, rewards, next_obs, not_dones = self._sample(
+            idxs, aug=L.AUG_CROP, off_obs=o_obs, off_next=o_next, pad_or_size=size)
+        pos = self._sample(idxs, next_obs=False, scalars=False, aug=L.AUG_CROP, off_obs=o_pos, pad_or_size=size)[0]
+        return obs, actions, rewards, next_obs, not_dones, pos
+
+    def sample_drq(self, n=None, pad=4, *, idxs=None, offsets=None):
+        """src/utils.py:260-270: gather + random_shift of obs and next_obs in one kernel.
+        offsets: optional dict {"obs","next_obs"} -> (B,2) (row,col) draws in [0, 2*pad]."""
+        if idxs is None:
+            idxs = self._get_idxs(n)
+        B = len(idxs)
+        offsets = offsets or {}
+        o_obs = self._offsets(B, 0, 2 * pad + 1, offsets.get("obs"))
+        o_next = self._offsets(B, 0, 2 * pad + 1, offsets.get("next_obs"))
+        return self._sample(idxs, aug=L.AUG_SHIFT, off_obs=o_obs, off_next=o_next, pad_or_size=pad)
+
+    def sample_svea(self, n=None, pad=4, *, idxs=None, offsets=None):
+        """The SVEA / AugCL access pattern (src/algorithms/svea.py:66-70, augcl.py:69-72) as one kernel:
+        obs is shifted, next_obs is returned un-augmented."""
+        if idxs is None:
+            idxs = self._get_idxs(n)
+        o_obs = self._offsets(len(idxs), 0, 2 * pad + 1, offsets)
+        return self._sample(idxs, aug=L.AUG_SHIFT, off_obs=o_obs, off_next=None, pad_or_size=pad)
+
+    def fill_synthetic(self, count=None, seed=0):
+        """Benchmarks/tests: fill slots [0,count) with Philox frames and scalars on the device."""
+        count = self.capacity if count is None else int(count)
+        self._flush()
+        L.call("augcl_ring_fill_synthetic", self._ring, count, int(seed), self._stream())
+        n = count
+        a = np.empty((n, self.action_dim), dtype=np.float32)
+        L.call("augcl_ring_get", self._ring, 0, n, None, None, a.ctypes.data, self.rewards.ctypes.data,
+               self.not_dones.ctypes.data, self._stream())
+        torch.cuda.current_stream(self.device).synchronize()
+        self.actions[:n] = a.reshape((n,) + self.actions.shape[1:])
+        self.idx = count % self.capacity
+        self.full = self.full or count == self.capacity
+
+    def ring_bytes(self):
+        return int(L.lib().augcl_ring_bytes(self._ring))

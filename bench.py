@@ -1,0 +1,376 @@
+#!/usr/bin/env python
+"""bench.py — replay gather + random_shift throughput (BASELINE.json configs[1]) on N B200s.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--batch 128] [--impl ours|reference]
+
+A "step" is one pass of the hot path over one minibatch: gather B transitions (obs + next_obs,
+9x84x84 u8 each) from the 100k-transition device ring by random index, cast u8->f32 and apply
+random_shift(pad=4) to both (the DrQ K=M=1 pattern; ReplayBuffer.sample_drq) — ONE kernel launch.
+Prints ONE JSON line (rank 0).  `value` = samples/s with everything resident in HBM, timed with
+CUDA events on the launching stream; `e2e` = the same through ReplayBuffer.sample_drq() with HOST
+indices/offsets (pinned H2D inside the timed region) and a D2H read of the step's rewards.
+Multi-GPU (torchrun): one ring shard + one seed per rank, no data-path collective; elapsed = max
+over ranks.  `--impl reference` times the reference's CPU path for the same step on the host cores.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+CAP, K_FRAMES, S, A_DIM, PAD = 100_000, 3, 84, 6, 4
+C = 3 * K_FRAMES
+S8 = C * S * S                      # 63 504 B: one u8 stack
+BYTES_PER_SAMPLE = 2 * S8 + 2 * 4 * S8   # read obs+next u8, write obs+next f32 = 635 040 B
+METRIC = "augmented samples/sec (9x84x84, gather+aug)"
+UNIT = "samples/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20000)
+    ap.add_argument("--warmup", type=int, default=200)
+    ap.add_argument("--batch", type=int, default=128)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-sweep", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU budget of the cpu_baseline leg")
+    return ap.parse_args()
+
+
+def config_dict(args, n_gpus):
+    return {"workload": "BASELINE.json configs[1]: DrQ replay sample + random_shift(pad=4) on obs and next_obs, "
+                        f"batch {args.batch}, frame_stack 3, 84x84, {CAP}-transition ring per GPU",
+            "batch_per_gpu": args.batch, "global_batch": args.batch * n_gpus, "capacity_per_gpu": CAP,
+            "obs_shape": [C, S, S], "pad": PAD, "parallelism": f"{n_gpus} independent ring shards, no collectives",
+            "l2_policy": "inputs larger than L2: 12.7 GB ring, fresh random indices every step; outputs rotate over "
+                         "8 buffer sets (520 MB at batch 128)"}
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU legs: the reference's algorithm for one step, on the host cores.  The only place bench.py
+# touches oracle/ (as the measured *baseline*, never as the product path).
+# ------------------------------------------------------------------------------------------------
+def cpu_step_factory(batch, cap_host=20_000, seed=0):
+    """Returns (step_fn, kind, sample_description).  Uses the reference's own code when
+    /root/reference is mounted (build container), else the oracle port (GPU box)."""
+    import torch
+    from oracle import augcl_oracle as O
+    from oracle import ref_harness as R
+    rng = np.random.RandomState(seed)
+    frames = rng.randint(0, 256, (cap_host + K_FRAMES, 3, S, S), dtype=np.uint8)
+    if R.available():
+        kind = "reference"
+        buf = R.ref_replay_buffer((C, S, S), (A_DIM,), cap_host, batch)
+        lf = R.ref_lazy_frames
+    else:
+        kind = "port"
+        buf = O.HostRing((C, S, S), (A_DIM,), cap_host, batch)
+        lf = O.LazyFrames
+    act = np.zeros(A_DIM, dtype=np.float32)
+    for t in range(cap_host):
+        buf.add(lf(frames[t:t + K_FRAMES]), act, 0.0, lf(frames[t + 1:t + 1 + K_FRAMES]), False)
+
+    def step():
+        idxs = rng.randint(0, cap_host, size=batch)
+        o1, o2 = rng.randint(0, 2 * PAD + 1, (batch, 2)), rng.randint(0, 2 * PAD + 1, (batch, 2))
+        if kind == "reference":
+            obs, a, r, nxt, nd = R.ref_sample(buf, idxs)
+            return R.ref_random_shift(obs, o1, PAD), R.ref_random_shift(nxt, o2, PAD)
+        obs, a, r, nxt, nd = buf.sample(idxs)
+        return O.random_shift_int(obs, o1, PAD), O.random_shift_int(nxt, o2, PAD)
+
+    desc = (f"ReplayBuffer._encode_obses + .float() + random_shift(pad={PAD}) on obs and next_obs, batch {batch}, "
+            f"host ring of {cap_host} transitions (frames shared like FrameStack), torch threads = all cores")
+    return step, kind, desc
+
+
+def time_cpu(step, budget_s, min_steps=3):
+    import torch
+    step()                                   # warm-up
+    n, t0 = 0, time.perf_counter()
+    while True:
+        step()
+        n += 1
+        el = time.perf_counter() - t0
+        if n >= min_steps and el >= budget_s:
+            return n, el
+
+
+def run_reference(args):
+    import torch
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    step, kind, desc = cpu_step_factory(args.batch)
+    for _ in range(max(1, min(args.warmup, 3))):
+        step()
+    steps = max(1, min(args.steps, 300))     # bounded: ~20 ms per step on a server core
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    el = time.perf_counter() - t0
+    value = steps * args.batch / el
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+        "warmup": min(args.warmup, 3), "ms_per_step": 1e3 * el / steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u8->f32", "data": "synthetic", "config": config_dict(args, args.gpus),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind,
+                         "sample": f"{steps} steps: " + desc},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks during the timed region (NVML; same fields as the recipe's nvidia-smi line)
+# ------------------------------------------------------------------------------------------------
+class ClockSampler(threading.Thread):
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
+
+    def __init__(self, index, period_s=0.005):
+        super().__init__(daemon=True)
+        self.index, self.period, self.stop_flag = index, period_s, threading.Event()
+        self.sm, self.reasons, self.max_mhz, self.err = [], set(), None, None
+
+    def run(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            while not self.stop_flag.is_set():
+                self.sm.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                bits = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                for bit, name in self.REASONS.items():
+                    if bits & bit:
+                        self.reasons.add(name)
+                time.sleep(self.period)
+        except Exception as e:  # reported, never fatal
+            self.err = repr(e)
+
+    def summary(self):
+        self.stop_flag.set()
+        self.join(timeout=2)
+        sm = sorted(self.sm)
+        out = {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+               "samples": len(sm)}
+        if self.err:
+            out["error"] = self.err
+        return out
+
+
+def physical_gpu_index(local_rank):
+    vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+    if vis:
+        try:
+            return int(vis.split(",")[local_rank])
+        except Exception:
+            return local_rank
+    return local_rank
+
+
+# ------------------------------------------------------------------------------------------------
+# our arm
+# ------------------------------------------------------------------------------------------------
+def run_ours(args):
+    import ctypes
+    import torch
+    import torch.distributed as dist
+    import __graft_entry__ as entry
+    entry.build()
+    from augcl_b200 import _lib as L
+    from augcl_b200 import utils as U
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; augcl_b200 has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    B, K, W = args.batch, args.steps, max(args.warmup, 3)
+
+    # ---- one ring shard per rank, synthetic frames, per-rank seed
+    buf = U.ReplayBuffer((C, S, S), (A_DIM,), CAP, B, device=dev)
+    buf.fill_synthetic(seed=1000 + rank)
+    g = torch.Generator(device="cpu").manual_seed(rank)
+    n_sets = 8
+    outs = [(torch.empty((B, C, S, S), dtype=torch.float32, device=dev), torch.empty((B, C, S, S), dtype=torch.float32, device=dev),
+             torch.empty((B, A_DIM), device=dev), torch.empty((B, 1), device=dev), torch.empty((B, 1), device=dev))
+            for _ in range(n_sets)]
+    T = K + W
+    idx = torch.randint(0, CAP, (T, B), generator=g).to(dev)                       # resident before the timed region
+    off = torch.randint(0, 2 * PAD + 1, (T, 2, B, 2), generator=g, dtype=torch.int32).to(dev)
+    stream = torch.cuda.current_stream(dev)
+    sp = stream.cuda_stream
+    ring = buf._ring
+    fn = L.lib().augcl_ring_sample
+    idx_p, off_p = idx.data_ptr(), off.data_ptr()
+    ptrs = [tuple(t.data_ptr() for t in o) for o in outs]
+
+    def step(t):
+        o = ptrs[t % n_sets]
+        rc = fn(ring, idx_p + t * B * 8, B, o[0], o[1], o[2], o[3], o[4], L.AUG_SHIFT, off_p + t * 16 * B,
+                off_p + t * 16 * B + 8 * B, PAD, 0, sp)
+        if rc:
+            raise RuntimeError(L.lib().augcl_last_error().decode())
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    for t in range(W):
+        step(t)
+    barrier()
+    sampler = ClockSampler(physical_gpu_index(local))
+    sampler.start()
+    l0 = L.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for t in range(W, T):
+        step(t)
+    e1.record(stream)
+    barrier()
+    launches = L.launch_count() - l0
+    clocks = sampler.summary()
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        tmax = torch.tensor([ms], device=dev)
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)       # off the data path: one scalar after timing stops
+        ms = float(tmax.item())
+    value = world * K * B / (ms * 1e-3)
+
+    # ---- e2e: public API with HOST indices/offsets, pinned H2D + D2H of the rewards every step
+    Ke = min(K, 2000)
+    h_idx = torch.randint(0, CAP, (Ke + 3, B), generator=g).pin_memory()
+    h_off = torch.randint(0, 2 * PAD + 1, (Ke + 3, 2, B, 2), generator=g, dtype=torch.int32).pin_memory()
+    h_rew = torch.empty((B, 1), dtype=torch.float32).pin_memory()
+
+    def e2e_step(t):
+        obs, act, rew, nxt, nd = buf.sample_drq(pad=PAD, idxs=h_idx[t], offsets={"obs": h_off[t, 0], "next_obs": h_off[t, 1]})
+        h_rew.copy_(rew, non_blocking=True)
+        stream.synchronize()
+        return obs
+
+    for t in range(3):
+        e2e_step(t)
+    barrier()
+    t0 = time.perf_counter()
+    for t in range(3, Ke + 3):
+        e2e_step(t)
+    torch.cuda.synchronize(dev)
+    el = time.perf_counter() - t0
+    if world > 1:
+        tmax = torch.tensor([el], device=dev, dtype=torch.float64)
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        el = float(tmax.item())
+    e2e = {"value": world * Ke * B / el, "unit": UNIT, "h2d_bytes_per_step": B * 8 + 2 * B * 2 * 4,
+           "d2h_bytes_per_step": B * 4, "steps": Ke, "ms_per_step": 1e3 * el / Ke,
+           "api": "ReplayBuffer.sample_drq(idxs=host, offsets=host) + D2H of rewards + stream sync per step"}
+    return dict(buf=buf, dev=dev, world=world, rank=rank, ms=ms, value=value, launches=launches, clocks=clocks, e2e=e2e,
+                step_raw=fn, K=K, W=W, B=B)
+
+
+def batch_sweep(res, batches=(128, 256, 512, 1024, 2048, 4096, 8192, 16384)):
+    """BASELINE.json configs[4] in brief (extra evidence, not the bench line): same step at larger batches,
+    device-timed, fresh indices each iteration."""
+    import torch
+    from augcl_b200 import _lib as L
+    buf, dev = res["buf"], res["dev"]
+    peak = load_peaks()[0]
+    out = []
+    g = torch.Generator().manual_seed(99)
+    stream = torch.cuda.current_stream(dev)
+    for B in batches:
+        iters = max(20, min(400, (1 << 19) // B))
+        n_sets = max(2, min(8, (600 << 20) // (2 * B * S8 * 4)))
+        o = [(torch.empty((B, C, S, S), device=dev), torch.empty((B, C, S, S), device=dev)) for _ in range(n_sets)]
+        idx = torch.randint(0, CAP, (iters + 3, B), generator=g).to(dev)
+        off = torch.randint(0, 2 * PAD + 1, (iters + 3, 2, B, 2), generator=g, dtype=torch.int32).to(dev)
+
+        def step(t):
+            a, b = o[t % n_sets]
+            L.call("augcl_ring_sample", buf._ring, idx[t].data_ptr(), B, a.data_ptr(), b.data_ptr(), None, None, None,
+                   L.AUG_SHIFT, off[t, 0].data_ptr(), off[t, 1].data_ptr(), PAD, 0, stream.cuda_stream)
+        for t in range(3):
+            step(t)
+        torch.cuda.synchronize(dev)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for t in range(3, iters + 3):
+            step(t)
+        e1.record(stream)
+        torch.cuda.synchronize(dev)
+        ms = e0.elapsed_time(e1) / iters
+        gbs = B * BYTES_PER_SAMPLE / (ms * 1e-3) / 1e9
+        out.append({"batch": B, "us_per_step": round(ms * 1e3, 2), "samples_per_s": round(B / (ms * 1e-3)),
+                    "GB/s": round(gbs, 1), "frac": round(gbs / peak, 4)})
+        del o
+    return out
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.isfile(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        return run_reference(args)
+    res = run_ours(args)
+    import torch
+    import torch.distributed as dist
+    world, rank, K, B = res["world"], res["rank"], res["K"], res["B"]
+    if rank == 0:
+        peak, peak_src = load_peaks()
+        us = res["ms"] * 1e3 / K
+        achieved = B * BYTES_PER_SAMPLE / (us * 1e-6) / 1e9
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "traffic.json")     # dram bytes per launch from the ncu --set full capture
+        if os.path.isfile(tp):
+            traffic = json.load(open(tp)).get(f"ring_sample_b{B}")
+        line = {
+            "metric": METRIC, "value": res["value"], "unit": UNIT, "n_gpus": world, "steps": K, "warmup": res["W"],
+            "ms_per_step": res["ms"] / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u8->f32", "data": "synthetic", "config": config_dict(args, world),
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": traffic, "kernel": "ring_sample_tma_kernel<21>", "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": B * BYTES_PER_SAMPLE,
+                         "note": "per-launch time = timed region / steps (one launch per step, CUDA events on the launching stream)"},
+            "clocks": res["clocks"], "e2e": res["e2e"], "gpu_launches": res["launches"],
+        }
+        if world == 1 and not args.no_sweep:
+            line["batch_sweep"] = batch_sweep(res)
+        if world == 1 and not args.no_cpu_baseline:
+            cores = os.cpu_count() or 1
+            torch.set_num_threads(cores)
+            step, kind, desc = cpu_step_factory(B)
+            n, el = time_cpu(step, args.cpu_seconds)
+            line["cpu_baseline"] = {"value": n * B / el, "unit": UNIT, "cores": cores, "kind": kind,
+                                    "sample": f"{n} steps in {el:.1f} s: " + desc}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

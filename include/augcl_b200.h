@@ -163,6 +163,10 @@ int augcl_rng_fill_indices(int64_t* out, int64_t count, int64_t lo, int64_t hi, 
                            uint64_t subsequence, augcl_stream stream);
 int augcl_rng_fill_normal(float* out, int64_t count, uint64_t seed, uint64_t subsequence,
                           augcl_stream stream);
+/* Uniform bytes (synthetic frames / background bank; stands in for the absent Places365 / COCO
+ * images of src/augmentations.py:19-74).  Byte e = byte (e % 16) of Philox block e / 16. */
+int augcl_rng_fill_bytes(uint8_t* out, int64_t count, uint64_t seed, uint64_t subsequence,
+                         augcl_stream stream);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,155 @@
+"""GPU parity of the device-resident replay ring and its fused sample kernel
+(augcl_b200.utils.ReplayBuffer -> augcl_ring_* C ABI) against the reference's recorded outputs
+(tests/golden/replay_*.npz), the CPU oracle, and size-independent properties at BASELINE.json's
+full size (100k-transition ring)."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import REPLAY_CASES
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def U():
+    from augcl_b200 import utils
+    return utils
+
+
+@pytest.fixture(scope="module")
+def O():
+    from oracle import augcl_oracle
+    return augcl_oracle
+
+
+def replay_into(d, buf, LF):
+    k, fr = int(d["k"]), d["frames"]
+    for t in range(len(d["actions"])):
+        buf.add(LF(list(fr[t:t + k])), d["actions"][t], d["rewards"][t], LF(list(fr[t + 1:t + 1 + k])), bool(d["dones"][t]))
+
+
+@pytest.mark.parametrize("name", REPLAY_CASES)
+def test_add_sample_against_reference_golden(U, golden, name):
+    d = golden(name)
+    S, k = d["frames"].shape[-1], int(d["k"])
+    buf = U.ReplayBuffer((3 * k, S, S), d["actions"].shape[1:], int(d["cap"]), len(d["idxs"]))
+    replay_into(d, buf, U.LazyFrames)
+    assert buf.idx == int(d["end_idx"]) and buf.full == bool(d["end_full"])
+    obs, act, rew, nxt, nd = buf.sample(idxs=d["idxs"])
+    assert obs.dtype == torch.float32 and obs.is_cuda and obs.is_contiguous()
+    assert torch.equal(obs.cpu(), torch.from_numpy(d["out_obs"]).float())
+    assert torch.equal(nxt.cpu(), torch.from_numpy(d["out_next"]).float())
+    assert torch.equal(act.cpu(), torch.from_numpy(d["out_act"]))
+    assert torch.equal(rew.cpu(), torch.from_numpy(d["out_rew"])) and rew.shape == (len(d["idxs"]), 1)
+    assert torch.equal(nd.cpu(), torch.from_numpy(d["out_nd"]))
+    o2, n2, a2, r2, nd2 = buf.tensor_buffer_samples(d["idxs"])      # reference's other return order
+    assert torch.equal(o2, obs) and torch.equal(n2, nxt) and torch.equal(a2, act)
+
+
+@pytest.mark.parametrize("S,size,pad", [(84, 64, 4), (100, 84, 4), (21, 16, 3), (18, 12, 2)])
+def test_fused_samplers_against_oracle(U, O, S, size, pad):
+    """sample_drq / sample_curl / sample_svea / sample_obs == oracle gather followed by oracle aug."""
+    rng = np.random.RandomState(S)
+    cap, k, A_, B = 50, 3, 5, 13
+    buf = U.ReplayBuffer((3 * k, S, S), (A_,), cap, B)
+    ora = O.HostRing((3 * k, S, S), (A_,), cap, B)
+    frames = rng.randint(0, 256, (70 + k, 3, S, S)).astype(np.uint8)
+    for t in range(70):     # wraps the ring (cap 50)
+        a, r, dn = rng.randn(A_).astype(np.float32), float(rng.randn()), bool(rng.rand() < 0.2)
+        buf.add(U.LazyFrames(list(frames[t:t + k])), a, r, U.LazyFrames(list(frames[t + 1:t + 1 + k])), dn)
+        ora.add(O.LazyFrames(frames[t:t + k]), a, r, O.LazyFrames(frames[t + 1:t + 1 + k]), dn)
+    assert (buf.idx, buf.full) == (ora.idx, ora.full)
+    idxs = rng.randint(0, cap, size=B)
+    o_obs, o_act, o_rew, o_next, o_nd = ora.sample(idxs)
+
+    off = {"obs": rng.randint(0, 2 * pad + 1, (B, 2)), "next_obs": rng.randint(0, 2 * pad + 1, (B, 2))}
+    obs, act, rew, nxt, nd = buf.sample_drq(pad=pad, idxs=idxs, offsets=off)
+    assert torch.equal(obs.cpu(), O.random_shift_int(o_obs, off["obs"], pad))
+    assert torch.equal(nxt.cpu(), O.random_shift_int(o_next, off["next_obs"], pad))
+    assert torch.equal(act.cpu(), o_act) and torch.equal(rew.cpu(), o_rew) and torch.equal(nd.cpu(), o_nd)
+
+    obs, _, _, nxt, _ = buf.sample_svea(pad=pad, idxs=idxs, offsets=off["obs"])
+    assert torch.equal(obs.cpu(), O.random_shift_int(o_obs, off["obs"], pad)) and torch.equal(nxt.cpu(), o_next)
+
+    co = {key: rng.randint(0, S - size, (B, 2)) for key in ("pos", "obs", "next_obs")}
+    co["obs"][0] = (0, S - size - 1)
+    obs, act, rew, nxt, nd, pos = buf.sample_curl(idxs=idxs, size=size, offsets=co)
+    assert obs.shape == (B, 3 * k, size, size)
+    assert torch.equal(obs.cpu(), O.random_crop(o_obs, size, co["obs"][:, 0], co["obs"][:, 1]))
+    assert torch.equal(nxt.cpu(), O.random_crop(o_next, size, co["next_obs"][:, 0], co["next_obs"][:, 1]))
+    assert torch.equal(pos.cpu(), O.random_crop(o_obs, size, co["pos"][:, 0], co["pos"][:, 1]))
+
+    np.random.seed(11)
+    want_idx = np.random.randint(0, cap, size=B)
+    np.random.seed(11)
+    assert torch.equal(buf.sample_obs().cpu(), ora.sample(want_idx)[0])      # same numpy index stream as the reference
+
+    # staging A/B: the generic (unstaged) kernel returns the same tensors
+    from augcl_b200 import _lib as L
+    a = buf.sample_drq(pad=pad, idxs=idxs, offsets=off)
+    L.set_option("staging", "generic")
+    try:
+        b = buf.sample_drq(pad=pad, idxs=idxs, offsets=off)
+    finally:
+        L.set_option("staging", "tma")
+    assert all(torch.equal(p, q) for p, q in zip(a, b))
+
+
+def test_full_size_ring_properties(U):
+    """BASELINE.json config 2 at full size: 100k-transition ring, k=3, 84x84, batch 128 (and 4096)."""
+    from augcl_b200 import augmentations as A
+    cap = 100_000
+    buf = U.ReplayBuffer((9, 84, 84), (6,), cap, 128)
+    buf.fill_synthetic(seed=7)
+    assert buf.full and buf.idx == 0
+    assert buf.ring_bytes() >= 2 * cap * 9 * 84 * 84
+    g = torch.Generator().manual_seed(0)
+    for B in (128, 4096):
+        idxs = torch.randint(0, cap, (B,), generator=g)
+        idxs[0], idxs[1] = 0, cap - 1                       # extreme slots
+        obs, act, rew, nxt, nd = buf.sample(idxs=idxs.numpy())
+        # integer-valued pixels in 0..255, exact
+        assert torch.equal(obs, obs.round()) and float(obs.min()) >= 0 and float(obs.max()) <= 255
+        # idempotence / determinism: same indices -> same bytes
+        obs2 = buf.sample(idxs=idxs.numpy())[0]
+        assert torch.equal(obs, obs2)
+        # duplicated indices give duplicated rows
+        dup = torch.cat([idxs[:5], idxs[:5]])
+        od = buf.sample(idxs=dup.numpy())[0]
+        assert torch.equal(od[:5], od[5:]) and torch.equal(od[:5], obs[:5])
+        # fused shift == stand-alone shift kernel applied to the plain sample (two independent kernels)
+        off_o, off_n = torch.randint(0, 9, (B, 2), generator=g), torch.randint(0, 9, (B, 2), generator=g)
+        so, _, _, sn, _ = buf.sample_drq(idxs=idxs.numpy(), offsets={"obs": off_o, "next_obs": off_n})
+        assert torch.equal(so, A.random_shift(obs, 4, offsets=off_o)) and torch.equal(sn, A.random_shift(nxt, 4, offsets=off_n))
+        # centre offsets are the identity
+        ident = torch.full((B, 2), 4)
+        io = buf.sample_drq(idxs=idxs.numpy(), offsets={"obs": ident, "next_obs": ident})[0]
+        assert torch.equal(io, obs)
+        # checksum of checksums against the raw bytes read back through ring_get
+        raw = torch.empty((8, 9, 84, 84), dtype=torch.uint8)
+        from augcl_b200 import _lib as L
+        s0 = int(idxs[2]) if int(idxs[2]) + 8 <= cap else 0
+        L.call("augcl_ring_get", buf._ring, s0, 8, raw.data_ptr(), None, None, None, None, None)
+        torch.cuda.synchronize()
+        got = buf.sample(idxs=np.arange(s0, s0 + 8))[0]
+        assert torch.equal(got.cpu(), raw.float())
+        assert act.shape == (B, 6) and rew.shape == (B, 1) and nd.shape == (B, 1)
+        assert torch.equal(act.cpu(), torch.from_numpy(buf.actions[idxs.numpy()]))
+        assert torch.equal(nd.cpu(), torch.from_numpy(buf.not_dones[idxs.numpy()]))
+
+
+def test_normalize_flag_and_empty_requests(U):
+    buf = U.ReplayBuffer((9, 84, 84), (2,), 64, 8)
+    buf.fill_synthetic(seed=1)
+    idxs = np.arange(8)
+    o = buf._sample(idxs)[0]
+    on = buf._sample(idxs, normalize=True)[0]
+    assert torch.equal(on, o / 255.0)            # IEEE division, same as NormalizeImg (modules.py:85-90)
+    only_next = buf._sample(idxs, obs=False, scalars=False)
+    assert only_next[0] is None and only_next[1] is None and only_next[3] is not None
+    from augcl_b200._lib import AugclError
+    with pytest.raises(AugclError):
+        buf._sample(idxs, obs=False, next_obs=False)
+    with pytest.raises(AugclError):
+        buf._sample(np.zeros(0, dtype=np.int64))
