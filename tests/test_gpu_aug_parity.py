@@ -57,7 +57,7 @@ def test_against_reference_golden(A, golden, name):
         cs = A.splice(dev(d["conv_out"]), 0, 0, 0.6, bank_idx=rows)
         assert torch.equal(cs.cpu(), torch.from_numpy(d["conv_splice_out"]))
         # f32 bank in [0,1] (what the reference's loader yields) gives the same results as the u8 bank
-        A.set_background_bank(bank.float() / 255.0)
+        A.set_background_bank((bank.cpu().float() / 255.0).cuda())    # IEEE division on the host, like ToTensor
         assert torch.equal(A.splice(x, 0, 0, 0.6, bank_idx=rows).cpu(), torch.from_numpy(d["splice_out_06"]))
         assert norm_err(A.random_overlay(x, bank_idx=rows), d["overlay_out"]) <= TOL_NORM
         if "crop_out" in d:
