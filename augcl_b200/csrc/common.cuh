@@ -132,4 +132,24 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, u
       : "memory");
 }
 
+
+// 16-byte store through the global (not generic) address space: STG.E.128.
+__device__ __forceinline__ void st_global_f4(float4* ptr, const float4& v) {
+  asm volatile("st.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(__cvta_generic_to_global(ptr)), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+// Programmatic dependent launch (PDL): a kernel launched with the programmatic-stream-serialization
+// attribute may become resident while its predecessor drains; pdl_wait() blocks until the predecessor
+// has completed and its writes are visible, pdl_launch_dependents() lets the successor start early.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+// Byte selector for replicate padding of a 4-pixel group.  The group wants columns c0..c0+3 of a row of
+// width W; the word actually loaded starts at cs = clamp(c0, 0, W-4).  d = clamp(c0 - cs, -4, 4) and
+// output byte j must take loaded byte clamp(j + d, 0, 3): a 16-bit PRMT selector cut out of the constant
+// 0x3333'3210'0000 (d = 0 -> 0x3210 identity, d = -1 -> 0x2100, d = +1 -> 0x3321, |d| = 4 -> all edge).
+__device__ __forceinline__ uint32_t edge_selector(int d) {
+  return __funnelshift_rc(0x32100000u, 0x00003333u, (uint32_t)(4 * (d + 4))) & 0xFFFFu;
+}
+
 }  // namespace augcl

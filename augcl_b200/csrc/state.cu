@@ -6,8 +6,10 @@
 namespace augcl {
 std::atomic<int64_t> g_launches{0};
 std::atomic<int> g_staging{0};
-std::atomic<int> g_sample_stages{3};
+std::atomic<int> g_sample_stages{0};   // 0 = auto (4 when a CTA gets few units, else 2: scripts/tune_sample.py)
 std::atomic<int> g_sample_ctas_per_sm{6};
+std::atomic<int> g_sample_pdl{1};
+std::atomic<int> g_sample_band{1};
 static thread_local std::string t_error;
 void set_error(const std::string& msg) { t_error = msg; }
 }  // namespace augcl
@@ -28,7 +30,7 @@ int augcl_set_option(const char* key, const char* value) {
   }
   if (!strcmp(key, "sample_stages")) {
     int v = atoi(value);
-    AUGCL_REQUIRE(v >= 1 && v <= 8, "sample_stages must be in [1,8]");
+    AUGCL_REQUIRE(v >= 0 && v <= 8, "sample_stages must be in [0,8] (0 = auto)");
     g_sample_stages = v; return AUGCL_OK;
   }
   if (!strcmp(key, "sample_ctas_per_sm")) {
@@ -36,6 +38,8 @@ int augcl_set_option(const char* key, const char* value) {
     AUGCL_REQUIRE(v >= 1 && v <= 16, "sample_ctas_per_sm must be in [1,16]");
     g_sample_ctas_per_sm = v; return AUGCL_OK;
   }
+  if (!strcmp(key, "sample_pdl")) { g_sample_pdl = atoi(value) != 0; return AUGCL_OK; }
+  if (!strcmp(key, "sample_band")) { g_sample_band = atoi(value) != 0; return AUGCL_OK; }
   AUGCL_FAIL(AUGCL_ERR_BAD_ARG, "augcl_set_option: unknown key '%s'", key);
 }
 

@@ -153,3 +153,49 @@ def test_normalize_flag_and_empty_requests(U):
         buf._sample(idxs, obs=False, next_obs=False)
     with pytest.raises(AugclError):
         buf._sample(np.zeros(0, dtype=np.int64))
+
+
+@pytest.mark.parametrize("S,aug,B", [(84, "shift", 128), (84, "none", 1), (84, "shift", 1000), (100, "crop", 77),
+                                      (100, "none", 130), (84, "svea", 5)])
+def test_band_kernel_equals_generic_kernel_full_ring(U, S, aug, B):
+    """Size-independent property: every staging variant (band / plane TMA pipeline, with and without PDL,
+    odd stage and CTA counts) returns bit-identical tensors to the no-staging one-thread-per-element kernel,
+    on a ring filled on the device, including out-of-range offsets at the replicate border."""
+    from augcl_b200 import _lib as L
+    cap = 3000
+    buf = U.ReplayBuffer((9, S, S), (4,), cap, B)
+    buf.fill_synthetic(seed=S + B)
+    rng = np.random.RandomState(B)
+    idxs = rng.randint(0, cap, size=B)
+    idxs[0], idxs[-1] = 0, cap - 1
+    pad = 4
+
+    def draw():
+        if aug == "shift":
+            o = {"obs": rng.randint(0, 2 * pad + 1, (B, 2)), "next_obs": rng.randint(0, 2 * pad + 1, (B, 2))}
+            o["obs"][0] = (0, 0); o["next_obs"][0] = (2 * pad, 2 * pad); o["obs"][-1] = (2 * pad, 0)
+            return lambda: buf.sample_drq(pad=pad, idxs=idxs, offsets=o)
+        if aug == "svea":
+            o = rng.randint(0, 2 * pad + 1, (B, 2))
+            return lambda: buf.sample_svea(pad=pad, idxs=idxs, offsets=o)
+        if aug == "crop":
+            o = {k: rng.randint(0, S - 84, (B, 2)) for k in ("pos", "obs", "next_obs")}
+            o["obs"][0] = (0, 0); o["next_obs"][0] = (S - 85, S - 85)
+            return lambda: buf.sample_curl(idxs=idxs, size=84, offsets=o)
+        return lambda: buf.sample(idxs=idxs)
+
+    call = draw()
+    try:
+        L.set_option("staging", "generic")
+        want = [t.clone() for t in call() if t is not None]
+        L.set_option("staging", "tma")
+        for band, pdl, stages, cps in [(1, 0, 3, 6), (1, 1, 3, 6), (1, 1, 2, 7), (1, 0, 4, 3), (1, 0, 1, 1), (0, 0, 3, 6), (0, 1, 2, 5)]:
+            for k, v in (("sample_band", band), ("sample_pdl", pdl), ("sample_stages", stages), ("sample_ctas_per_sm", cps)):
+                L.set_option(k, str(v))
+            for rep in range(2):       # back-to-back launches exercise the PDL overlap
+                got = [t for t in call() if t is not None]
+            for w, g in zip(want, got):
+                assert torch.equal(w, g), (band, pdl, stages, cps)
+    finally:
+        for k, v in (("staging", "tma"), ("sample_band", 1), ("sample_pdl", 1), ("sample_stages", 0), ("sample_ctas_per_sm", 6)):
+            L.set_option(k, str(v))
