@@ -12,10 +12,11 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libaugcl_b200.so")
 
 # enums of include/augcl_b200.h
-AUG_NONE, AUG_SHIFT, AUG_CROP = 0, 1, 2
+AUG_NONE, AUG_SHIFT, AUG_CROP, AUG_SHIFT_OBS = 0, 1, 2, 3
 SHIFT_INT, SHIFT_BILINEAR = 0, 1
 BANK_U8, BANK_F32 = 0, 1
 SPLICE, CS_SPLICE = 0, 1
+SRC_DEVICE, SRC_HOST, SRC_PHILOX = 0, 1, 2
 
 _p, _i, _i64, _u64, _f = C.c_void_p, C.c_int, C.c_int64, C.c_uint64, C.c_float
 
@@ -32,6 +33,7 @@ SIGNATURES = {
     "augcl_ring_get": (_i, [_p, _i64, _i64, _p, _p, _p, _p, _p, _p]),
     "augcl_ring_fill_synthetic": (_i, [_p, _i64, _u64, _p]),
     "augcl_ring_sample": (_i, [_p, _p, _i, _p, _p, _p, _p, _p, _i, _p, _p, _i, _i, _p]),
+    "augcl_ring_sample_ex": (_i, [_p, _i, _p, _i64, _i, _p, _p, _p, _p, _p, _i, _i, _p, _p, _i, _i, _u64, _u64, _p]),
     "augcl_random_shift": (_i, [_p, _p, _i, _i, _i, _i, _i, _p, _i, _p, _p]),
     "augcl_drq_base_grid": (_i, [_i, _i, C.POINTER(_f)]),
     "augcl_random_crop": (_i, [_p, _p, _i, _i, _i, _i, _i, _p, _p]),

@@ -50,6 +50,14 @@ def _next_subsequence() -> int:
     return _calls - 1
 
 
+def _reserve_subsequences(k: int) -> int:
+    """First of k consecutive Philox subsequences (the fused sample kernel uses 3: indices, obs and
+    next_obs offsets)."""
+    global _calls
+    _calls += k
+    return _calls - k
+
+
 def _stream(t: torch.Tensor) -> int:
     return torch.cuda.current_stream(t.device).cuda_stream
 

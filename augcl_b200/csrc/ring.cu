@@ -57,18 +57,79 @@ struct SampleParams {
   int tmap[2];
   int stage_bytes;
   int stages;
+  // where the draws come from (AUGCL_SRC_*; kSrcInline = by value in the launch's parameter block, kSrcNone = identity)
+  int idx_mode;
+  int off_mode[2];
+  uint32_t off_range;      // PHILOX offsets are uniform in [0, off_range)
+  uint64_t idx_hi;         // PHILOX indices are uniform in [0, idx_hi)
+  uint64_t seed, subseq;   // PHILOX streams: indices = subseq, obs offsets = subseq + 1, next_obs offsets = subseq + 2
 };
+
+constexpr int kSrcInline = 3;
+constexpr int kSrcNone = 4;
+constexpr int kInlineMax = 256;   // the reference's batch sizes: 128 (src/arguments.py:30) and 256 (soda_batch_size, :60)
+
+// Draws carried BY VALUE in the kernel's parameter block (constant bank): a host caller's indices and
+// offsets reach the GPU inside the launch itself -- no separate H2D copy, no device scratch.
+template <int NB>
+struct InlineDraws {
+  int32_t idx[NB];
+  int8_t off[2][NB][2];
+};
+template <>
+struct InlineDraws<0> {};
 
 __device__ __forceinline__ int64_t clamp_idx(int64_t i, int64_t cap) {
   return i < 0 ? 0 : (i >= cap ? cap - 1 : i);
 }
 
-__device__ __forceinline__ void gather_scalars(const SampleParams& p) {
+__device__ __forceinline__ uint32_t philox_word(uint64_t e, uint64_t subseq, uint64_t seed) {
+  const uint4 r = philox4x32_10(e >> 2, subseq, seed);
+  const uint32_t k = (uint32_t)e & 3u;
+  return k == 0 ? r.x : (k == 1 ? r.y : (k == 2 ? r.z : r.w));
+}
+
+// Ring slot of sample b (always clamped into [0, capacity) for memory safety).
+template <class Inl>
+__device__ __forceinline__ int64_t sample_index(const SampleParams& p, const Inl& inl, int b) {
+  int64_t i;
+  if constexpr (sizeof(Inl) > 1) {
+    if (p.idx_mode == kSrcInline) return clamp_idx((int64_t)inl.idx[b], p.capacity);
+  }
+  if (p.idx_mode == AUGCL_SRC_PHILOX)   // same values as augcl_rng_fill_indices(out, B, 0, idx_hi, seed, subseq)
+    i = (int64_t)(((uint64_t)philox_word((uint64_t)b, p.subseq, p.seed) * p.idx_hi) >> 32);
+  else
+    i = p.idx[b];
+  return clamp_idx(i, p.capacity);
+}
+
+// (dy, dx) of sample b for tensor t: source coordinate = output coordinate + (dy, dx), clamped.
+template <class Inl>
+__device__ __forceinline__ void sample_offset(const SampleParams& p, const Inl& inl, int t, int b, int& dy, int& dx) {
+  const int m = p.off_mode[t];
+  if (m == kSrcNone) { dy = 0; dx = 0; return; }
+  int oy = 0, ox = 0;
+  if (m == AUGCL_SRC_PHILOX) {          // same values as augcl_rng_fill_offsets(out, 2B, 0, off_range, seed, subseq+1+t)
+    const uint4 r = philox4x32_10((uint64_t)(b >> 1), p.subseq + 1 + t, p.seed);
+    oy = (int)__umulhi((b & 1) ? r.z : r.x, p.off_range);
+    ox = (int)__umulhi((b & 1) ? r.w : r.y, p.off_range);
+  } else {
+    bool done = false;
+    if constexpr (sizeof(Inl) > 1) {
+      if (m == kSrcInline) { oy = inl.off[t][b][0]; ox = inl.off[t][b][1]; done = true; }
+    }
+    if (!done) { oy = p.off[t][2 * b]; ox = p.off[t][2 * b + 1]; }
+  }
+  dy = oy - p.pad; dx = ox - p.pad;
+}
+
+template <class Inl>
+__device__ __forceinline__ void gather_scalars(const SampleParams& p, const Inl& inl) {
   // actions / rewards / not_dones rows (src/utils.py:210-212): a few hundred floats, done by a grid-stride loop
   const int per = p.A + 2;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < p.B * per; i += gridDim.x * blockDim.x) {
     const int b = i / per, j = i - b * per;
-    const int64_t s = clamp_idx(p.idx[b], p.capacity);
+    const int64_t s = sample_index(p, inl, b);
     if (j < p.A) {
       if (p.out_act) p.out_act[(int64_t)b * p.A + j] = p.act[s * p.A + j];
     } else if (j == p.A) {
@@ -96,7 +157,7 @@ struct ItemMeta {
 
 // WQ = Wo/4 as a compile-time constant (0 = runtime) so the row/column split is a multiply-shift.
 template <int WQ>
-__global__ void __launch_bounds__(256) ring_sample_tma_kernel(const SampleParams p) {
+__global__ void __launch_bounds__(256, 6) ring_sample_tma_kernel(const SampleParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
   const int S = p.stages;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem);                       // S mbarriers
@@ -107,25 +168,27 @@ __global__ void __launch_bounds__(256) ring_sample_tma_kernel(const SampleParams
   const int total = p.B * p.nt * p.C;
   const int wq = WQ ? WQ : (p.Wo >> 2);
   const int nvec = p.Ho * wq;
+  const InlineDraws<0> none{};
 
   if (tid == 0) {
     for (int s = 0; s < S; ++s) mbar_init(&bars[s], 1);
     mbar_fence_init();
   }
   __syncthreads();
+  pdl_wait();
 
   auto issue = [&](int item, int s) {   // tid 0 only
     const int ch = item % p.C;
     const int bt = item / p.C;
     const int slot = bt % p.nt, b = bt / p.nt;
     const int t = p.tmap[slot];
-    const int64_t row = clamp_idx(p.idx[b], p.capacity);
+    const int64_t row = sample_index(p, none, b);
     const uint8_t* src = p.store[t] + (row * p.C + ch) * (int64_t)P;
     const uintptr_t a = reinterpret_cast<uintptr_t>(src);
     const int lead = (int)(a & 15);
     const uint32_t bytes = (uint32_t)((lead + P + 15) & ~15);
-    int dy = -p.pad, dx = -p.pad;
-    if (p.off[t]) { dy += p.off[t][2 * b]; dx += p.off[t][2 * b + 1]; } else { dy = 0; dx = 0; }
+    int dy, dx;
+    sample_offset(p, none, t, b, dy, dx);
     meta[s] = ItemMeta{lead, dy, dx, 0};
     mbar_expect_tx(&bars[s], bytes);
     bulk_g2s(bufs + (size_t)s * p.stage_bytes, src - lead, bytes, &bars[s]);
@@ -137,8 +200,9 @@ __global__ void __launch_bounds__(256) ring_sample_tma_kernel(const SampleParams
       if (item < total) issue(item, j);
     }
   }
+  pdl_launch_dependents();
 
-  gather_scalars(p);
+  gather_scalars(p, none);
 
   int s = 0;
   uint32_t phase = 0;
@@ -197,8 +261,9 @@ struct BandMeta {   // written by the issuing lane before the copy is started, r
 };
 static_assert(sizeof(BandMeta) == 32, "BandMeta is 32 bytes");
 
-template <int H, int W, int HO, int WO>
-__global__ void __launch_bounds__(256) ring_sample_band_kernel(const SampleParams p) {
+template <int H, int W, int HO, int WO, int NB>
+__global__ void __launch_bounds__(256, 6) ring_sample_band_kernel(const SampleParams p,
+                                                               const __grid_constant__ InlineDraws<NB> inl) {
   constexpr int WQ = WO / 4, RPI = 256 / WQ, ACTIVE = RPI * WQ, NIT = HO / RPI, P = H * W;
   static_assert(WO % 4 == 0 && HO % RPI == 0, "geometry must tile into row groups");
   extern __shared__ __align__(128) uint8_t smem[];
@@ -226,9 +291,9 @@ __global__ void __launch_bounds__(256) ring_sample_band_kernel(const SampleParam
     const int64_t bt = plane / p.C;
     const int slot = (int)(bt % p.nt), b = (int)(bt / p.nt);
     const int t = p.tmap[slot];
-    const int64_t row = clamp_idx(p.idx[b], p.capacity);
-    int dy = 0, dx = 0;
-    if (p.off[t]) { dy = p.off[t][2 * b] - p.pad; dx = p.off[t][2 * b + 1] - p.pad; }
+    const int64_t row = sample_index(p, inl, b);
+    int dy, dx;
+    sample_offset(p, inl, t, b, dy, dx);
     const int it_lo = k == 0 ? (int)(u0 - pl0 * NIT) : 0;
     const int64_t rem = u1 - plane * NIT;
     const int it_hi = rem < NIT ? (int)rem : NIT;
@@ -248,7 +313,7 @@ __global__ void __launch_bounds__(256) ring_sample_band_kernel(const SampleParam
 
   if (tid < S && tid < nseg) issue(tid, tid);   // the S prologue copies are prepared by S lanes in parallel
   pdl_launch_dependents();
-  gather_scalars(p);
+  gather_scalars(p, inl);
 
   const int r0 = tid / WQ, q4 = tid - r0 * WQ;
   int s = 0;
@@ -281,7 +346,8 @@ __global__ void __launch_bounds__(256) ring_sample_band_kernel(const SampleParam
 // No staging, any shape: one thread per output element.  Fallback for Wo % 4 != 0 and the
 // "generic" arm of the staging A/B switch.
 __global__ void __launch_bounds__(256) ring_sample_generic_kernel(const SampleParams p) {
-  gather_scalars(p);
+  const InlineDraws<0> none{};
+  gather_scalars(p, none);
   const int64_t plane_o = (int64_t)p.Ho * p.Wo;
   const int64_t total = (int64_t)p.B * p.nt * p.C * plane_o;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
@@ -292,10 +358,10 @@ __global__ void __launch_bounds__(256) ring_sample_generic_kernel(const SamplePa
     const int slot = (int)(rest % p.nt);
     const int b = (int)(rest / p.nt);
     const int t = p.tmap[slot];
-    int dy = 0, dx = 0;
-    if (p.off[t]) { dy = p.off[t][2 * b] - p.pad; dx = p.off[t][2 * b + 1] - p.pad; }
+    int dy, dx;
+    sample_offset(p, none, t, b, dy, dx);
     const int rr = clampi(r + dy, 0, p.H - 1), cc = clampi(q + dx, 0, p.W - 1);
-    const int64_t row = clamp_idx(p.idx[b], p.capacity);
+    const int64_t row = sample_index(p, none, b);
     float v = (float)p.store[t][((row * p.C + ch) * p.H + rr) * (int64_t)p.W + cc];
     if (p.normalize) v = __fdiv_rn(v, 255.0f);
     p.out[t][(((int64_t)b * p.C + ch) * p.Ho + r) * p.Wo + q] = v;
@@ -424,43 +490,84 @@ int augcl_ring_fill_synthetic(augcl_ring* r, int64_t count, uint64_t seed, augcl
   return AUGCL_OK;
 }
 
-int augcl_ring_sample(augcl_ring* r, const int64_t* idx, int B, float* out_obs, float* out_next, float* out_act,
-                      float* out_rew, float* out_nd, int aug_mode, const int32_t* off_obs, const int32_t* off_next,
-                      int pad_or_size, int normalize, augcl_stream stream) {
-  AUGCL_REQUIRE(r, "augcl_ring_sample: ring is NULL");
-  AUGCL_REQUIRE(idx, "augcl_ring_sample: idx is NULL");
-  AUGCL_REQUIRE(B > 0, "augcl_ring_sample: B must be positive (got %d)", B);
-  AUGCL_REQUIRE(out_obs || out_next, "augcl_ring_sample: both image outputs are NULL");
-  AUGCL_REQUIRE(aug_mode == AUGCL_AUG_NONE || aug_mode == AUGCL_AUG_SHIFT || aug_mode == AUGCL_AUG_CROP,
-                "augcl_ring_sample: unknown aug_mode %d", aug_mode);
+// Shared implementation of augcl_ring_sample / augcl_ring_sample_ex.
+static int sample_impl(const char* who, augcl_ring* r, int idx_src, const int64_t* idx, int64_t idx_hi, int B,
+                       float* out_obs, float* out_next, float* out_act, float* out_rew, float* out_nd, int aug_mode,
+                       int off_src, const int32_t* off_obs, const int32_t* off_next, int pad_or_size, int normalize,
+                       uint64_t seed, uint64_t subsequence, cudaStream_t st) {
+  AUGCL_REQUIRE(r, "%s: ring is NULL", who);
+  AUGCL_REQUIRE(B > 0, "%s: B must be positive (got %d)", who, B);
+  AUGCL_REQUIRE(out_obs || out_next, "%s: both image outputs are NULL", who);
+  AUGCL_REQUIRE(aug_mode == AUGCL_AUG_NONE || aug_mode == AUGCL_AUG_SHIFT || aug_mode == AUGCL_AUG_CROP ||
+                    aug_mode == AUGCL_AUG_SHIFT_OBS, "%s: unknown aug_mode %d", who, aug_mode);
+  const bool obs_only = aug_mode == AUGCL_AUG_SHIFT_OBS;
+  if (obs_only) { aug_mode = AUGCL_AUG_SHIFT; off_next = nullptr; }
+  AUGCL_REQUIRE(idx_src == AUGCL_SRC_DEVICE || idx_src == AUGCL_SRC_HOST || idx_src == AUGCL_SRC_PHILOX,
+                "%s: unknown idx_src %d", who, idx_src);
+  AUGCL_REQUIRE(off_src == AUGCL_SRC_DEVICE || off_src == AUGCL_SRC_HOST || off_src == AUGCL_SRC_PHILOX,
+                "%s: unknown off_src %d", who, off_src);
+  if (idx_src == AUGCL_SRC_PHILOX)
+    AUGCL_REQUIRE(idx_hi > 0 && idx_hi <= r->capacity, "%s: idx_hi %lld outside (0, capacity]", who, (long long)idx_hi);
+  else
+    AUGCL_REQUIRE(idx, "%s: idx is NULL", who);
   SampleParams p{};
   p.store[0] = r->obs; p.store[1] = r->next;
   p.out[0] = out_obs; p.out[1] = out_next;
-  p.off[0] = off_obs; p.off[1] = off_next;
   p.idx = idx; p.act = r->act; p.rew = r->rew; p.nd = r->nd;
   p.out_act = out_act; p.out_rew = out_rew; p.out_nd = out_nd;
   p.capacity = r->capacity;
   p.B = B; p.C = r->C; p.H = r->H; p.W = r->W; p.A = r->A;
   p.Ho = r->H; p.Wo = r->W; p.pad = 0; p.normalize = normalize ? 1 : 0;
+  p.idx_mode = idx_src; p.idx_hi = (uint64_t)idx_hi; p.seed = seed; p.subseq = subsequence;
+  const int32_t* off[2] = {off_obs, off_next};
+  float* outs[2] = {out_obs, out_next};
+  int hi_row = 0, hi_col = 0;   // valid offsets: row in [0, hi_row], col in [0, hi_col]
   if (aug_mode == AUGCL_AUG_SHIFT) {
-    AUGCL_REQUIRE(pad_or_size >= 0 && pad_or_size < (1 << 15), "augcl_ring_sample: bad pad %d", pad_or_size);
+    AUGCL_REQUIRE(pad_or_size >= 0 && pad_or_size < (1 << 15), "%s: bad pad %d", who, pad_or_size);
     p.pad = pad_or_size;
+    hi_row = hi_col = 2 * pad_or_size;
+    p.off_range = (uint32_t)(2 * pad_or_size + 1);         // kornia RandomCrop: [0, 2*pad]
   } else if (aug_mode == AUGCL_AUG_CROP) {
     AUGCL_REQUIRE(pad_or_size > 0 && pad_or_size <= r->H && pad_or_size <= r->W,
-                  "augcl_ring_sample: crop size %d does not fit %dx%d", pad_or_size, r->H, r->W);
-    AUGCL_REQUIRE((!out_obs || off_obs) && (!out_next || off_next),
-                  "augcl_ring_sample: CROP needs offsets for every tensor that is written");
+                  "%s: crop size %d does not fit %dx%d", who, pad_or_size, r->H, r->W);
     p.Ho = p.Wo = pad_or_size;
-  } else {
-    p.off[0] = p.off[1] = nullptr;
+    hi_row = r->H - pad_or_size; hi_col = r->W - pad_or_size;
+    p.off_range = (uint32_t)(r->W - pad_or_size);           // random_(0, crop_max): upper bound exclusive (:404-405)
+    if (off_src == AUGCL_SRC_PHILOX)
+      AUGCL_REQUIRE(r->H == r->W && p.off_range > 0, "%s: PHILOX crop offsets need a square image larger than the crop", who);
+  }
+  for (int t = 0; t < 2; ++t) {
+    if (aug_mode == AUGCL_AUG_NONE || !outs[t] || (obs_only && t == 1)) { p.off_mode[t] = kSrcNone; continue; }
+    if (off_src == AUGCL_SRC_PHILOX) { p.off_mode[t] = off[t] ? AUGCL_SRC_DEVICE : AUGCL_SRC_PHILOX; p.off[t] = off[t]; continue; }
+    if (!off[t]) {
+      AUGCL_REQUIRE(aug_mode != AUGCL_AUG_CROP, "%s: CROP needs offsets for every tensor that is written", who);
+      p.off_mode[t] = kSrcNone;     // SHIFT without offsets = identity for that tensor (SVEA: next_obs un-augmented)
+      continue;
+    }
+    p.off_mode[t] = off_src;
+    p.off[t] = off[t];
   }
   p.nt = 0;
   if (out_obs) p.tmap[p.nt++] = 0;
   if (out_next) p.tmap[p.nt++] = 1;
-  AUGCL_REQUIRE((int64_t)B * p.nt * p.C < (1ll << 31), "augcl_ring_sample: batch too large");
+  AUGCL_REQUIRE((int64_t)B * p.nt * p.C < (1ll << 31), "%s: batch too large", who);
   DeviceGuard g(r->device);
   AUGCL_CUDA(g.err);
-  cudaStream_t st = (cudaStream_t)stream;
+
+  // ---- HOST draws: validate (the reference raises IndexError on a bad index), then carry them by value
+  //      in the launch (small batches, band geometries) or stage them through stream-ordered scratch.
+  const bool host_idx = idx_src == AUGCL_SRC_HOST;
+  const bool host_off = off_src == AUGCL_SRC_HOST && (p.off_mode[0] == AUGCL_SRC_HOST || p.off_mode[1] == AUGCL_SRC_HOST);
+  if (host_idx)
+    for (int b = 0; b < B; ++b)
+      AUGCL_REQUIRE(idx[b] >= 0 && idx[b] < r->capacity, "%s: index %lld (position %d) out of range [0, %lld)", who,
+                    (long long)idx[b], b, (long long)r->capacity);
+  if (host_off)
+    for (int t = 0; t < 2; ++t)
+      if (p.off_mode[t] == AUGCL_SRC_HOST)
+        for (int e = 0; e < 2 * B; ++e)
+          AUGCL_REQUIRE(off[t][e] >= 0 && off[t][e] <= ((e & 1) ? hi_col : hi_row),
+                        "%s: offset %d (tensor %d, element %d) outside [0, %d]", who, off[t][e], t, e, (e & 1) ? hi_col : hi_row);
 
   const int kMaxSmem = 227 * 1024;
   const int P = p.H * p.W;
@@ -468,7 +575,58 @@ int augcl_ring_sample(augcl_ring* r, const int64_t* idx, int B, float* out_obs, 
   const int kHeader = 64 + 8 * (int)sizeof(BandMeta);   // mbarriers + per-stage metas (both kernels fit in it)
   const bool vec_ok = (p.Wo % 4 == 0) && aligned(out_obs, 16) && aligned(out_next, 16) &&
                       kHeader + p.stage_bytes <= kMaxSmem;
-  if (g_staging.load() == 0 && vec_ok) {
+  const bool staged = g_staging.load() == 0 && vec_ok;
+  int geom = 0;   // compile-time geometries of the reference's two image sizes (src/arguments.py:155-163)
+  if (staged && g_sample_band.load()) {
+    if (p.H == 84 && p.W == 84 && p.Ho == 84 && p.Wo == 84) geom = 1;
+    else if (p.H == 100 && p.W == 100 && p.Ho == 100 && p.Wo == 100) geom = 2;
+    else if (p.H == 100 && p.W == 100 && p.Ho == 84 && p.Wo == 84) geom = 3;
+  }
+
+  InlineDraws<kInlineMax> inl;
+  bool use_inline = false;
+  void* scratch = nullptr;
+  if (host_idx || host_off) {
+    if (geom && B <= kInlineMax && r->capacity < (1ll << 31) && hi_row <= 127 && hi_col <= 127) {
+      use_inline = true;
+      if (host_idx) {
+        for (int b = 0; b < B; ++b) inl.idx[b] = (int32_t)idx[b];
+        p.idx_mode = kSrcInline;
+      }
+      for (int t = 0; t < 2; ++t)
+        if (p.off_mode[t] == AUGCL_SRC_HOST) {
+          for (int b = 0; b < B; ++b) { inl.off[t][b][0] = (int8_t)off[t][2 * b]; inl.off[t][b][1] = (int8_t)off[t][2 * b + 1]; }
+          p.off_mode[t] = kSrcInline;
+        }
+    } else {
+      // stream-ordered scratch: [idx int64 B][off_obs int32 2B][off_next int32 2B]
+      const size_t ib = (size_t)B * 8, ob = (size_t)B * 8;
+      AUGCL_CUDA(cudaMallocAsync(&scratch, ib + 2 * ob, st));
+      uint8_t* sp = static_cast<uint8_t*>(scratch);
+      cudaError_t e = cudaSuccess;
+      if (host_idx) {
+        e = cudaMemcpyAsync(sp, idx, ib, cudaMemcpyHostToDevice, st);
+        p.idx = reinterpret_cast<const int64_t*>(sp);
+        p.idx_mode = AUGCL_SRC_DEVICE;
+      }
+      for (int t = 0; t < 2 && e == cudaSuccess; ++t)
+        if (p.off_mode[t] == AUGCL_SRC_HOST) {
+          e = cudaMemcpyAsync(sp + ib + t * ob, off[t], ob, cudaMemcpyHostToDevice, st);
+          p.off[t] = reinterpret_cast<const int32_t*>(sp + ib + t * ob);
+          p.off_mode[t] = AUGCL_SRC_DEVICE;
+        }
+      if (e != cudaSuccess) {
+        cudaFreeAsync(scratch, st);
+        AUGCL_FAIL(AUGCL_ERR_CUDA, "%s: staging the host draws failed: %s", who, cudaGetErrorString(e));
+      }
+    }
+  }
+  auto finish_call = [&](int rc) -> int {
+    if (scratch) cudaFreeAsync(scratch, st);   // stream-ordered: released after the kernel that reads it
+    return rc;
+  };
+
+  if (staged) {
     int stages = g_sample_stages.load();
     if (stages == 0) stages = (int64_t)B * p.nt * p.C <= 8 * kNumSMs * 6 ? 4 : 2;   // short launches: deeper prefetch hides the ramp
     int ctas_per_sm = g_sample_ctas_per_sm.load();
@@ -479,7 +637,7 @@ int augcl_ring_sample(augcl_ring* r, const int64_t* idx, int B, float* out_obs, 
     if (ctas_per_sm > fit) ctas_per_sm = fit < 1 ? 1 : fit;
     if (ctas_per_sm > 8) ctas_per_sm = 8;   // 2048 threads / 256
     const bool pdl = g_sample_pdl.load() != 0;
-    auto launch = [&](auto kern, int64_t work_items) -> int {
+    auto launch = [&](auto kern, int64_t work_items, auto... args) -> int {
       static std::atomic<uint64_t> configured{0};   // one bit per device, per kernel instantiation
       if (!(configured.load() >> (r->device & 63) & 1)) {
         AUGCL_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem));
@@ -497,27 +655,50 @@ int augcl_ring_sample(augcl_ring* r, const int64_t* idx, int B, float* out_obs, 
       attr[0].val.programmaticStreamSerializationAllowed = 1;
       cfg.attrs = attr;
       cfg.numAttrs = pdl ? 1 : 0;
-      AUGCL_CUDA(cudaLaunchKernelEx(&cfg, kern, p));
+      AUGCL_CUDA(cudaLaunchKernelEx(&cfg, kern, args...));
       AUGCL_LAUNCHED();
       return AUGCL_OK;
     };
     const int64_t planes = (int64_t)B * p.nt * p.C;
-    if (g_sample_band.load()) {
-      // compile-time geometries of the reference's two image sizes (src/arguments.py:155-163)
-      if (p.H == 84 && p.W == 84 && p.Ho == 84 && p.Wo == 84) return launch(ring_sample_band_kernel<84, 84, 84, 84>, planes * 7);
-      if (p.H == 100 && p.W == 100 && p.Ho == 100 && p.Wo == 100) return launch(ring_sample_band_kernel<100, 100, 100, 100>, planes * 10);
-      if (p.H == 100 && p.W == 100 && p.Ho == 84 && p.Wo == 84) return launch(ring_sample_band_kernel<100, 100, 84, 84>, planes * 7);
+    const InlineDraws<0> none{};
+    if (use_inline) {
+      if (geom == 1) return launch(ring_sample_band_kernel<84, 84, 84, 84, kInlineMax>, planes * 7, p, inl);
+      if (geom == 2) return launch(ring_sample_band_kernel<100, 100, 100, 100, kInlineMax>, planes * 10, p, inl);
+      return launch(ring_sample_band_kernel<100, 100, 84, 84, kInlineMax>, planes * 7, p, inl);
     }
-    if (p.Wo == 84) return launch(ring_sample_tma_kernel<21>, planes);
-    if (p.Wo == 100) return launch(ring_sample_tma_kernel<25>, planes);
-    return launch(ring_sample_tma_kernel<0>, planes);
+    if (geom == 1) return finish_call(launch(ring_sample_band_kernel<84, 84, 84, 84, 0>, planes * 7, p, none));
+    if (geom == 2) return finish_call(launch(ring_sample_band_kernel<100, 100, 100, 100, 0>, planes * 10, p, none));
+    if (geom == 3) return finish_call(launch(ring_sample_band_kernel<100, 100, 84, 84, 0>, planes * 7, p, none));
+    if (p.Wo == 84) return finish_call(launch(ring_sample_tma_kernel<21>, planes, p));
+    if (p.Wo == 100) return finish_call(launch(ring_sample_tma_kernel<25>, planes, p));
+    return finish_call(launch(ring_sample_tma_kernel<0>, planes, p));
   }
   const int64_t total = (int64_t)B * p.nt * p.C * p.Ho * p.Wo;
   int64_t blocks = (total + 255) / 256;
   if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
   ring_sample_generic_kernel<<<(int)blocks, 256, 0, st>>>(p);
-  AUGCL_LAUNCHED();
-  return AUGCL_OK;
+  cudaError_t le = cudaGetLastError();
+  if (le != cudaSuccess) {
+    finish_call(0);
+    AUGCL_FAIL(AUGCL_ERR_CUDA, "%s: launch failed: %s", who, cudaGetErrorString(le));
+  }
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  return finish_call(AUGCL_OK);
+}
+
+int augcl_ring_sample(augcl_ring* r, const int64_t* idx, int B, float* out_obs, float* out_next, float* out_act,
+                      float* out_rew, float* out_nd, int aug_mode, const int32_t* off_obs, const int32_t* off_next,
+                      int pad_or_size, int normalize, augcl_stream stream) {
+  return sample_impl("augcl_ring_sample", r, AUGCL_SRC_DEVICE, idx, 0, B, out_obs, out_next, out_act, out_rew, out_nd,
+                     aug_mode, AUGCL_SRC_DEVICE, off_obs, off_next, pad_or_size, normalize, 0, 0, (cudaStream_t)stream);
+}
+
+int augcl_ring_sample_ex(augcl_ring* r, int idx_src, const int64_t* idx, int64_t idx_hi, int B, float* out_obs,
+                         float* out_next, float* out_act, float* out_rew, float* out_nd, int aug_mode, int off_src,
+                         const int32_t* off_obs, const int32_t* off_next, int pad_or_size, int normalize, uint64_t seed,
+                         uint64_t subsequence, augcl_stream stream) {
+  return sample_impl("augcl_ring_sample_ex", r, idx_src, idx, idx_hi, B, out_obs, out_next, out_act, out_rew, out_nd,
+                     aug_mode, off_src, off_obs, off_next, pad_or_size, normalize, seed, subsequence, (cudaStream_t)stream);
 }
 
 }  // extern "C"

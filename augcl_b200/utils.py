@@ -21,6 +21,13 @@ from . import _lib as L
 from . import augmentations
 
 
+try:                                    # raw cudaStream_t of torch's current stream without building a Stream object
+    _raw_stream = torch._C._cuda_getCurrentRawStream
+except AttributeError:                  # pragma: no cover
+    def _raw_stream(index):
+        return torch.cuda.current_stream(index).cuda_stream
+
+
 class LazyFrames(object):
     """k frames concatenated along channels on demand (src/utils.py:283-322)."""
 
@@ -76,6 +83,9 @@ class ReplayBuffer(object):
         self.capacity = int(capacity)
         self.batch_size = batch_size
         self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        if self.device.index is None:
+            self.device = torch.device("cuda", torch.cuda.current_device())
+        self._dev_index = self.device.index
         c, h, w = obs_shape
         if c % frame_channels:
             raise ValueError(f"obs channels {c} not a multiple of frame_channels {frame_channels}")
@@ -91,9 +101,10 @@ class ReplayBuffer(object):
         self.refilled = False
 
         h_ring = C.c_void_p()
-        L.call("augcl_ring_create", C.byref(h_ring), self.device.index or 0, self.capacity, c // frame_channels,
+        L.call("augcl_ring_create", C.byref(h_ring), self._dev_index, self.capacity, c // frame_channels,
                frame_channels, h, w, self.action_dim)
         self._ring = h_ring
+        self._fn_sample = L.lib().augcl_ring_sample_ex
         self._stack_bytes = c * h * w
         n = min(self.STAGE, self.capacity)
         self._st_obs = torch.empty((n, c, h, w), dtype=torch.uint8).pin_memory()
@@ -157,38 +168,103 @@ class ReplayBuffer(object):
             n = self.batch_size
         return np.random.randint(0, self.capacity if self.full else self.idx, size=n)
 
-    def _dev_idxs(self, idxs):
-        if isinstance(idxs, torch.Tensor):
-            return idxs.to(device=self.device, dtype=torch.int64).contiguous()
-        return torch.from_numpy(np.ascontiguousarray(idxs, dtype=np.int64)).to(self.device, non_blocking=True)
-
     # ------------------------------------------------------------------ the fused sample kernel
-    def _sample(self, idxs, *, obs=True, next_obs=True, scalars=True, aug=L.AUG_NONE, off_obs=None,
-                off_next=None, pad_or_size=0, normalize=False):
-        """One augcl_ring_sample launch.  Returns (obs, actions, rewards, next_obs, not_dones); entries
-        that were not requested are None."""
-        self._flush()
-        with torch.cuda.device(self.device):
-            di = self._dev_idxs(idxs)
-            B = di.numel()
-            c, h, w = self.obs_shape
-            ho, wo = (pad_or_size, pad_or_size) if aug == L.AUG_CROP else (h, w)
-            dev = self.device
-            o = torch.empty((B, c, ho, wo), dtype=torch.float32, device=dev) if obs else None
-            no = torch.empty((B, c, ho, wo), dtype=torch.float32, device=dev) if next_obs else None
-            act = torch.empty((B,) + self.actions.shape[1:], dtype=torch.float32, device=dev) if scalars else None
-            rew = torch.empty((B, 1), dtype=torch.float32, device=dev) if scalars else None
-            nd = torch.empty((B, 1), dtype=torch.float32, device=dev) if scalars else None
-            p = lambda t: None if t is None else t.data_ptr()  # noqa: E731
-            L.call("augcl_ring_sample", self._ring, di.data_ptr(), B, p(o), p(no), p(act), p(rew), p(nd), aug,
-                   p(off_obs), p(off_next), int(pad_or_size), 1 if normalize else 0, self._stream())
-        return o, act, rew, no, nd
+    def _idx_arg(self, idxs):
+        """-> (AUGCL_SRC_*, pointer, B, keepalive).  numpy / list / CPU tensor = HOST (the reference's case:
+        np.random.randint on the host, src/utils.py:229-232); CUDA tensor = DEVICE."""
+        if isinstance(idxs, torch.Tensor):
+            t = idxs.reshape(-1)
+            if t.dtype != torch.int64 or not t.is_contiguous():
+                t = t.to(torch.int64).contiguous()
+            if t.is_cuda:
+                if t.device != self.device:
+                    t = t.to(self.device)
+                return L.SRC_DEVICE, t.data_ptr(), t.numel(), t
+            return L.SRC_HOST, t.data_ptr(), t.numel(), t
+        a = np.ascontiguousarray(idxs, dtype=np.int64).reshape(-1)
+        return L.SRC_HOST, a.ctypes.data, a.size, a
 
-    def _offsets(self, B, lo, hi, supplied):
-        if supplied is not None:
-            return augmentations._dev_i32(supplied, B, self.device, "ReplayBuffer")
-        with torch.cuda.device(self.device):
-            return augmentations._draw_offsets(B, lo, hi, self.device)
+    def _off_arg(self, v, B):
+        """-> None | (AUGCL_SRC_*, pointer, keepalive) for one (B,2) offsets array."""
+        if v is None:
+            return None
+        if isinstance(v, torch.Tensor) and v.is_cuda:
+            t = v.to(device=self.device, dtype=torch.int32).contiguous()
+            if tuple(t.shape) != (B, 2):
+                raise ValueError(f"ReplayBuffer: offsets must have shape ({B}, 2), got {tuple(t.shape)}")
+            return L.SRC_DEVICE, t.data_ptr(), t
+        a = v.numpy() if isinstance(v, torch.Tensor) else np.asarray(v)
+        a = np.ascontiguousarray(a, dtype=np.int32)
+        if a.shape != (B, 2):
+            raise ValueError(f"ReplayBuffer: offsets must have shape ({B}, 2), got {a.shape}")
+        return L.SRC_HOST, a.ctypes.data, a
+
+    def _sample(self, idxs=None, *, n=None, obs=True, next_obs=True, scalars=True, aug=L.AUG_NONE, off_obs=None,
+                off_next=None, pad_or_size=0, normalize=False, device_indices=False):
+        """One augcl_ring_sample_ex launch.  Returns (obs, actions, rewards, next_obs, not_dones); entries
+        that were not requested are None.  Host indices / offsets travel inside the launch (no extra H2D);
+        offsets that are not supplied are drawn inside the kernel (Philox stream of augmentations.seed())."""
+        self._flush()
+        sub = augmentations._reserve_subsequences(3)
+        if device_indices and idxs is None:
+            B = self.batch_size if n is None else int(n)
+            i_src, i_ptr, keep_i = L.SRC_PHILOX, None, None
+            idx_hi = self.capacity if self.full else self.idx
+        else:
+            if idxs is None:
+                idxs = self._get_idxs(n)
+            i_src, i_ptr, B, keep_i = self._idx_arg(idxs)
+            idx_hi = 0
+        oo, on = self._off_arg(off_obs, B), self._off_arg(off_next, B)
+        need_draw = aug in (L.AUG_SHIFT, L.AUG_CROP) and ((obs and oo is None) or (next_obs and on is None))
+        need_draw = need_draw or (aug == L.AUG_SHIFT_OBS and obs and oo is None)
+        kinds = {x[0] for x in (oo, on) if x is not None}
+        if need_draw or len(kinds) > 1:
+            # PHILOX draws for the missing tensors; supplied arrays must then be DEVICE arrays
+            def to_dev(x):
+                if x is None or x[0] == L.SRC_DEVICE:
+                    return x
+                t = torch.from_numpy(x[2]).to(self.device, non_blocking=False)
+                return L.SRC_DEVICE, t.data_ptr(), t
+            oo, on = to_dev(oo), to_dev(on)
+            o_src = L.SRC_PHILOX if need_draw else L.SRC_DEVICE
+        else:
+            o_src = kinds.pop() if kinds else L.SRC_DEVICE
+        c, h, w = self.obs_shape
+        ho, wo = (pad_or_size, pad_or_size) if aug == L.AUG_CROP else (h, w)
+        dev = self.device
+        guard = None
+        if torch.cuda.current_device() != self._dev_index:    # rare: only then pay for a device context switch
+            guard = torch.cuda.device(dev)
+            guard.__enter__()
+        try:
+            o = no = act = rew = nd = None
+            po = pn = pa = pr = pd = None
+            if obs and next_obs:
+                o, no = torch.empty((2, B, c, ho, wo), dtype=torch.float32, device=dev).unbind(0)
+                po = o.data_ptr()
+                pn = po + 4 * B * c * ho * wo
+            elif obs:
+                o = torch.empty((B, c, ho, wo), dtype=torch.float32, device=dev)
+                po = o.data_ptr()
+            elif next_obs:
+                no = torch.empty((B, c, ho, wo), dtype=torch.float32, device=dev)
+                pn = no.data_ptr()
+            if scalars:
+                act = torch.empty((B,) + self.actions.shape[1:], dtype=torch.float32, device=dev)
+                rew, nd = torch.empty((2, B, 1), dtype=torch.float32, device=dev).unbind(0)
+                pa, pr = act.data_ptr(), rew.data_ptr()
+                pd = pr + 4 * B
+            rc = self._fn_sample(self._ring, i_src, i_ptr, idx_hi, B, po, pn, pa, pr, pd, aug, o_src,
+                                 None if oo is None else oo[1], None if on is None else on[1], int(pad_or_size),
+                                 1 if normalize else 0, augmentations._seed, sub, _raw_stream(self._dev_index))
+            if rc != 0:
+                raise L.AugclError("augcl_ring_sample_ex", rc, L.lib().augcl_last_error().decode(errors="replace"))
+        finally:
+            if guard is not None:
+                guard.__exit__(None, None, None)
+        self._keep = (keep_i, oo, on)   # page-locked host sources of a staged (B > 256) call must outlive the copy
+        return o, act, rew, no, nd
 
     # ------------------------------------------------------------------ reference API
     def tensor_buffer_samples(self, idxs):
@@ -196,54 +272,44 @@ class ReplayBuffer(object):
         obs, actions, rewards, next_obs, not_dones = self._sample(idxs)
         return obs, next_obs, actions, rewards, not_dones
 
-    def sample(self, n=None, idxs=None):
-        """src/utils.py:272-280."""
-        if idxs is None:
-            idxs = self._get_idxs(n)
-        return self._sample(idxs)
+    def sample(self, n=None, idxs=None, *, device_indices=False):
+        """src/utils.py:272-280.  device_indices=True draws the indices inside the kernel instead of with
+        numpy's global RNG (no host work at all)."""
+        return self._sample(idxs, n=n, device_indices=device_indices)
 
-    def sample_obs(self, n=None):
+    def sample_obs(self, n=None, *, idxs=None):
         """src/utils.py:242-245."""
-        return self._sample(self._get_idxs(n), next_obs=False, scalars=False)[0]
+        return self._sample(idxs, n=n, next_obs=False, scalars=False)[0]
 
     def sample_curl(self, n=None, *, idxs=None, size=84, offsets=None):
         """src/utils.py:247-258: three independent random crops (pos, obs, next_obs), fused into the
         gather.  offsets: optional dict {"pos","obs","next_obs"} -> (B,2) (w1,h1) draws."""
         if idxs is None:
             idxs = self._get_idxs(n)
-        B = len(idxs)
         c, h, w = self.obs_shape
         crop_max = w - size
         if crop_max <= 0:   # random_crop passthrough (src/augmentations.py:396-399)
             obs, actions, rewards, next_obs, not_dones = self._sample(idxs)
             return obs, actions, rewards, next_obs, not_dones, obs.clone()
         offsets = offsets or {}
-        o_pos = self._offsets(B, 0, crop_max, offsets.get("pos"))       # draw order of the reference
-        o_obs = self._offsets(B, 0, crop_max, offsets.get("obs"))
-        o_next = self._offsets(B, 0, crop_max, offsets.get("next_obs"))
         obs, actions, rewards, next_obs, not_dones = self._sample(
-            idxs, aug=L.AUG_CROP, off_obs=o_obs, off_next=o_next, pad_or_size=size)
-        pos = self._sample(idxs, next_obs=False, scalars=False, aug=L.AUG_CROP, off_obs=o_pos, pad_or_size=size)[0]
+            idxs, aug=L.AUG_CROP, off_obs=offsets.get("obs"), off_next=offsets.get("next_obs"), pad_or_size=size)
+        pos = self._sample(idxs, next_obs=False, scalars=False, aug=L.AUG_CROP, off_obs=offsets.get("pos"),
+                           pad_or_size=size)[0]
         return obs, actions, rewards, next_obs, not_dones, pos
 
-    def sample_drq(self, n=None, pad=4, *, idxs=None, offsets=None):
+    def sample_drq(self, n=None, pad=4, *, idxs=None, offsets=None, device_indices=False):
         """src/utils.py:260-270: gather + random_shift of obs and next_obs in one kernel.
         offsets: optional dict {"obs","next_obs"} -> (B,2) (row,col) draws in [0, 2*pad]."""
-        if idxs is None:
-            idxs = self._get_idxs(n)
-        B = len(idxs)
         offsets = offsets or {}
-        o_obs = self._offsets(B, 0, 2 * pad + 1, offsets.get("obs"))
-        o_next = self._offsets(B, 0, 2 * pad + 1, offsets.get("next_obs"))
-        return self._sample(idxs, aug=L.AUG_SHIFT, off_obs=o_obs, off_next=o_next, pad_or_size=pad)
+        return self._sample(idxs, n=n, aug=L.AUG_SHIFT, off_obs=offsets.get("obs"), off_next=offsets.get("next_obs"),
+                            pad_or_size=pad, device_indices=device_indices)
 
-    def sample_svea(self, n=None, pad=4, *, idxs=None, offsets=None):
+    def sample_svea(self, n=None, pad=4, *, idxs=None, offsets=None, device_indices=False):
         """The SVEA / AugCL access pattern (src/algorithms/svea.py:66-70, augcl.py:69-72) as one kernel:
-        obs is shifted, next_obs is returned un-augmented."""
-        if idxs is None:
-            idxs = self._get_idxs(n)
-        o_obs = self._offsets(len(idxs), 0, 2 * pad + 1, offsets)
-        return self._sample(idxs, aug=L.AUG_SHIFT, off_obs=o_obs, off_next=None, pad_or_size=pad)
+        obs is shifted, next_obs is returned un-augmented.  offsets: optional (B,2) draws for obs."""
+        return self._sample(idxs, n=n, aug=L.AUG_SHIFT_OBS, off_obs=offsets, pad_or_size=pad,
+                            device_indices=device_indices)
 
     def fill_synthetic(self, count=None, seed=0):
         """Benchmarks/tests: fill slots [0,count) with Philox frames and scalars on the device."""

@@ -261,8 +261,10 @@ def run_ours(args):
     h_off = torch.randint(0, 2 * PAD + 1, (Ke + 3, 2, B, 2), generator=g, dtype=torch.int32).pin_memory()
     h_rew = torch.empty((B, 1), dtype=torch.float32).pin_memory()
 
+    n_idx, n_off = h_idx.numpy(), h_off.numpy()          # views of the pinned buffers
+
     def e2e_step(t):
-        obs, act, rew, nxt, nd = buf.sample_drq(pad=PAD, idxs=h_idx[t], offsets={"obs": h_off[t, 0], "next_obs": h_off[t, 1]})
+        obs, act, rew, nxt, nd = buf.sample_drq(pad=PAD, idxs=n_idx[t], offsets={"obs": n_off[t, 0], "next_obs": n_off[t, 1]})
         h_rew.copy_(rew, non_blocking=True)
         stream.synchronize()
         return obs
@@ -281,7 +283,8 @@ def run_ours(args):
         el = float(tmax.item())
     e2e = {"value": world * Ke * B / el, "unit": UNIT, "h2d_bytes_per_step": B * 8 + 2 * B * 2 * 4,
            "d2h_bytes_per_step": B * 4, "steps": Ke, "ms_per_step": 1e3 * el / Ke,
-           "api": "ReplayBuffer.sample_drq(idxs=host, offsets=host) + D2H of rewards + stream sync per step"}
+           "api": "ReplayBuffer.sample_drq(idxs=host, offsets=host) + D2H of rewards + stream sync per step; "
+                  "host draws travel by value in the kernel launch (augcl_ring_sample_ex, HOST)"}
     return dict(buf=buf, dev=dev, world=world, rank=rank, ms=ms, value=value, launches=launches, clocks=clocks, e2e=e2e,
                 step_raw=fn, K=K, W=W, B=B)
 

@@ -46,7 +46,9 @@ typedef enum augcl_status {
 } augcl_status;
 
 /* aug_mode of augcl_ring_sample */
-enum { AUGCL_AUG_NONE = 0, AUGCL_AUG_SHIFT = 1, AUGCL_AUG_CROP = 2 };
+/* SHIFT_OBS: random_shift on obs only, next_obs gathered un-augmented (the SVEA / AugCL update,
+ * src/algorithms/svea.py:66-70, augcl.py:69-72); off_next is ignored. */
+enum { AUGCL_AUG_NONE = 0, AUGCL_AUG_SHIFT = 1, AUGCL_AUG_CROP = 2, AUGCL_AUG_SHIFT_OBS = 3 };
 /* mode of augcl_random_shift */
 enum { AUGCL_SHIFT_INT = 0, AUGCL_SHIFT_BILINEAR = 1 };
 /* bank_dtype of overlay / splice */
@@ -110,6 +112,32 @@ int augcl_ring_sample(augcl_ring* ring, const int64_t* idx, int B, float* out_ob
                       float* out_act, float* out_rew, float* out_nd, int aug_mode,
                       const int32_t* off_obs, const int32_t* off_next, int pad_or_size,
                       int normalize, augcl_stream stream);
+
+/* Where augcl_ring_sample_ex takes the sampled indices / the offsets from. */
+enum { AUGCL_SRC_DEVICE = 0, AUGCL_SRC_HOST = 1, AUGCL_SRC_PHILOX = 2 };
+
+/* augcl_ring_sample with the draws taken from the HOST or generated inside the kernel.  This is the
+ * entry point behind ReplayBuffer.sample*() when the caller holds numpy indices, as the reference does
+ * (np.random.randint on the host, src/utils.py:229-232, then H2D of the gathered batch, :206-214).
+ *   idx_src  DEVICE: idx = device int64[B] (== augcl_ring_sample)
+ *            HOST:   idx = host int64[B], consumed before the call returns; every value must be in
+ *                    [0, capacity) (AUGCL_ERR_BAD_ARG otherwise, like the reference's IndexError).  For
+ *                    B <= 256 and the 84x84 / 100x100 geometries the indices (and HOST offsets) travel BY
+ *                    VALUE in the kernel's parameter block: no separate H2D copy; otherwise they are staged
+ *                    through stream-ordered scratch (cudaMallocAsync) with one cudaMemcpyAsync per array.
+ *            PHILOX: idx ignored; slot of sample b = (philox_word(b; seed, subsequence) * idx_hi) >> 32,
+ *                    identical to augcl_rng_fill_indices(out, B, 0, idx_hi, seed, subsequence).
+ *   off_src  DEVICE / HOST: off_obs / off_next = int32[B,2] there (NULL = identity for SHIFT).
+ *            PHILOX: offsets of a tensor whose pointer is NULL are drawn in the kernel, uniform in
+ *                    [0, 2*pad] (SHIFT) or [0, W-size) (CROP; the reference's exclusive bound), identical to
+ *                    augcl_rng_fill_offsets(out, 2*B, 0, range, seed, subsequence + 1) for obs and
+ *                    (…, subsequence + 2) for next_obs; a non-NULL pointer is a DEVICE array and wins.
+ * All other arguments as in augcl_ring_sample. */
+int augcl_ring_sample_ex(augcl_ring* ring, int idx_src, const int64_t* idx, int64_t idx_hi, int B,
+                         float* out_obs, float* out_next, float* out_act, float* out_rew, float* out_nd,
+                         int aug_mode, int off_src, const int32_t* off_obs, const int32_t* off_next,
+                         int pad_or_size, int normalize, uint64_t seed, uint64_t subsequence,
+                         augcl_stream stream);
 
 /* ------------------------------------------------------------------------------------------
  * Stand-alone augmentations on f32 NCHW batches (in and out must not alias).

@@ -199,3 +199,58 @@ def test_band_kernel_equals_generic_kernel_full_ring(U, S, aug, B):
     finally:
         for k, v in (("staging", "tma"), ("sample_band", 1), ("sample_pdl", 1), ("sample_stages", 0), ("sample_ctas_per_sm", 6)):
             L.set_option(k, str(v))
+
+
+@pytest.mark.parametrize("S,B", [(84, 128), (84, 300), (100, 64), (36, 10)])
+def test_fused_philox_draws_equal_explicit_draws(U, O, S, B):
+    """Offsets / indices drawn INSIDE the sample kernel are the same numbers augcl_rng_fill_* produce for the same
+    (seed, subsequence) -- and the same the oracle's Philox restatement produces -- so a fused-draw call equals the
+    call with those draws supplied explicitly (inline by-value path for B <= 256, staged path above)."""
+    from augcl_b200 import _lib as L
+    from augcl_b200 import augmentations as A
+    cap, pad = 500, 4
+    buf = U.ReplayBuffer((9, S, S), (3,), cap, B)
+    buf.fill_synthetic(seed=7)
+    A.seed(4242)
+    sub = A._calls                      # the next _sample reserves (sub, sub+1, sub+2)
+    got = buf.sample_drq(pad=pad, device_indices=True)
+    idx = O.rng_randint(B, 0, cap, 4242, sub)
+    o1 = O.rng_randint(2 * B, 0, 2 * pad + 1, 4242, sub + 1).reshape(B, 2)
+    o2 = O.rng_randint(2 * B, 0, 2 * pad + 1, 4242, sub + 2).reshape(B, 2)
+    want = buf.sample_drq(pad=pad, idxs=idx, offsets={"obs": o1, "next_obs": o2})
+    for g, w in zip(got, want):
+        assert torch.equal(g, w)
+    # SVEA pattern: obs drawn, next_obs untouched
+    sub = A._calls
+    got = buf.sample_svea(pad=pad, idxs=idx)
+    o1 = O.rng_randint(2 * B, 0, 2 * pad + 1, 4242, sub + 1).reshape(B, 2)
+    want = buf.sample_svea(pad=pad, idxs=idx, offsets=o1)
+    plain = buf.sample(idxs=idx)
+    assert torch.equal(got[0], want[0]) and torch.equal(got[3], plain[3]) and torch.equal(want[3], plain[3])
+    # same call with DEVICE tensors for indices and offsets
+    dev = buf.sample_svea(pad=pad, idxs=torch.from_numpy(idx).cuda(), offsets=torch.from_numpy(o1).cuda())
+    assert torch.equal(dev[0], want[0]) and torch.equal(dev[1], want[1])
+    if S > 84:      # CURL: crop draws have the reference's exclusive upper bound
+        sub = A._calls
+        got = buf.sample_curl(idxs=idx, size=84)
+        cm = S - 84
+        oo = O.rng_randint(2 * B, 0, cm, 4242, sub + 1).reshape(B, 2)
+        on = O.rng_randint(2 * B, 0, cm, 4242, sub + 2).reshape(B, 2)
+        op = O.rng_randint(2 * B, 0, cm, 4242, sub + 4).reshape(B, 2)     # second launch: (sub+3, +4, +5)
+        want = buf.sample_curl(idxs=idx, size=84, offsets={"obs": oo, "next_obs": on, "pos": op})
+        for g, w in zip(got, want):
+            assert torch.equal(g, w)
+
+
+def test_host_draws_are_validated(U):
+    from augcl_b200._lib import AugclError
+    buf = U.ReplayBuffer((9, 84, 84), (2,), 50, 8)
+    buf.fill_synthetic(seed=1)
+    with pytest.raises(AugclError):
+        buf.sample(idxs=np.array([0, 50]))           # the reference raises IndexError here
+    with pytest.raises(AugclError):
+        buf.sample(idxs=np.array([-1, 3]))
+    with pytest.raises(AugclError):
+        buf.sample_drq(pad=4, idxs=np.array([1, 2]), offsets={"obs": np.array([[0, 9], [0, 0]]), "next_obs": np.zeros((2, 2))})
+    with pytest.raises(ValueError):
+        buf.sample_drq(pad=4, idxs=np.array([1, 2]), offsets={"obs": np.zeros((3, 2)), "next_obs": np.zeros((2, 2))})
