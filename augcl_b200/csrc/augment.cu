@@ -98,25 +98,39 @@ __global__ void __launch_bounds__(256) shift_bilinear_kernel(const float* __rest
 }
 
 // ---------------------------------------------------------------------------------------------
-// random_conv: CTA = one RGB frame x one band of kBand rows.  The band (+1-row/col replicate halo),
-// already divided by 255, is staged in shared memory; the 81 weights of the sample sit in shared
-// memory as [27][4] so one broadcast LDS.128 feeds the three output channels of a tap.  Each thread
-// produces a 1x4 strip for all three output channels: 324 explicit FMAs, then sigmoid and *255.
+// random_conv: CTA (128 threads) = one RGB frame x one band of kBand rows.  The band (+1-row/col replicate
+// halo), already divided by 255, is staged in shared memory ([ci][row][1 + col], so the 6-wide input window
+// of a 4-pixel strip is one aligned LDS.128 + one LDS.64); the 81 weights of the sample sit in shared memory
+// as [27][4] so one broadcast LDS.128 feeds the three output channels of a tap.  A thread produces a 2x4
+// block of pixels for all three output channels: 648 explicit FMAs from 24 input and 27 weight loads, then
+// sigmoid and *255.  Per output element: 27 FMA + 2 MUFU -- the kernel sits at the FP32/HBM ridge.
 // ---------------------------------------------------------------------------------------------
 constexpr int kBand = 12;
+constexpr int kConvThreads = 128;
 
 __device__ __forceinline__ float sigmoid255(float v) {
   return __fdividef(1.0f, 1.0f + __expf(-v)) * 255.0f;
 }
 
-__global__ void __launch_bounds__(256, 3) random_conv_kernel(const float* __restrict__ in, float* __restrict__ out,
-                                                          int frames, int k, int h, int w,
-                                                          const float* __restrict__ weights, int bands, int RS) {
+// x / 255 correctly rounded (== __fdiv_rn(x, 255.0f) for every x whose quotient is a normal float) in three
+// FP ops: Markstein's correction of q0 = x * fl(1/255) by the exact remainder.  tests/ checks it against IEEE
+// division over all integers 0..255 and 2^24 random floats.
+__device__ __forceinline__ float div255(float x) {
+  const float rcp = 0.00392156862745098f;          // fl(1/255)
+  const float q0 = x * rcp;
+  const float rem = fmaf(-255.0f, q0, x);
+  return fmaf(rem, rcp, q0);
+}
+
+__global__ void __launch_bounds__(kConvThreads, 6) random_conv_kernel(const float* __restrict__ in, float* __restrict__ out,
+                                                                      int frames, int k, int h, int w,
+                                                                      const float* __restrict__ weights, int bands, int RS,
+                                                                      int vec) {
   extern __shared__ __align__(16) float csm[];
   float* wsm = csm;              // [27][4]
   float* tile = csm + 27 * 4;    // [3][kBand+2][RS]
   const int tid = threadIdx.x;
-  const int wq = (w + 3) >> 2;
+  const int nq = (w + 3) >> 2;
   for (int work = blockIdx.x; work < frames * bands; work += gridDim.x) {
     const int frame = work / bands, band = work - frame * bands;
     const int sample = frame / k;
@@ -130,52 +144,82 @@ __global__ void __launch_bounds__(256, 3) random_conv_kernel(const float* __rest
       wsm[tap * 4 + co] = weights[(int64_t)sample * 81 + tid];
     }
     const int trows = rows + 2;
-    for (int e = tid; e < 3 * trows * RS; e += blockDim.x) {
-      const int pc = e % RS;
-      const int t2 = e / RS;
-      const int pr = t2 % trows, ch = t2 / trows;
-      const int rr = clampi(r0 + pr - 1, 0, h - 1), cc = clampi(pc - 1, 0, w - 1);
-      tile[(ch * (kBand + 2) + pr) * RS + pc] = __fdiv_rn(__ldg(src + ((int64_t)ch * h + rr) * w + cc), 255.0f);
+    for (int e = tid; e < 3 * trows * nq; e += kConvThreads) {
+      const int q = e % nq;
+      const int t2 = e / nq;
+      const int pr = t2 % trows, ci = t2 / trows;
+      const int rr = clampi(r0 + pr - 1, 0, h - 1);
+      const float* row = src + ((int64_t)ci * h + rr) * w;
+      float* trow = tile + (ci * (kBand + 2) + pr) * RS;
+      float v[4];
+      if (vec) {
+        const float4 t = __ldg(reinterpret_cast<const float4*>(row) + q);
+        v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+      } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) v[j] = __ldg(row + min(4 * q + j, w - 1));
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) v[j] = div255(v[j]);
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (vec || 4 * q + j < w) trow[1 + 4 * q + j] = v[j];
+      if (q == 0) trow[0] = v[0];                                   // replicate pad, left
+      if (q == nq - 1) trow[w + 1] = v[(w - 1) & 3];                // replicate pad, right (column w-1)
     }
     __syncthreads();
-    for (int v = tid; v < rows * wq; v += blockDim.x) {
-      const int r = v / wq, q4 = v - r * wq;
-      float acc[3][4];
+    const int ntask = ((rows + 1) >> 1) * nq;
+    for (int task = tid; task < ntask; task += kConvThreads) {
+      const int rp = task / nq, q4 = task - rp * nq;
+      const int r = rp * 2;
+      float acc[2][3][4];
 #pragma unroll
-      for (int co = 0; co < 3; ++co)
+      for (int a = 0; a < 2; ++a)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) acc[co][j] = 0.0f;
+        for (int co = 0; co < 3; ++co)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) acc[a][co][j] = 0.0f;
 #pragma unroll 1
       for (int ci = 0; ci < 3; ++ci) {
+        float x[4][6];
 #pragma unroll
-        for (int ky = 0; ky < 3; ++ky) {
-          const float* trow = tile + (ci * (kBand + 2) + r + ky) * RS + q4 * 4;
+        for (int y = 0; y < 4; ++y) {
+          const float* trow = tile + (ci * (kBand + 2) + r + y) * RS + q4 * 4;
           const float4 a = *reinterpret_cast<const float4*>(trow);
           const float2 b = *reinterpret_cast<const float2*>(trow + 4);
-          const float x[6] = {a.x, a.y, a.z, a.w, b.x, b.y};
+          x[y][0] = a.x; x[y][1] = a.y; x[y][2] = a.z; x[y][3] = a.w; x[y][4] = b.x; x[y][5] = b.y;
+        }
+#pragma unroll
+        for (int ky = 0; ky < 3; ++ky) {
 #pragma unroll
           for (int kx = 0; kx < 3; ++kx) {
             const float4 wv = *reinterpret_cast<const float4*>(wsm + (ci * 9 + ky * 3 + kx) * 4);
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              acc[0][j] = fmaf(x[j + kx], wv.x, acc[0][j]);
-              acc[1][j] = fmaf(x[j + kx], wv.y, acc[1][j]);
-              acc[2][j] = fmaf(x[j + kx], wv.z, acc[2][j]);
-            }
+            for (int a = 0; a < 2; ++a)
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                acc[a][0][j] = fmaf(x[a + ky][j + kx], wv.x, acc[a][0][j]);
+                acc[a][1][j] = fmaf(x[a + ky][j + kx], wv.y, acc[a][1][j]);
+                acc[a][2][j] = fmaf(x[a + ky][j + kx], wv.z, acc[a][2][j]);
+              }
           }
         }
       }
       const int col = q4 * 4;
 #pragma unroll
-      for (int co = 0; co < 3; ++co) {
-        float* dst = out + (((int64_t)frame * 3 + co) * h + (r0 + r)) * w + col;
-        const float4 o = make_float4(sigmoid255(acc[co][0]), sigmoid255(acc[co][1]), sigmoid255(acc[co][2]),
-                                     sigmoid255(acc[co][3]));
-        if ((w & 3) == 0) {
-          *reinterpret_cast<float4*>(dst) = o;
-        } else {
-          const float ov[4] = {o.x, o.y, o.z, o.w};
-          for (int j = 0; j < 4 && col + j < w; ++j) dst[j] = ov[j];
+      for (int a = 0; a < 2; ++a) {
+        if (r + a >= rows) break;
+#pragma unroll
+        for (int co = 0; co < 3; ++co) {
+          float* dst = out + (((int64_t)frame * 3 + co) * h + (r0 + r + a)) * w + col;
+          const float4 o = make_float4(sigmoid255(acc[a][co][0]), sigmoid255(acc[a][co][1]), sigmoid255(acc[a][co][2]),
+                                       sigmoid255(acc[a][co][3]));
+          if (vec) {
+            *reinterpret_cast<float4*>(dst) = o;
+          } else {
+            const float ov[4] = {o.x, o.y, o.z, o.w};
+            for (int j = 0; j < 4 && col + j < w; ++j) dst[j] = ov[j];
+          }
         }
       }
     }
@@ -188,30 +232,37 @@ __global__ void __launch_bounds__(256, 3) random_conv_kernel(const float* __rest
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ float overlay_px(float x, float img, float oma, float alpha) {
   // ((1 - alpha) * (x / 255.0) + alpha * imgs) * 255.0     (src/augmentations.py:262)
-  return (oma * __fdiv_rn(x, 255.0f) + alpha * img) * 255.0f;
+  return (oma * div255(x) + alpha * img) * 255.0f;
 }
 
+// Thread = one 4-pixel group of one background channel (sample i, ch, p4): the background pixels are
+// loaded and normalised once and reused for the k frames of the sample (channel f*3+ch of x uses img[ch]).
+// blockIdx.x = (i * 3 + ch) * chunks + chunk: the decode is per CTA, not per thread.
 template <bool BANK_U8>
 __global__ void __launch_bounds__(256) overlay_vec_kernel(const float4* __restrict__ in, float4* __restrict__ out,
-                                                          int64_t nvec, int c, int hw4, const void* __restrict__ bank,
+                                                          int k, int hw4, int chunks, const void* __restrict__ bank,
                                                           int64_t bank_len, const int64_t* __restrict__ bank_idx,
                                                           float oma, float alpha) {
-  for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t plane = v / hw4;
-    const int p4 = (int)(v - plane * hw4);
-    const int i = (int)(plane / c), ch = (int)(plane - (int64_t)i * c);
-    int64_t row = bank_idx[i];
-    row = row < 0 ? 0 : (row >= bank_len ? bank_len - 1 : row);
-    const int64_t boff = (row * 3 + (ch % 3)) * (int64_t)hw4 + p4;
-    float4 g;
-    if (BANK_U8) {
-      const float4 t = bytes_to_float4(__ldg(reinterpret_cast<const uint32_t*>(bank) + boff));
-      g = make_float4(__fdiv_rn(t.x, 255.0f), __fdiv_rn(t.y, 255.0f), __fdiv_rn(t.z, 255.0f), __fdiv_rn(t.w, 255.0f));
-    } else {
-      g = __ldg(reinterpret_cast<const float4*>(bank) + boff);
-    }
-    const float4 x = __ldg(in + v);
-    out[v] = make_float4(overlay_px(x.x, g.x, oma, alpha), overlay_px(x.y, g.y, oma, alpha),
+  const int chunk = blockIdx.x % chunks;
+  const int ic = blockIdx.x / chunks;
+  const int i = ic / 3, ch = ic - 3 * i;
+  const int p4 = chunk * 256 + threadIdx.x;
+  if (p4 >= hw4) return;
+  int64_t row = bank_idx[i];
+  row = row < 0 ? 0 : (row >= bank_len ? bank_len - 1 : row);
+  const int64_t boff = (row * 3 + ch) * (int64_t)hw4 + p4;
+  float4 g;
+  if (BANK_U8) {
+    const float4 t = bytes_to_float4(__ldg(reinterpret_cast<const uint32_t*>(bank) + boff));
+    g = make_float4(div255(t.x), div255(t.y), div255(t.z), div255(t.w));
+  } else {
+    g = __ldg(reinterpret_cast<const float4*>(bank) + boff);
+  }
+  const int64_t base = ((int64_t)i * 3 * k + ch) * hw4 + p4;
+  for (int f = 0; f < k; ++f) {
+    const int64_t o = base + (int64_t)f * 3 * hw4;
+    const float4 x = __ldg(in + o);
+    out[o] = make_float4(overlay_px(x.x, g.x, oma, alpha), overlay_px(x.y, g.y, oma, alpha),
                          overlay_px(x.z, g.z, oma, alpha), overlay_px(x.w, g.w, oma, alpha));
   }
 }
@@ -240,13 +291,23 @@ struct SpliceThr {
 };
 
 // kornia.color.rgb_to_hsv (0.5.x, eps=1e-6) + the threshold test of create_hsv_mask, per pixel.
+// Fast path for hue_thres == sat_thres == 0 (the reference's defaults, src/augmentations.py:295): the three
+// divisions only decide signs there.  With delta = max - min >= 0 and d = delta (or 1):
+//   s   = delta / (max + eps) > 0   <=>  delta > 0 and max + eps > 0
+//   hue = 2pi * frac(hsel / d / 6) > 0  <=>  hsel != 0, and hsel is >= d when g or b is the first maximum,
+//         so only the r-is-max branch (hsel = (max-b) - (max-g)) can be zero.
+// (No quotient can underflow for inputs below 2^100.)  Other thresholds take the full formula.
 __device__ __forceinline__ bool hsv_gt(float r, float g, float b, float ht, float st, float vt) {
   const float maxc = fmaxf(fmaxf(r, g), b);
   const float minc = fminf(fminf(r, g), b);
   const float delta = maxc - minc;
+  const float rc = maxc - r, gc = maxc - g, bc = maxc - b;
+  if (ht == 0.0f && st == 0.0f) {
+    const bool hue_pos = !(r == maxc && (bc - gc) == 0.0f);
+    return delta > 0.0f && (maxc + 1e-6f) > 0.0f && hue_pos && maxc > vt;
+  }
   const float s = __fdiv_rn(delta, maxc + 1e-6f);
   const float d = (delta == 0.0f) ? 1.0f : delta;
-  const float rc = maxc - r, gc = maxc - g, bc = maxc - b;
   const float hsel = (r == maxc) ? (bc - gc) : ((g == maxc) ? ((2.0f * d + rc) - bc) : ((4.0f * d + gc) - rc));
   float hh = __fdiv_rn(__fdiv_rn(hsel, d), 6.0f);
   if (hh < 0.0f) hh = hh + 1.0f;                 // torch.remainder(., 1.0) for |.| < 1
@@ -256,7 +317,7 @@ __device__ __forceinline__ bool hsv_gt(float r, float g, float b, float ht, floa
 
 __device__ __forceinline__ void splice_px(float xr, float xg, float xb, float gr, float gg, float gb,
                                           const SpliceThr& t, float& o_r, float& o_g, float& o_b) {
-  const float r = __fdiv_rn(xr, 255.0f), g = __fdiv_rn(xg, 255.0f), b = __fdiv_rn(xb, 255.0f);
+  const float r = div255(xr), g = div255(xg), b = div255(xb);
   bool keep = hsv_gt(r, g, b, t.hue, t.sat, t.val);
   if (t.variant == AUGCL_CS_SPLICE) {
     // overlay[mask2] = x[mask2]; overlay[~mask] = x[~mask]   (src/augmentations.py:318-323)
@@ -272,34 +333,35 @@ template <bool BANK_U8>
 __device__ __forceinline__ float4 bank_vec(const void* bank, int64_t off4) {
   if (BANK_U8) {
     const float4 t = bytes_to_float4(__ldg(reinterpret_cast<const uint32_t*>(bank) + off4));
-    return make_float4(__fdiv_rn(t.x, 255.0f), __fdiv_rn(t.y, 255.0f), __fdiv_rn(t.z, 255.0f), __fdiv_rn(t.w, 255.0f));
+    return make_float4(div255(t.x), div255(t.y), div255(t.z), div255(t.w));
   }
   return __ldg(reinterpret_cast<const float4*>(bank) + off4);
 }
 
+// Thread = one 4-pixel group of one RGB frame; blockIdx.x = frame * chunks + chunk (per-CTA decode).
 template <bool BANK_U8>
 __global__ void __launch_bounds__(256) splice_vec_kernel(const float4* __restrict__ in, float4* __restrict__ out,
-                                                         int64_t nwork, int n, int hw4, const void* __restrict__ bank,
+                                                         int n, int hw4, int chunks, const void* __restrict__ bank,
                                                          int64_t bank_len, const int64_t* __restrict__ bank_idx,
                                                          SpliceThr thr) {
-  for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nwork; v += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t frame = v / hw4;          // row j of x.reshape(n*k, 3, h, w)
-    const int p4 = (int)(v - frame * hw4);
-    int64_t row = bank_idx[frame % n];      // overlay = batch.repeat(k,1,1,1): row j <- background j mod n
-    row = row < 0 ? 0 : (row >= bank_len ? bank_len - 1 : row);
-    const int64_t xo = frame * 3 * hw4 + p4, bo = row * 3 * hw4 + p4;
-    const float4 xr = __ldg(in + xo), xg = __ldg(in + xo + hw4), xb = __ldg(in + xo + 2 * (int64_t)hw4);
-    const float4 gr = bank_vec<BANK_U8>(bank, bo), gg = bank_vec<BANK_U8>(bank, bo + hw4),
-                 gb = bank_vec<BANK_U8>(bank, bo + 2 * (int64_t)hw4);
-    float4 o_r, o_g, o_b;
-    splice_px(xr.x, xg.x, xb.x, gr.x, gg.x, gb.x, thr, o_r.x, o_g.x, o_b.x);
-    splice_px(xr.y, xg.y, xb.y, gr.y, gg.y, gb.y, thr, o_r.y, o_g.y, o_b.y);
-    splice_px(xr.z, xg.z, xb.z, gr.z, gg.z, gb.z, thr, o_r.z, o_g.z, o_b.z);
-    splice_px(xr.w, xg.w, xb.w, gr.w, gg.w, gb.w, thr, o_r.w, o_g.w, o_b.w);
-    out[xo] = o_r;
-    out[xo + hw4] = o_g;
-    out[xo + 2 * (int64_t)hw4] = o_b;
-  }
+  const int chunk = blockIdx.x % chunks;
+  const int frame = blockIdx.x / chunks;     // row j of x.reshape(n*k, 3, h, w)
+  const int p4 = chunk * 256 + threadIdx.x;
+  if (p4 >= hw4) return;
+  int64_t row = bank_idx[frame % n];         // overlay = batch.repeat(k,1,1,1): row j <- background j mod n
+  row = row < 0 ? 0 : (row >= bank_len ? bank_len - 1 : row);
+  const int64_t xo = (int64_t)frame * 3 * hw4 + p4, bo = row * 3 * hw4 + p4;
+  const float4 xr = __ldg(in + xo), xg = __ldg(in + xo + hw4), xb = __ldg(in + xo + 2 * (int64_t)hw4);
+  const float4 gr = bank_vec<BANK_U8>(bank, bo), gg = bank_vec<BANK_U8>(bank, bo + hw4),
+               gb = bank_vec<BANK_U8>(bank, bo + 2 * (int64_t)hw4);
+  float4 o_r, o_g, o_b;
+  splice_px(xr.x, xg.x, xb.x, gr.x, gg.x, gb.x, thr, o_r.x, o_g.x, o_b.x);
+  splice_px(xr.y, xg.y, xb.y, gr.y, gg.y, gb.y, thr, o_r.y, o_g.y, o_b.y);
+  splice_px(xr.z, xg.z, xb.z, gr.z, gg.z, gb.z, thr, o_r.z, o_g.z, o_b.z);
+  splice_px(xr.w, xg.w, xb.w, gr.w, gg.w, gb.w, thr, o_r.w, o_g.w, o_b.w);
+  out[xo] = o_r;
+  out[xo + hw4] = o_g;
+  out[xo + 2 * (int64_t)hw4] = o_b;
 }
 
 template <bool BANK_U8>
@@ -414,9 +476,10 @@ int augcl_random_conv(const float* in, float* out, int n, int c, int h, int w, c
   static std::atomic<bool> configured{false};
   if (!configured.exchange(true))
     AUGCL_CUDA(cudaFuncSetAttribute(random_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  const int vec = ((w & 3) == 0 && aligned(in, 16) && aligned(out, 16)) ? 1 : 0;
   const int64_t work = (int64_t)frames * bands;
-  const int grid = (int)(work < kNumSMs * 8 ? work : kNumSMs * 8);
-  random_conv_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(in, out, frames, k, h, w, weights, bands, RS);
+  const int grid = (int)(work < kNumSMs * 12 ? work : kNumSMs * 12);
+  random_conv_kernel<<<grid, kConvThreads, smem, (cudaStream_t)stream>>>(in, out, frames, k, h, w, weights, bands, RS, vec);
   AUGCL_LAUNCHED();
   return AUGCL_OK;
 }
@@ -441,12 +504,14 @@ int augcl_random_overlay(const float* in, float* out, int n, int c, int h, int w
   const bool vec = g_staging.load() == 0 && (hw & 3) == 0 && aligned(in, 16) && aligned(out, 16) &&
                    aligned(bank, u8 ? 4 : 16);
   if (vec) {
-    const int64_t nvec = total / 4;
-    const int grid = grid_for(nvec, 256, 8);
+    const int hw4 = hw / 4, chunks = (hw4 + 255) / 256;
+    const int64_t grid64 = (int64_t)n * 3 * chunks;
+    AUGCL_REQUIRE(grid64 < (1ll << 31), "augcl_random_overlay: batch too large");
+    const unsigned grid = (unsigned)grid64;
     if (u8)
-      overlay_vec_kernel<true><<<grid, 256, 0, st>>>((const float4*)in, (float4*)out, nvec, c, hw / 4, bank, bank_len, bank_idx, oma, alpha);
+      overlay_vec_kernel<true><<<grid, 256, 0, st>>>((const float4*)in, (float4*)out, c / 3, hw4, chunks, bank, bank_len, bank_idx, oma, alpha);
     else
-      overlay_vec_kernel<false><<<grid, 256, 0, st>>>((const float4*)in, (float4*)out, nvec, c, hw / 4, bank, bank_len, bank_idx, oma, alpha);
+      overlay_vec_kernel<false><<<grid, 256, 0, st>>>((const float4*)in, (float4*)out, c / 3, hw4, chunks, bank, bank_len, bank_idx, oma, alpha);
   } else {
     const int grid = grid_for(total, 256, 16);
     if (u8)
@@ -473,12 +538,14 @@ int augcl_splice(const float* in, float* out, int n, int c, int h, int w, const 
   const bool vec = g_staging.load() == 0 && (hw & 3) == 0 && aligned(in, 16) && aligned(out, 16) &&
                    aligned(bank, u8 ? 4 : 16);
   if (vec) {
-    const int64_t nwork = frames * (hw / 4);
-    const int grid = grid_for(nwork, 256, 8);
+    const int hw4 = hw / 4, chunks = (hw4 + 255) / 256;
+    const int64_t grid64 = frames * chunks;
+    AUGCL_REQUIRE(grid64 < (1ll << 31), "augcl_splice: batch too large");
+    const unsigned grid = (unsigned)grid64;
     if (u8)
-      splice_vec_kernel<true><<<grid, 256, 0, st>>>((const float4*)in, (float4*)out, nwork, n, hw / 4, bank, bank_len, bank_idx, thr);
+      splice_vec_kernel<true><<<grid, 256, 0, st>>>((const float4*)in, (float4*)out, n, hw4, chunks, bank, bank_len, bank_idx, thr);
     else
-      splice_vec_kernel<false><<<grid, 256, 0, st>>>((const float4*)in, (float4*)out, nwork, n, hw / 4, bank, bank_len, bank_idx, thr);
+      splice_vec_kernel<false><<<grid, 256, 0, st>>>((const float4*)in, (float4*)out, n, hw4, chunks, bank, bank_len, bank_idx, thr);
   } else {
     const int64_t nwork = frames * hw;
     const int grid = grid_for(nwork, 256, 16);
