@@ -22,6 +22,7 @@ template <int WQ>
 __global__ void __launch_bounds__(256) window_copy_vec_kernel(const float* __restrict__ in, float* __restrict__ out,
                                                               int planes, int c, int H, int W, int Ho, int Wo,
                                                               const int32_t* __restrict__ offsets, int pad) {
+  constexpr int UNR = 4;   // 16 independent loads in flight per thread before the first store
   const int wq = WQ ? WQ : (Wo >> 2);
   const int nvec = Ho * wq;
   for (int plane = blockIdx.x; plane < planes; plane += gridDim.x) {
@@ -29,18 +30,24 @@ __global__ void __launch_bounds__(256) window_copy_vec_kernel(const float* __res
     const int dy = offsets[2 * i] - pad, dx = offsets[2 * i + 1] - pad;
     const float* src = in + (int64_t)plane * H * W;
     float4* dst = reinterpret_cast<float4*>(out + (int64_t)plane * Ho * Wo);
-    for (int v = threadIdx.x; v < nvec; v += blockDim.x) {
-      const int r = v / wq, q4 = v - r * wq;
-      const float* row = src + (int64_t)clampi(r + dy, 0, H - 1) * W;
-      const int c0 = q4 * 4 + dx;
-      float4 o;
-      if (c0 >= 0 && c0 + 3 < W) {
-        o = make_float4(__ldg(row + c0), __ldg(row + c0 + 1), __ldg(row + c0 + 2), __ldg(row + c0 + 3));
-      } else {
-        o = make_float4(__ldg(row + clampi(c0, 0, W - 1)), __ldg(row + clampi(c0 + 1, 0, W - 1)),
-                        __ldg(row + clampi(c0 + 2, 0, W - 1)), __ldg(row + clampi(c0 + 3, 0, W - 1)));
+    for (int v0 = threadIdx.x; v0 < nvec; v0 += UNR * 256) {
+      float4 o[UNR];
+#pragma unroll
+      for (int u = 0; u < UNR; ++u) {
+        const int v = v0 + u * 256;
+        if (v < nvec) {
+          const int r = v / wq, q4 = v - r * wq;
+          const float* row = src + (int64_t)clampi(r + dy, 0, H - 1) * W;
+          const int c0 = q4 * 4 + dx;
+          o[u] = make_float4(__ldg(row + clampi(c0, 0, W - 1)), __ldg(row + clampi(c0 + 1, 0, W - 1)),
+                             __ldg(row + clampi(c0 + 2, 0, W - 1)), __ldg(row + clampi(c0 + 3, 0, W - 1)));
+        }
       }
-      dst[v] = o;
+#pragma unroll
+      for (int u = 0; u < UNR; ++u) {
+        const int v = v0 + u * 256;
+        if (v < nvec) dst[v] = o[u];
+      }
     }
   }
 }
@@ -227,6 +234,125 @@ __global__ void __launch_bounds__(kConvThreads, 6) random_conv_kernel(const floa
 }
 
 // ---------------------------------------------------------------------------------------------
+// random_conv, TMA-staged (w % 4 == 0, 16-B aligned tensors): same 2x4 register blocking, but the band is
+// brought in RAW by one cp.async.bulk per row (336 B at w = 84) into a double-buffered tile -- the next
+// work item's rows are in flight while this one is computed, and no thread spends instructions on the
+// fill.  The /255 moves into the 81 weights (conv(x/255, W) == conv(x, W/255) up to fp32 rounding, well
+// inside the 1e-5 normalised tolerance); the replicate columns are patched by 3*(rows+2) threads after the
+// copy lands.  Tile row layout: [3]=left pad, [4 .. 4+w) = pixels (16-B aligned for the bulk copy and the
+// LDS.128 of the window), [4+w] = right pad.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kConvThreads, 6) random_conv_tma_kernel(const float* __restrict__ in, float* __restrict__ out,
+                                                                          int frames, int k, int h, int w,
+                                                                          const float* __restrict__ weights, int bands, int RS) {
+  extern __shared__ __align__(128) float csm[];
+  uint64_t* bars = reinterpret_cast<uint64_t*>(csm);       // 2 mbarriers (16 B), padded to 16 floats
+  float* wsm = csm + 16;                                   // [27][4]
+  float* tiles = csm + 16 + 27 * 4;                        // [2][3][kBand+2][RS]   (124 floats in: 16-B aligned)
+  const int tile_floats = 3 * (kBand + 2) * RS;
+  const int tid = threadIdx.x;
+  const int nq = w >> 2;
+  const int total = frames * bands;
+  if (tid == 0) {
+    mbar_init(&bars[0], 1);
+    mbar_init(&bars[1], 1);
+    mbar_fence_init();
+  }
+  __syncthreads();
+  pdl_wait();
+
+  auto issue = [&](int work, int buf) {   // threads 0 .. 3*trows-1: one row each
+    const int frame = work / bands, band = work - frame * bands;
+    const int r0 = band * kBand;
+    const int trows = min(kBand, h - r0) + 2;
+    if (tid == 0) mbar_expect_tx(&bars[buf], (uint32_t)(3 * trows * w * 4));
+    if (tid < 3 * trows) {
+      const int ci = tid / trows, pr = tid - ci * trows;
+      const int rr = clampi(r0 + pr - 1, 0, h - 1);
+      const float* src = in + (((int64_t)frame * 3 + ci) * h + rr) * w;
+      float* dst = tiles + buf * tile_floats + (ci * (kBand + 2) + pr) * RS + 4;
+      bulk_g2s(dst, src, (uint32_t)(w * 4), &bars[buf]);
+    }
+  };
+
+  if ((int)blockIdx.x < total) issue(blockIdx.x, 0);
+  pdl_launch_dependents();
+  int n = 0;
+  for (int work = blockIdx.x; work < total; work += gridDim.x, ++n) {
+    const int buf = n & 1;
+    const uint32_t phase = (uint32_t)(n >> 1) & 1u;
+    if (work + (int)gridDim.x < total) issue(work + gridDim.x, buf ^ 1);   // that buffer was released by the sync below
+    const int frame = work / bands, band = work - frame * bands;
+    const int sample = frame / k;
+    const int r0 = band * kBand;
+    const int rows = min(kBand, h - r0);
+    if (tid < 81) {
+      // weights[sample][co][ci][ky][kx] / 255 -> wsm[(ci*9 + ky*3 + kx)*4 + co]
+      const int co = tid / 27, tap = tid - co * 27;
+      wsm[tap * 4 + co] = __fdiv_rn(weights[(int64_t)sample * 81 + tid], 255.0f);
+    }
+    mbar_wait(&bars[buf], phase);
+    float* tile = tiles + buf * tile_floats;
+    if (tid < 3 * (rows + 2)) {
+      const int trows = rows + 2;
+      const int ci = tid / trows, pr = tid - ci * trows;
+      float* trow = tile + (ci * (kBand + 2) + pr) * RS;
+      trow[3] = trow[4];
+      trow[4 + w] = trow[3 + w];
+    }
+    __syncthreads();
+    const int ntask = ((rows + 1) >> 1) * nq;
+    for (int task = tid; task < ntask; task += kConvThreads) {
+      const int rp = task / nq, q4 = task - rp * nq;
+      const int r = rp * 2;
+      float acc[2][3][4];
+#pragma unroll
+      for (int a = 0; a < 2; ++a)
+#pragma unroll
+        for (int co = 0; co < 3; ++co)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) acc[a][co][j] = 0.0f;
+#pragma unroll 1
+      for (int ci = 0; ci < 3; ++ci) {
+        float x[4][6];
+#pragma unroll
+        for (int y = 0; y < 4; ++y) {
+          const float* trow = tile + (ci * (kBand + 2) + r + y) * RS + q4 * 4;
+          const float4 a = *reinterpret_cast<const float4*>(trow + 4);
+          x[y][0] = trow[3]; x[y][1] = a.x; x[y][2] = a.y; x[y][3] = a.z; x[y][4] = a.w; x[y][5] = trow[8];
+        }
+#pragma unroll
+        for (int ky = 0; ky < 3; ++ky) {
+#pragma unroll
+          for (int kx = 0; kx < 3; ++kx) {
+            const float4 wv = *reinterpret_cast<const float4*>(wsm + (ci * 9 + ky * 3 + kx) * 4);
+#pragma unroll
+            for (int a = 0; a < 2; ++a)
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                acc[a][0][j] = fmaf(x[a + ky][j + kx], wv.x, acc[a][0][j]);
+                acc[a][1][j] = fmaf(x[a + ky][j + kx], wv.y, acc[a][1][j]);
+                acc[a][2][j] = fmaf(x[a + ky][j + kx], wv.z, acc[a][2][j]);
+              }
+          }
+        }
+      }
+#pragma unroll
+      for (int a = 0; a < 2; ++a) {
+        if (r + a >= rows) break;
+#pragma unroll
+        for (int co = 0; co < 3; ++co) {
+          float4* dst = reinterpret_cast<float4*>(out + (((int64_t)frame * 3 + co) * h + (r0 + r + a)) * w) + q4;
+          st_global_f4(dst, make_float4(sigmoid255(acc[a][co][0]), sigmoid255(acc[a][co][1]), sigmoid255(acc[a][co][2]),
+                                        sigmoid255(acc[a][co][3])));
+        }
+      }
+    }
+    __syncthreads();   // tile[buf] and wsm are free again
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
 // overlay / splice: streaming elementwise kernels.  Background rows come from a device-resident bank
 // ([M][3][h][w], u8 or f32 in [0,1]); a u8 pixel is divided by 255 like torchvision's ToTensor.
 // ---------------------------------------------------------------------------------------------
@@ -238,7 +364,7 @@ __device__ __forceinline__ float overlay_px(float x, float img, float oma, float
 // Thread = one 4-pixel group of one background channel (sample i, ch, p4): the background pixels are
 // loaded and normalised once and reused for the k frames of the sample (channel f*3+ch of x uses img[ch]).
 // blockIdx.x = (i * 3 + ch) * chunks + chunk: the decode is per CTA, not per thread.
-template <bool BANK_U8>
+template <bool BANK_U8, int K>
 __global__ void __launch_bounds__(256) overlay_vec_kernel(const float4* __restrict__ in, float4* __restrict__ out,
                                                           int k, int hw4, int chunks, const void* __restrict__ bank,
                                                           int64_t bank_len, const int64_t* __restrict__ bank_idx,
@@ -259,6 +385,16 @@ __global__ void __launch_bounds__(256) overlay_vec_kernel(const float4* __restri
     g = __ldg(reinterpret_cast<const float4*>(bank) + boff);
   }
   const int64_t base = ((int64_t)i * 3 * k + ch) * hw4 + p4;
+  if (K > 0) {   // frame_stack known at compile time: all K loads are issued before the first use
+    float4 x[K > 0 ? K : 1];
+#pragma unroll
+    for (int f = 0; f < K; ++f) x[f] = __ldg(in + base + (int64_t)f * 3 * hw4);
+#pragma unroll
+    for (int f = 0; f < K; ++f)
+      out[base + (int64_t)f * 3 * hw4] = make_float4(overlay_px(x[f].x, g.x, oma, alpha), overlay_px(x[f].y, g.y, oma, alpha),
+                                                    overlay_px(x[f].z, g.z, oma, alpha), overlay_px(x[f].w, g.w, oma, alpha));
+    return;
+  }
   for (int f = 0; f < k; ++f) {
     const int64_t o = base + (int64_t)f * 3 * hw4;
     const float4 x = __ldg(in + o);
@@ -478,6 +614,22 @@ int augcl_random_conv(const float* in, float* out, int n, int c, int h, int w, c
     AUGCL_CUDA(cudaFuncSetAttribute(random_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   const int vec = ((w & 3) == 0 && aligned(in, 16) && aligned(out, 16)) ? 1 : 0;
   const int64_t work = (int64_t)frames * bands;
+  AUGCL_REQUIRE(work < (1ll << 30), "augcl_random_conv: batch too large");
+  if (vec && g_staging.load() == 0) {
+    const int RS2 = (w + 8) & ~3;
+    const size_t smem2 = (16 + 27 * 4 + 2 * 3 * (kBand + 2) * (size_t)RS2) * sizeof(float);
+    if (smem2 <= 200 * 1024) {
+      static std::atomic<bool> configured2{false};
+      if (!configured2.exchange(true))
+        AUGCL_CUDA(cudaFuncSetAttribute(random_conv_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+      int per_sm = (int)((228 * 1024) / (smem2 + 1024));
+      per_sm = per_sm < 1 ? 1 : (per_sm > 6 ? 6 : per_sm);
+      const int grid = (int)(work < kNumSMs * per_sm ? work : kNumSMs * per_sm);
+      random_conv_tma_kernel<<<grid, kConvThreads, smem2, (cudaStream_t)stream>>>(in, out, frames, k, h, w, weights, bands, RS2);
+      AUGCL_LAUNCHED();
+      return AUGCL_OK;
+    }
+  }
   const int grid = (int)(work < kNumSMs * 12 ? work : kNumSMs * 12);
   random_conv_kernel<<<grid, kConvThreads, smem, (cudaStream_t)stream>>>(in, out, frames, k, h, w, weights, bands, RS, vec);
   AUGCL_LAUNCHED();
@@ -508,10 +660,11 @@ int augcl_random_overlay(const float* in, float* out, int n, int c, int h, int w
     const int64_t grid64 = (int64_t)n * 3 * chunks;
     AUGCL_REQUIRE(grid64 < (1ll << 31), "augcl_random_overlay: batch too large");
     const unsigned grid = (unsigned)grid64;
-    if (u8)
-      overlay_vec_kernel<true><<<grid, 256, 0, st>>>((const float4*)in, (float4*)out, c / 3, hw4, chunks, bank, bank_len, bank_idx, oma, alpha);
-    else
-      overlay_vec_kernel<false><<<grid, 256, 0, st>>>((const float4*)in, (float4*)out, c / 3, hw4, chunks, bank, bank_len, bank_idx, oma, alpha);
+    const int k = c / 3;
+#define AUGCL_OV(U8, KK) overlay_vec_kernel<U8, KK><<<grid, 256, 0, st>>>((const float4*)in, (float4*)out, k, hw4, chunks, bank, bank_len, bank_idx, oma, alpha)
+    if (u8) { if (k == 3) AUGCL_OV(true, 3); else AUGCL_OV(true, 0); }
+    else    { if (k == 3) AUGCL_OV(false, 3); else AUGCL_OV(false, 0); }
+#undef AUGCL_OV
   } else {
     const int grid = grid_for(total, 256, 16);
     if (u8)

@@ -193,9 +193,9 @@ def run_ours(args):
     from augcl_b200 import _lib as L
     from augcl_b200 import utils as U
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
+    from augcl_b200 import shard
+    plan = shard.plan(CAP, args.batch, base_seed=0)
+    world, rank, local = plan.world, plan.rank, plan.local_rank
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; augcl_b200 has no CPU path (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
@@ -206,8 +206,8 @@ def run_ours(args):
 
     # ---- one ring shard per rank, synthetic frames, per-rank seed
     buf = U.ReplayBuffer((C, S, S), (A_DIM,), CAP, B, device=dev)
-    buf.fill_synthetic(seed=1000 + rank)
-    g = torch.Generator(device="cpu").manual_seed(rank)
+    buf.fill_synthetic(seed=plan.ring_seed)
+    g = torch.Generator(device="cpu").manual_seed(plan.draw_seed)
     n_sets = 8
     outs = [(torch.empty((B, C, S, S), dtype=torch.float32, device=dev), torch.empty((B, C, S, S), dtype=torch.float32, device=dev),
              torch.empty((B, A_DIM), device=dev), torch.empty((B, 1), device=dev), torch.empty((B, 1), device=dev))
@@ -249,11 +249,8 @@ def run_ours(args):
     launches = L.launch_count() - l0
     clocks = sampler.summary()
     ms = e0.elapsed_time(e1)
-    if world > 1:
-        tmax = torch.tensor([ms], device=dev)
-        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)       # off the data path: one scalar after timing stops
-        ms = float(tmax.item())
-    value = world * K * B / (ms * 1e-3)
+    ms = shard.max_over_ranks(ms, device=dev)             # off the data path: one scalar after timing stops
+    value = shard.aggregate_rate(K * B, world, ms * 1e-3)
 
     # ---- e2e: public API with HOST indices/offsets, pinned H2D + D2H of the rewards every step
     Ke = min(K, 2000)
@@ -276,15 +273,31 @@ def run_ours(args):
     for t in range(3, Ke + 3):
         e2e_step(t)
     torch.cuda.synchronize(dev)
-    el = time.perf_counter() - t0
-    if world > 1:
-        tmax = torch.tensor([el], device=dev, dtype=torch.float64)
-        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-        el = float(tmax.item())
-    e2e = {"value": world * Ke * B / el, "unit": UNIT, "h2d_bytes_per_step": B * 8 + 2 * B * 2 * 4,
+    el = shard.max_over_ranks(time.perf_counter() - t0, device=dev)
+
+    # same steps, result read one step late (double-buffered D2H + events): what an asynchronous training loop sees
+    h_rew2 = [torch.empty((B, 1), dtype=torch.float32).pin_memory() for _ in range(2)]
+    evs = [torch.cuda.Event() for _ in range(2)]
+    acc = 0.0
+    barrier()
+    t0 = time.perf_counter()
+    for t in range(3, Ke + 3):
+        j = t & 1
+        if t >= 5:
+            evs[j].synchronize()
+            acc += float(h_rew2[j][0, 0])
+        obs, act, rew, nxt, nd = buf.sample_drq(pad=PAD, idxs=n_idx[t], offsets={"obs": n_off[t, 0], "next_obs": n_off[t, 1]})
+        h_rew2[j].copy_(rew, non_blocking=True)
+        evs[j].record(stream)
+    torch.cuda.synchronize(dev)
+    el_p = shard.max_over_ranks(time.perf_counter() - t0, device=dev)
+    e2e = {"value": world * Ke * B / el, "unit": UNIT, "h2d_bytes_per_step": B * 4 + 2 * B * 2,
            "d2h_bytes_per_step": B * 4, "steps": Ke, "ms_per_step": 1e3 * el / Ke,
-           "api": "ReplayBuffer.sample_drq(idxs=host, offsets=host) + D2H of rewards + stream sync per step; "
-                  "host draws travel by value in the kernel launch (augcl_ring_sample_ex, HOST)"}
+           "api": "ReplayBuffer.sample_drq(idxs=host numpy, offsets=host numpy) + D2H of the step's rewards + stream "
+                  "synchronize EVERY step; the host draws travel by value in the kernel launch's parameter block "
+                  "(augcl_ring_sample_ex HOST: int32 index + 2x2 int8 offsets per sample), so H2D is the launch itself",
+           "pipelined_value": world * Ke * B / el_p, "pipelined_ms_per_step": 1e3 * el_p / Ke,
+           "pipelined_note": "same call and copies, each step's rewards read one step late (2 pinned slots + events)"}
     return dict(buf=buf, dev=dev, world=world, rank=rank, ms=ms, value=value, launches=launches, clocks=clocks, e2e=e2e,
                 step_raw=fn, K=K, W=W, B=B)
 
@@ -355,7 +368,7 @@ def main():
             "ms_per_step": res["ms"] / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u8->f32", "data": "synthetic", "config": config_dict(args, world),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic, "kernel": "ring_sample_tma_kernel<21>", "peak_source": peak_src,
+                         "traffic": traffic, "kernel": "ring_sample_band_kernel<84,84,84,84,0>", "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": B * BYTES_PER_SAMPLE,
                          "note": "per-launch time = timed region / steps (one launch per step, CUDA events on the launching stream)"},
             "clocks": res["clocks"], "e2e": res["e2e"], "gpu_launches": res["launches"],
