@@ -19,6 +19,7 @@ import torch
 
 from . import _lib as L
 from . import augmentations
+from . import persist
 
 
 try:                                    # raw cudaStream_t of torch's current stream without building a Stream object
@@ -90,6 +91,7 @@ class ReplayBuffer(object):
         if c % frame_channels:
             raise ValueError(f"obs channels {c} not a multiple of frame_channels {frame_channels}")
         self.obs_shape = (int(c), int(h), int(w))
+        self._frame_channels = int(frame_channels)
         self.action_dim = int(np.prod(action_shape)) if len(action_shape) else 1
         self.actions = np.empty((self.capacity, *action_shape), dtype=np.float32)
         self.rewards = np.empty((self.capacity, 1), dtype=np.float32)
@@ -310,6 +312,89 @@ class ReplayBuffer(object):
         obs is shifted, next_obs is returned un-augmented.  offsets: optional (B,2) draws for obs."""
         return self._sample(idxs, n=n, aug=L.AUG_SHIFT_OBS, off_obs=offsets, pad_or_size=pad,
                             device_indices=device_indices)
+
+    # ------------------------------------------------------------------ persistence (reference chunk format)
+    IO_BLOCK = 2048   # transitions moved between the ring and pinned host memory per copy
+
+    def _drain(self, start, end):
+        """Ring slots [start, end) -> (obs, next) uint8 host arrays, in IO_BLOCK pieces."""
+        c, h, w = self.obs_shape
+        n = end - start
+        obs = np.empty((n, c, h, w), dtype=np.uint8)
+        nxt = np.empty((n, c, h, w), dtype=np.uint8)
+        blk = min(self.IO_BLOCK, max(n, 1))
+        po = torch.empty((blk, c, h, w), dtype=torch.uint8).pin_memory()
+        pn = torch.empty((blk, c, h, w), dtype=torch.uint8).pin_memory()
+        stream = torch.cuda.current_stream(self.device)
+        for s0 in range(0, n, blk):
+            m = min(blk, n - s0)
+            L.call("augcl_ring_get", self._ring, start + s0, m, po.data_ptr(), pn.data_ptr(), None, None, None,
+                   self._stream())
+            stream.synchronize()
+            obs[s0:s0 + m] = po.numpy()[:m]
+            nxt[s0:s0 + m] = pn.numpy()[:m]
+        return obs, nxt
+
+    def __save__(self, save_dir, last_save_idx):
+        """src/utils.py:156-167: chunk "<last>_<idx>.tar" with the transitions added since the last save."""
+        if self.idx == last_save_idx:
+            return self.idx
+        self._flush()
+        end = max(self.idx, last_save_idx)   # the reference slices [last:idx]: empty once the ring has wrapped
+        obs, nxt = self._drain(last_save_idx, end)
+        pairs = persist.encode_obses(obs, nxt, self._frame_channels, LazyFrames)
+        path = os.path.join(save_dir, persist.chunk_name(last_save_idx, self.idx))
+        persist.save_chunk(path, pairs, self.actions[last_save_idx:self.idx], self.rewards[last_save_idx:self.idx],
+                           self.not_dones[last_save_idx:self.idx])
+        return self.idx
+
+    def save(self, save_dir):
+        """src/utils.py:169-170."""
+        self.last_save = self.__save__(save_dir=save_dir, last_save_idx=self.last_save)
+
+    def requeue_save(self, save_dir):
+        """src/utils.py:172-175."""
+        self.last_requeue_save = self.__save__(save_dir=save_dir, last_save_idx=self.last_requeue_save)
+
+    def load(self, save_dir, end_step=None, is_requeue_load=True, is_load=True):
+        """src/utils.py:177-204: replay the chunks of save_dir, in order, into the ring."""
+        if self.refilled:
+            return
+        self._flush()
+        c, h, w = self.obs_shape
+        chunks = persist.list_chunks(save_dir)
+        stream = torch.cuda.current_stream(self.device)
+        for chunk in chunks:
+            start, end = persist.parse_chunk_name(chunk)
+            payload = persist.load_chunk(os.path.join(save_dir, chunk), LazyFrames)
+            assert self.idx == start, \
+                f"self.idx: {self.idx} DNE start: {start} for save_dir: {save_dir}. Current chunk is {chunk}. Chucks: {chunks}."
+            pairs = payload[0]
+            n = len(pairs)
+            if start + n > self.capacity:
+                raise ValueError(f"chunk {chunk} holds {n} transitions from slot {start}: beyond capacity {self.capacity}")
+            self.actions[start:end] = payload[1]
+            self.rewards[start:end] = payload[2]
+            self.not_dones[start:end] = payload[3]
+            blk = min(self.IO_BLOCK, max(n, 1))
+            po = torch.empty((blk, c, h, w), dtype=torch.uint8).pin_memory()
+            pn = torch.empty((blk, c, h, w), dtype=torch.uint8).pin_memory()
+            for s0 in range(0, n, blk):
+                m = min(blk, n - s0)
+                persist.decode_obses(pairs[s0:s0 + m], po.numpy(), pn.numpy())
+                a = np.ascontiguousarray(self.actions[start + s0:start + s0 + m], dtype=np.float32).reshape(m, -1)
+                r = np.ascontiguousarray(self.rewards[start + s0:start + s0 + m], dtype=np.float32)
+                d = np.ascontiguousarray(self.not_dones[start + s0:start + s0 + m], dtype=np.float32)
+                L.call("augcl_ring_put", self._ring, start + s0, m, po.data_ptr(), pn.data_ptr(), a.ctypes.data,
+                       r.ctypes.data, d.ctypes.data, self._stream())
+                stream.synchronize()       # the pinned staging is reused by the next block
+            self.idx = end
+            if end == end_step:
+                break
+        if is_requeue_load:
+            self.last_requeue_save = self.idx
+        if is_load:
+            self.last_save = self.idx
 
     def fill_synthetic(self, count=None, seed=0):
         """Benchmarks/tests: fill slots [0,count) with Philox frames and scalars on the device."""

@@ -119,6 +119,45 @@ def replay_case(name, seed, cap, k, S, A, n_add, B):
     print(name, os.path.getsize(path))
 
 
+def chunk_case(name, seed, cap, k, S, A, saves, B):
+    """Reference ReplayBuffer: add transitions (two episodes: reset repeats the first frame k times,
+    src/env/wrappers.py:193-197), save() at the steps in `saves` -> chunk files written BY THE REFERENCE,
+    then sample(idxs) from a fresh reference buffer that load()ed them."""
+    import shutil
+    rng = np.random.RandomState(seed)
+    n_add = saves[-1]
+    out_dir = os.path.join(OUT, name)
+    shutil.rmtree(out_dir, ignore_errors=True)
+    os.makedirs(out_dir)
+    buf = R.ref_replay_buffer((3 * k, S, S), (A,), cap, B)
+    raw = rng.randint(0, 256, (n_add + 2, 3, S, S)).astype(np.uint8)
+    actions = rng.randn(n_add, A).astype(np.float32)
+    rewards = rng.randn(n_add).astype(np.float32)
+    ep_len = n_add // 2 + 1
+    window, dones = None, []
+    for t in range(n_add):
+        if t % ep_len == 0:
+            window = [raw[t]] * k                      # reset: first frame k times (same ndarray object)
+        obs = R.ref_lazy_frames(list(window))
+        window = window[1:] + [raw[t + 1]]
+        nxt = R.ref_lazy_frames(list(window))
+        done = (t + 1) % ep_len == 0
+        dones.append(done)
+        buf.add(obs, actions[t], rewards[t], nxt, done)
+        if t + 1 in saves:
+            R.ref_buffer_save(buf, out_dir)
+    fresh = R.ref_replay_buffer((3 * k, S, S), (A,), cap, B)
+    R.ref_buffer_load(fresh, out_dir)
+    assert fresh.idx == n_add and fresh.last_save == n_add
+    idxs = rng.randint(0, n_add, size=B)
+    obs, act, rew, nobs, nd = R.ref_sample(fresh, idxs)
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), idxs=idxs.astype(np.int64), cap=np.int32(cap), k=np.int32(k),
+                        S=np.int32(S), A=np.int32(A), n_add=np.int32(n_add),
+                        out_obs=obs.numpy().astype(np.uint8), out_next=nobs.numpy().astype(np.uint8),
+                        out_act=act.numpy(), out_rew=rew.numpy(), out_nd=nd.numpy())
+    print(name, sorted(os.listdir(out_dir)), [os.path.getsize(os.path.join(out_dir, f)) for f in sorted(os.listdir(out_dir))])
+
+
 if __name__ == "__main__":
     assert R.available(), "needs /root/reference"
     os.makedirs(OUT, exist_ok=True)
@@ -128,3 +167,4 @@ if __name__ == "__main__":
     case("aug_odd", seed=4, n=4, c=9, h=13, w=11, pad=4, crop_from=(17, 10))   # widths not multiple of 4
     replay_case("replay_small", seed=5, cap=24, k=3, S=16, A=6, n_add=37, B=10)
     replay_case("replay_84", seed=6, cap=16, k=3, S=84, A=6, n_add=12, B=4)
+    chunk_case("chunks_ref", seed=7, cap=40, k=3, S=12, A=4, saves=[10, 25], B=9)

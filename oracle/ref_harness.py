@@ -248,3 +248,39 @@ def ref_sample(buf, idxs):
     """src/utils.py:272-280 with explicit idxs, run on CPU."""
     with cpu_shims():
         return buf.sample(idxs=np.asarray(idxs))
+
+
+# -------------------------- persistence (src/utils.py:156-204) --------------------------
+
+@contextlib.contextmanager
+def _as_utils_module():
+    """Pickle resolves ``utils.LazyFrames`` through sys.modules; the reference's module is kept out of it
+    (load_reference), so install it under its own name for the duration of a save / load.  torch >= 2.6
+    defaults torch.load to weights_only=True, which the reference's torch 1.7.1 did not have: restore the
+    old default for the call (third shim of the same kind as numpy's copy=False)."""
+    import functools
+    _, ref_utils = load_reference()
+    saved = sys.modules.get("utils")
+    sys.modules["utils"] = ref_utils
+    orig_load = ref_utils.torch.load
+    ref_utils.torch.load = functools.partial(orig_load, weights_only=False)
+    try:
+        yield ref_utils
+    finally:
+        ref_utils.torch.load = orig_load
+        if saved is None:
+            sys.modules.pop("utils", None)
+        else:
+            sys.modules["utils"] = saved
+
+
+def ref_buffer_save(buf, save_dir):
+    """ReplayBuffer.save (src/utils.py:169-170) of a reference buffer."""
+    with _as_utils_module():
+        buf.save(save_dir)
+
+
+def ref_buffer_load(buf, save_dir, **kw):
+    """ReplayBuffer.load (src/utils.py:177-204) into a reference buffer."""
+    with _as_utils_module(), cpu_shims():
+        buf.load(save_dir, **kw)
