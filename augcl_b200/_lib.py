@@ -40,6 +40,10 @@ SIGNATURES = {
     "augcl_random_conv": (_i, [_p, _p, _i, _i, _i, _i, _p, _p]),
     "augcl_random_overlay": (_i, [_p, _p, _i, _i, _i, _i, _p, _i, _i64, _p, _f, _p]),
     "augcl_splice": (_i, [_p, _p, _i, _i, _i, _i, _p, _i, _i64, _p, _f, _f, _f, _i, _p]),
+    "augcl_random_grayscale": (_i, [_p, _p, _i, _i, _i, _i, _p, _p]),
+    "augcl_random_flip": (_i, [_p, _p, _i, _i, _i, _i, _p, _p]),
+    "augcl_random_rotation": (_i, [_p, _p, _i, _i, _i, _i, _p, _p]),
+    "augcl_random_cutout_color": (_i, [_p, _p, _i, _i, _i, _i, _p, _p, _p]),
     "augcl_rng_fill_offsets": (_i, [_p, _i64, C.c_int32, C.c_int32, _u64, _u64, _p]),
     "augcl_rng_fill_indices": (_i, [_p, _i64, _i64, _i64, _u64, _u64, _p]),
     "augcl_rng_fill_normal": (_i, [_p, _i64, _u64, _u64, _p]),

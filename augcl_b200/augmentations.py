@@ -21,11 +21,13 @@ from __future__ import annotations
 
 import ctypes as C
 
+import numpy as np
 import torch
 
 from . import _lib as L
 
 __all__ = ["random_shift", "random_crop", "random_conv", "random_overlay", "splice", "CS_splice",
+           "random_grayscale", "random_flip", "random_rotation", "random_cutout_color",
            "identity", "aug_to_func", "seed", "set_background_bank", "load_dataloader"]
 
 # --------------------------------------------------------------------------------------------
@@ -273,6 +275,77 @@ def CS_splice(x, hue_thres=3.5, sat_thres=0, val_thres=0, *, bank_idx=None, data
     return _splice(x, (hue_thres, sat_thres, val_thres), L.CS_SPLICE, "CS_splice", bank_idx, dataset)
 
 
+# --------------------------------------------------------------------------------------------
+# the remaining aug_to_func entries (src/augmentations.py:111-213, 327-350).  Their per-sample decisions are
+# drawn with numpy's global RNG in the reference's own order, so a seeded run makes the same decisions;
+# every draw can also be supplied.
+# --------------------------------------------------------------------------------------------
+def _dev(a, dtype, device):
+    return torch.as_tensor(np.ascontiguousarray(a)).to(device=device, dtype=dtype).contiguous()
+
+
+def random_grayscale(images, p=0.3, *, mask=None):
+    """src/augmentations.py:111-136.  mask: optional (n,) bools = the reference's ``rnd <= p``."""
+    x = _prep(images, "random_grayscale")
+    n, c, h, w = x.shape
+    if mask is None:
+        mask = np.random.uniform(0.0, 1.0, size=(n,)) <= p
+    with torch.cuda.device(x.device):
+        m = _dev(np.asarray(mask).astype(np.uint8), torch.uint8, x.device)
+        out = torch.empty_like(x)
+        L.call("augcl_random_grayscale", x.data_ptr(), out.data_ptr(), n, c, h, w, m.data_ptr(), _stream(x))
+    return out
+
+
+def random_flip(images, p=0.2, *, mask=None):
+    """src/augmentations.py:139-168."""
+    x = _prep(images, "random_flip")
+    n, c, h, w = x.shape
+    if mask is None:
+        mask = np.random.uniform(0.0, 1.0, size=(n,)) <= p
+    with torch.cuda.device(x.device):
+        m = _dev(np.asarray(mask).astype(np.int32), torch.int32, x.device)
+        out = torch.empty_like(x)
+        L.call("augcl_random_flip", x.data_ptr(), out.data_ptr(), n, c, h, w, m.data_ptr(), _stream(x))
+    return out
+
+
+def random_rotation(images, p=0.3, *, rot=None):
+    """src/augmentations.py:171-213.  rot: optional (n,) quarter turns in {0,1,2,3}."""
+    x = _prep(images, "random_rotation")
+    n, c, h, w = x.shape
+    if rot is None:
+        rnd = np.random.uniform(0.0, 1.0, size=(n,))
+        rnd_rot = np.random.randint(1, 4, size=(n,))
+        rot = rnd_rot * (rnd <= p)
+    with torch.cuda.device(x.device):
+        r = _dev(np.asarray(rot).astype(np.int32), torch.int32, x.device)
+        out = torch.empty_like(x)
+        L.call("augcl_random_rotation", x.data_ptr(), out.data_ptr(), n, c, h, w, r.data_ptr(), _stream(x))
+    return out
+
+
+def random_cutout_color(imgs, min_cut=10, max_cut=30, *, w1=None, h1=None, colors=None):
+    """src/augmentations.py:327-350 (the reference round-trips through numpy and returns a CPU tensor; this
+    stays on the device).  colors: optional (n,c) floats = the reference's randint(0,255)/255.0."""
+    x = _prep(imgs, "random_cutout_color")
+    n, c, h, w = x.shape
+    if w1 is None:
+        w1 = np.random.randint(min_cut, max_cut, n)
+    if h1 is None:
+        h1 = np.random.randint(min_cut, max_cut, n)
+    if colors is None:
+        colors = np.random.randint(0, 255, size=(n, c)) / 255.0
+    box = np.stack([np.asarray(w1).reshape(n), np.asarray(h1).reshape(n)], axis=1).astype(np.int32)
+    with torch.cuda.device(x.device):
+        b = _dev(box, torch.int32, x.device)
+        col = _dev(np.asarray(colors, dtype=np.float64).reshape(n, c), torch.float32, x.device)
+        out = torch.empty_like(x)
+        L.call("augcl_random_cutout_color", x.data_ptr(), out.data_ptr(), n, c, h, w, b.data_ptr(), col.data_ptr(),
+               _stream(x))
+    return out
+
+
 def _not_native(name):
     def fn(*a, **k):
         raise NotImplementedError(
@@ -284,16 +357,16 @@ def _not_native(name):
 
 # same 12 keys as src/augmentations.py:436-449
 aug_to_func = {
-    "grayscale": _not_native("random_grayscale"),
-    "flip": _not_native("random_flip"),
-    "rotate": _not_native("random_rotation"),
+    "grayscale": random_grayscale,
+    "flip": random_flip,
+    "rotate": random_rotation,
     "conv": random_conv,
     "shift": random_shift,
     "color_jitter": _not_native("color_jitter"),
     "identity": identity,
     "splice": splice,
     "crop": random_crop,
-    "cutout_color": _not_native("random_cutout_color"),
+    "cutout_color": random_cutout_color,
     "CS_splice": CS_splice,
     "overlay": random_overlay,
 }

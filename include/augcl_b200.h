@@ -180,6 +180,30 @@ int augcl_splice(const float* in, float* out, int n, int c, int h, int w, const 
                  float sat_thres, float val_thres, int variant, augcl_stream stream);
 
 /* ------------------------------------------------------------------------------------------
+ * The remaining aug_to_func entries (src/augmentations.py:436-449).  Inherited from RAD, where images are
+ * in [0,1]; the reference applies them to its 0..255 tensors unchanged and so do these.
+ * ------------------------------------------------------------------------------------------ */
+
+/* random_grayscale (src/augmentations.py:111-136, grayscale :88-108): every pixel becomes
+ * trunc_u8(x*255)/255 (torch's CPU float->uint8 cast: truncate, low 8 bits); samples with mask[i] != 0
+ * additionally replace the three channels of each frame by trunc_u8(0.2989 r + 0.587 g + 0.114 b).
+ * mask: device uint8[n] (the reference's np.random.uniform(size=n) <= p). */
+int augcl_random_grayscale(const float* in, float* out, int n, int c, int h, int w, const uint8_t* mask,
+                           augcl_stream stream);
+/* random_flip (src/augmentations.py:139-168): horizontal flip of the samples with flip[i] != 0; device int32[n]. */
+int augcl_random_flip(const float* in, float* out, int n, int c, int h, int w, const int32_t* flip,
+                      augcl_stream stream);
+/* random_rotation (src/augmentations.py:171-213): torch.rot90(x, quarter_turns[i], [2,3]) per sample,
+ * quarter_turns device int32[n] in {0,1,2,3} (= rnd_rot * (rnd <= p)); requires h == w. */
+int augcl_random_rotation(const float* in, float* out, int n, int c, int h, int w, const int32_t* quarter_turns,
+                          augcl_stream stream);
+/* random_cutout_color (src/augmentations.py:327-350): box[i] = (w1, h1) device int32[n,2]; rows h1..2*h1-1 and
+ * cols w1..2*w1-1 (start == size: the reference's slicing) of channel ch become colors[i*c + ch] (device f32[n,c],
+ * the reference's randint(0,255)/255.0). */
+int augcl_random_cutout_color(const float* in, float* out, int n, int c, int h, int w, const int32_t* box,
+                              const float* colors, augcl_stream stream);
+
+/* ------------------------------------------------------------------------------------------
  * Device RNG (Philox4x32-10, counter = (block_lo, block_hi, subseq_lo, subseq_hi), key = seed).
  * Stand in for the reference's host draws: np.random.randint (src/utils.py:232),
  * LongTensor.random_ (src/augmentations.py:404-405), kornia's crop parameters (:382),

@@ -283,3 +283,45 @@ def rng_normal(count: int, seed: int, subsequence: int) -> np.ndarray:
     out[0::2] = r * np.cos(2 * math.pi * u2)
     out[1::2] = r * np.sin(2 * math.pi * u2)
     return out[:count].astype(np.float32)
+
+
+# ----------------------------------------------------------------------------
+# The remaining aug_to_func entries.  Draws are explicit arguments.
+# NOTE these reference functions were inherited from RAD, where images are in [0,1]; the
+# reference applies them to 0..255 tensors as they are (e.g. grayscale's x*255 -> uint8 wraps
+# modulo 256 on the CPU).  The restatements follow the reference's arithmetic literally.
+# ----------------------------------------------------------------------------
+def random_grayscale(x: torch.Tensor, mask) -> torch.Tensor:
+    """src/augmentations.py:88-136.  mask (n,) bool = (np.random.uniform <= p)."""
+    n, c, h, w = x.shape
+    k = c // 3
+    u8 = ((x * 255.0).to(torch.int64) % 256).to(torch.uint8)          # .type(torch.uint8): truncation, wraps mod 256
+    v = u8.view(n, k, 3, h, w)
+    gray = v[:, :, 0] * 0.2989 + v[:, :, 1] * 0.587 + v[:, :, 2] * 0.114
+    gray = gray.type(torch.uint8).float()[:, :, None].expand(n, k, 3, h, w)
+    m = torch.as_tensor(np.asarray(mask)).bool().view(n, 1, 1, 1, 1)
+    out = torch.where(m, gray, v.float())
+    return out.reshape(n, c, h, w) / 255.0
+
+
+def random_flip(x: torch.Tensor, mask) -> torch.Tensor:
+    """src/augmentations.py:139-168.  Horizontal flip of the samples where mask is set."""
+    m = torch.as_tensor(np.asarray(mask)).bool().view(-1, 1, 1, 1)
+    return torch.where(m, x.flip([3]), x)
+
+
+def random_rotation(x: torch.Tensor, rot) -> torch.Tensor:
+    """src/augmentations.py:171-213.  rot (n,) in {0,1,2,3} = rnd_rot * (rnd <= p): quarter turns."""
+    rot = np.asarray(rot)
+    return torch.stack([torch.rot90(x[i], int(rot[i]), [1, 2]) for i in range(x.shape[0])])
+
+
+def random_cutout_color(x: torch.Tensor, w1, h1, colors) -> torch.Tensor:
+    """src/augmentations.py:327-350.  Box rows h1:2*h1, cols w1:2*w1 (start == size, a reference quirk)
+    filled per channel with colors (n,c) = randint(0,255)/255.0 (float64, cast to the image dtype)."""
+    out = x.clone()
+    w1, h1 = np.asarray(w1), np.asarray(h1)
+    col = torch.as_tensor(np.asarray(colors, dtype=np.float64)).to(x.dtype)
+    for i in range(x.shape[0]):
+        out[i, :, h1[i]:2 * h1[i], w1[i]:2 * w1[i]] = col[i].view(-1, 1, 1)
+    return out

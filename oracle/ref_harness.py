@@ -284,3 +284,57 @@ def ref_buffer_load(buf, save_dir, **kw):
     """ReplayBuffer.load (src/utils.py:177-204) into a reference buffer."""
     with _as_utils_module(), cpu_shims():
         buf.load(save_dir, **kw)
+
+
+# -------------------------- remaining aug_to_func entries --------------------------
+
+@contextlib.contextmanager
+def _np_random(aug, uniform=None, randint=None):
+    """Replace the np.random draws inside the reference module with queued arrays."""
+    class _R:
+        def __init__(self):
+            self.u, self.r = list(uniform or []), list(randint or [])
+        def uniform(self, *a, **k):
+            return np.asarray(self.u.pop(0), dtype=np.float64)
+        def randint(self, *a, **k):
+            return np.asarray(self.r.pop(0))
+    orig = aug.np
+    shim = types.SimpleNamespace(**{k: getattr(orig, k) for k in dir(orig) if not k.startswith("__")})
+    shim.random = _R()
+    aug.np = shim
+    try:
+        yield
+    finally:
+        aug.np = orig
+
+
+def ref_random_grayscale(x, mask, p=0.3):
+    """src/augmentations.py:111-136 with rnd := 0 where mask else 1."""
+    aug, _ = load_reference()
+    u = np.where(np.asarray(mask), 0.0, 1.0)
+    with cpu_shims(), _np_random(aug, uniform=[u]):
+        return aug.random_grayscale(x.clone(), p)
+
+
+def ref_random_flip(x, mask, p=0.2):
+    aug, _ = load_reference()
+    u = np.where(np.asarray(mask), 0.0, 1.0)
+    with cpu_shims(), _np_random(aug, uniform=[u]):
+        return aug.random_flip(x.clone(), p)
+
+
+def ref_random_rotation(x, rot, p=0.3):
+    """rot (n,) in {0..3}: 0 = not rotated (rnd > p), else rnd_rot."""
+    aug, _ = load_reference()
+    rot = np.asarray(rot)
+    u = np.where(rot > 0, 0.0, 1.0)
+    rr = np.where(rot > 0, rot, 1)
+    with cpu_shims(), _np_random(aug, uniform=[u], randint=[rr]):
+        return aug.random_rotation(x.clone(), p)
+
+
+def ref_random_cutout_color(x, w1, h1, color_ints):
+    """color_ints (n,c) = the reference's randint(0,255) draw (it divides by 255.0 itself)."""
+    aug, _ = load_reference()
+    with cpu_shims(), _np_random(aug, randint=[np.asarray(w1), np.asarray(h1), np.asarray(color_ints)]):
+        return aug.random_cutout_color(x.clone())

@@ -57,3 +57,20 @@ def test_live_replay_gather():
     idxs = rng.randint(0, cap, size=7)
     for a, b in zip(R.ref_sample(ref, idxs), ora.sample(idxs)):
         assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize("unit_range", [False, True])
+def test_live_remaining_augs(unit_range):
+    """grayscale / flip / rotate / cutout_color: oracle restatement == the reference's functions with the
+    np.random draws injected."""
+    g = torch.Generator().manual_seed(3)
+    rng = np.random.RandomState(3)
+    n = 7
+    x = torch.rand(n, 9, 24, 24, generator=g) * (1.0 if unit_range else 255.0)
+    mask = rng.rand(n) < 0.5
+    assert torch.equal(R.ref_random_grayscale(x, mask), O.random_grayscale(x, mask))
+    assert torch.equal(R.ref_random_flip(x, mask), O.random_flip(x, mask))
+    rot = rng.randint(0, 4, n)
+    assert torch.equal(R.ref_random_rotation(x, rot), O.random_rotation(x, rot))
+    w1, h1, ci = rng.randint(1, 15, n), rng.randint(1, 15, n), rng.randint(0, 255, (n, 9))
+    assert torch.equal(R.ref_random_cutout_color(x, w1, h1, ci), O.random_cutout_color(x, w1, h1, ci / 255.0))
