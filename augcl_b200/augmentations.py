@@ -346,13 +346,21 @@ def random_cutout_color(imgs, min_cut=10, max_cut=30, *, w1=None, h1=None, color
     return out
 
 
-def _not_native(name):
-    def fn(*a, **k):
-        raise NotImplementedError(
-            f"augcl_b200: '{name}' is outside the replay-gather + augmentation hot path (SURVEY.md §8f-3) "
-            "and has no native kernel yet")
-    fn.__name__ = name
-    return fn
+def color_jitter(imgs, p=1):
+    """src/augmentations.py:225-237: torchvision ``ColorJitter(0, (0,2), (0,3), (-0.5,0.5))`` on a random subset of
+    the frames, IN PLACE like the reference.  Not a hand-written kernel: no reference algorithm or launch script
+    uses this entry (grep of scripts/, COMMANDS.md) and on 0..255 inputs torchvision clamps the result to [0,1];
+    it runs the reference's own torchvision op sequence on the device so ``--data_aug`` chains keep working."""
+    import torchvision.transforms as TF
+    if not (isinstance(imgs, torch.Tensor) and imgs.is_cuda):
+        raise AssertionError("color_jitter: input must be a CUDA tensor (augcl_b200 has no CPU path)")
+    b, c, h, w = imgs.shape
+    num_samples = int(p * b * int(c / 3))
+    sampled_idxs = torch.from_numpy(np.random.randint(0, b, num_samples))
+    flat = imgs.view(-1, 3, h, w)
+    model = TF.ColorJitter(0, (0, 2), (0, 3), (-0.5, 0.5))
+    flat[sampled_idxs] = model(flat[sampled_idxs])
+    return flat.view(b, c, h, w)
 
 
 # same 12 keys as src/augmentations.py:436-449
@@ -362,7 +370,7 @@ aug_to_func = {
     "rotate": random_rotation,
     "conv": random_conv,
     "shift": random_shift,
-    "color_jitter": _not_native("color_jitter"),
+    "color_jitter": color_jitter,
     "identity": identity,
     "splice": splice,
     "crop": random_crop,
