@@ -17,8 +17,26 @@ SHIFT_INT, SHIFT_BILINEAR = 0, 1
 BANK_U8, BANK_F32 = 0, 1
 SPLICE, CS_SPLICE = 0, 1
 SRC_DEVICE, SRC_HOST, SRC_PHILOX = 0, 1, 2
+OP_SPLICE, OP_CS_SPLICE, OP_OVERLAY, OP_CONV = 1, 2, 4, 8
+AUG_INPUT_PLAIN, AUG_INPUT_SHIFTED = 0, 1
 
 _p, _i, _i64, _u64, _f = C.c_void_p, C.c_int, C.c_int64, C.c_uint64, C.c_float
+
+
+
+class FusedDesc(C.Structure):
+    """augcl_fused_desc of include/augcl_b200.h (field for field)."""
+    _fields_ = [
+        ("struct_size", C.c_int32), ("B", C.c_int32), ("idx_src", C.c_int32), ("off_src", C.c_int32),
+        ("idx", _p), ("idx_hi", _i64), ("off_obs", _p), ("off_next", _p),
+        ("pad", C.c_int32), ("normalize", C.c_int32), ("seed", _u64), ("subsequence", _u64),
+        ("out_obs", _p), ("out_obs_shift", _p), ("out_obs_aug", _p), ("out_next", _p), ("out_next_shift", _p),
+        ("out_act", _p), ("out_rew", _p), ("out_nd", _p),
+        ("aug_input", C.c_int32), ("aug_ops", C.c_int32),
+        ("bank", _p), ("bank_len", _i64), ("bank_idx", _p), ("conv_weights", _p),
+        ("hue_thres", _f), ("sat_thres", _f), ("val_thres", _f), ("alpha", _f),
+    ]
+
 
 # name -> (restype, argtypes); every symbol include/augcl_b200.h declares
 SIGNATURES = {
@@ -34,6 +52,7 @@ SIGNATURES = {
     "augcl_ring_fill_synthetic": (_i, [_p, _i64, _u64, _p]),
     "augcl_ring_sample": (_i, [_p, _p, _i, _p, _p, _p, _p, _p, _i, _p, _p, _i, _i, _p]),
     "augcl_ring_sample_ex": (_i, [_p, _i, _p, _i64, _i, _p, _p, _p, _p, _p, _i, _i, _p, _p, _i, _i, _u64, _u64, _p]),
+    "augcl_ring_sample_fused": (_i, [_p, C.POINTER(FusedDesc), _p]),
     "augcl_random_shift": (_i, [_p, _p, _i, _i, _i, _i, _i, _p, _i, _p, _p]),
     "augcl_drq_base_grid": (_i, [_i, _i, C.POINTER(_f)]),
     "augcl_random_crop": (_i, [_p, _p, _i, _i, _i, _i, _i, _p, _p]),

@@ -10,8 +10,8 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
-SRC = [os.path.join(HERE, "csrc", f) for f in ("state.cu", "ring.cu", "augment.cu", "augment2.cu", "rng.cu")]
-HDRS = [os.path.join(HERE, "csrc", "common.cuh"), os.path.join(ROOT, "include", "augcl_b200.h")]
+SRC = [os.path.join(HERE, "csrc", f) for f in ("state.cu", "ring.cu", "fused.cu", "augment.cu", "augment2.cu", "rng.cu")]
+HDRS = [os.path.join(HERE, "csrc", h) for h in ("common.cuh", "ring.cuh", "pixel.cuh")] + [os.path.join(ROOT, "include", "augcl_b200.h")]
 LIB = os.path.join(HERE, "libaugcl_b200.so")
 
 NVCC_FLAGS = [

@@ -1,0 +1,503 @@
+// Fused per-algorithm sampler: gather + u8->f32 + random_shift + {splice | CS_splice | overlay} + random_conv
+// in ONE kernel, straight out of the device ring (include/augcl_b200.h: augcl_ring_sample_fused).
+//
+// Replaces, per update() of SVEA / AugCL (/root/reference/src/algorithms/svea.py:66-70, augcl.py:69-72), the chain
+//   ReplayBuffer.sample (src/utils.py:272-280) -> random_shift (src/augmentations.py:378-382)
+//   -> RAD.apply_aug (src/algorithms/rad.py:18-22) over splice / random_overlay / random_conv (:253-324)
+// which in the unfused form costs four kernels and 2.2 MB of HBM traffic per sample; fused, every u8 frame is read
+// once and only the final f32 tensors are written (952 560 B per sample for AugCL's splice-conv at 9x84x84).
+//
+// Work unit = a band of kFBand rows of one RGB frame (3 u8 planes) of one (tensor, sample).  The units of a launch
+// are laid out obs-first and split over the persistent CTAs by COST (an obs unit writes several tensors and may
+// convolve; a next_obs unit is a plain copy), contiguously, so a CTA walks consecutive bands of the same frame and
+// re-reads its halo rows out of L2.  Per unit, one lane starts <= 6 bulk copies (cp.async.bulk, SASS UBLKCP): the
+// hull of source rows of the 3 planes and, for splice / overlay, the matching rows of the 3 background planes;
+// they land in a 2-deep stage ring guarded by mbarriers while the CTA works on the previous unit.
+//   phase A (elementwise): thread = 4 pixels x 3 channels of one tile row.  Plain word = 1 LDS.32; shifted word =
+//     2 LDS.32 + funnel shift + PRMT replicate selector (as in ring_sample_band_kernel); HSV mask / overlay in
+//     registers; direct outputs are STG.128; the conv input goes to an f32 tile ([3][rows+2][W+8]) in shared memory.
+//   phase B (conv): the 2x4x3 register-blocked loop of random_conv_tma_kernel on that tile (weights / 255).
+#include "pixel.cuh"
+#include "ring.cuh"
+
+namespace augcl {
+
+std::atomic<int> g_fused_ctas_per_sm{6};
+std::atomic<int> g_fused_cost_obs{0};    // 0 = auto
+std::atomic<int> g_fused_cost_next{0};
+
+constexpr int kFBand = 12;
+constexpr int kFThreads = 128;
+
+struct FusedParams {
+  SampleParams sp;          // stores, draw sources, scalar gather (sp.out unused)
+  float* o_plain[2];        // [obs, next]
+  float* o_shift[2];
+  float* o_aug;
+  const uint8_t* bank;
+  const int64_t* bank_idx;
+  const float* weights;
+  int64_t bank_len;
+  SpliceThr thr;
+  float oma, alpha;
+  int ops;                  // AUGCL_OP_*
+  int aug_shifted;          // chain input: 0 plain, 1 shifted
+  int k, bands;             // frames per stack, bands per frame
+  int64_t units_obs, units_next;
+  int cost_obs, cost_next;
+  int plane_stage, bank_stage, stage_bytes, tile_rs;
+  int normalize;
+};
+
+struct FusedMeta {
+  float* o_plain;   // plane 0 of this frame in each output (nullptr = not written by this unit)
+  float* o_shift;
+  float* o_aug;
+  int koff;         // byte offset of source pixel (row 0, col 0) inside a plane's stage buffer (may be negative)
+  int gkoff;        // same for the background planes
+  int dy, dx;
+  int r0, rows;     // band
+  int sample;
+  int pad_;
+};
+
+__device__ __forceinline__ float fin(float v, int normalize) { return normalize ? __fdiv_rn(v, 255.0f) : v; }
+__device__ __forceinline__ float4 fin4(float4 v, int normalize) {
+  return make_float4(fin(v.x, normalize), fin(v.y, normalize), fin(v.z, normalize), fin(v.w, normalize));
+}
+
+__global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const __grid_constant__ FusedParams p) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem);                 // 2 mbarriers
+  FusedMeta* meta = reinterpret_cast<FusedMeta*>(smem + 16);          // 2 metas (2 x 56 B -> 128 B reserved)
+  float* wsm = reinterpret_cast<float*>(smem + 144);                  // [27][4] conv weights / 255
+  uint8_t* stage = smem + 144 + 432;                                  // 2 x stage_bytes (576 = 16 * 36: 16-B aligned)
+  float* tile = reinterpret_cast<float*>(stage + 2 * p.stage_bytes);  // [3][kFBand+2][tile_rs]
+  const int tid = threadIdx.x;
+  const int H = p.sp.H, W = p.sp.W, nq = W >> 2;
+  const bool conv = (p.ops & AUGCL_OP_CONV) != 0;
+  const bool splice = (p.ops & (AUGCL_OP_SPLICE | AUGCL_OP_CS_SPLICE)) != 0;
+  const bool overlay = (p.ops & AUGCL_OP_OVERLAY) != 0;
+  const bool use_bank = splice || overlay;
+  const int hal = conv ? 1 : 0;
+  const InlineDraws<0> none{};
+
+  // ---- static partition of the cost line [0, T) over the CTAs; a CTA owns the units whose start falls in its range
+  const int64_t T = p.units_obs * p.cost_obs + p.units_next * p.cost_next;
+  const int64_t c0 = T * blockIdx.x / gridDim.x, c1 = T * (blockIdx.x + 1) / gridDim.x;
+  auto first_unit_at = [&](int64_t c) -> int64_t {   // smallest unit whose start cost >= c
+    const int64_t To = p.units_obs * p.cost_obs;
+    if (c <= To) return p.cost_obs ? (c + p.cost_obs - 1) / p.cost_obs : 0;
+    return p.units_obs + (c - To + p.cost_next - 1) / p.cost_next;
+  };
+  const int64_t u0 = first_unit_at(c0), u1 = first_unit_at(c1);
+  const int nun = (int)(u1 - u0);
+
+  if (tid == 0) {
+    mbar_init(&bars[0], 1);
+    mbar_init(&bars[1], 1);
+    mbar_fence_init();
+  }
+  __syncthreads();
+  pdl_wait();
+
+  auto issue = [&](int kk, int s) {   // one lane: decode unit u0+kk, write its meta, start its copies into stage s
+    int64_t u = u0 + kk;
+    const int t = u >= p.units_obs ? 1 : 0;
+    if (t) u -= p.units_obs;
+    const int band = (int)(u % p.bands);
+    const int64_t fr = u / p.bands;            // frame row of x.reshape(B*k, 3, H, W)
+    const int f = (int)(fr % p.k), b = (int)(fr / p.k);
+    const int r0 = band * kFBand, rows = min(kFBand, H - r0);
+    const int64_t slot = sample_index(p.sp, none, b);
+    int dy, dx;
+    sample_offset(p.sp, none, t, b, dy, dx);
+    const bool want_aug = t == 0 && p.o_aug != nullptr;
+    const bool want_shift = p.o_shift[t] != nullptr;
+    const bool want_plain = p.o_plain[t] != nullptr;
+    // hull of the source rows this unit touches
+    int lo = H, hi = -1;
+    if (want_plain || (want_aug && !p.aug_shifted)) {
+      const int h2 = (want_aug && !p.aug_shifted) ? hal : 0;
+      lo = min(lo, max(r0 - h2, 0)); hi = max(hi, min(r0 + rows - 1 + h2, H - 1));
+    }
+    if (want_shift || (want_aug && p.aug_shifted)) {
+      const int h2 = (want_aug && p.aug_shifted) ? hal : 0;
+      const int a = clampi(max(r0 - h2, 0) + dy, 0, H - 1), z = clampi(min(r0 + rows - 1 + h2, H - 1) + dy, 0, H - 1);
+      lo = min(lo, a); hi = max(hi, z);
+    }
+    const int64_t P = (int64_t)H * W;
+    const size_t fo = (((size_t)b * p.sp.C + (size_t)f * 3) * H) * W;
+    FusedMeta m;
+    m.o_plain = want_plain ? p.o_plain[t] + fo : nullptr;
+    m.o_shift = want_shift ? p.o_shift[t] + fo : nullptr;
+    m.o_aug = want_aug ? p.o_aug + fo : nullptr;
+    m.dy = dy; m.dx = dx; m.r0 = r0; m.rows = rows; m.sample = b; m.pad_ = 0;
+    const uint8_t* src = p.sp.store[t] + (slot * p.sp.C + (int64_t)f * 3) * P;   // plane 0 of the frame
+    const uintptr_t a0 = reinterpret_cast<uintptr_t>(src + (int64_t)lo * W) & ~(uintptr_t)15;
+    const uintptr_t a1 = (reinterpret_cast<uintptr_t>(src + (int64_t)(hi + 1) * W) + 15) & ~(uintptr_t)15;
+    m.koff = (int)((intptr_t)reinterpret_cast<uintptr_t>(src) - (intptr_t)a0);
+    const uint32_t sbytes = (uint32_t)(a1 - a0);
+    uint32_t gbytes = 0;
+    uintptr_t g0 = 0;
+    m.gkoff = 0;
+    if (want_aug && use_bank) {
+      const int64_t j = splice ? ((int64_t)b * p.k + f) % p.sp.B : b;   // batch-tiled (splice) vs channel-tiled (overlay)
+      int64_t row = p.bank_idx[j];
+      row = row < 0 ? 0 : (row >= p.bank_len ? p.bank_len - 1 : row);
+      const uint8_t* g = p.bank + row * 3 * P;
+      const int glo = max(r0 - hal, 0), ghi = min(r0 + rows - 1 + hal, H - 1);
+      g0 = reinterpret_cast<uintptr_t>(g + (int64_t)glo * W) & ~(uintptr_t)15;
+      const uintptr_t g1 = (reinterpret_cast<uintptr_t>(g + (int64_t)(ghi + 1) * W) + 15) & ~(uintptr_t)15;
+      m.gkoff = (int)((intptr_t)reinterpret_cast<uintptr_t>(g) - (intptr_t)g0);
+      gbytes = (uint32_t)(g1 - g0);
+    }
+    meta[s] = m;
+    mbar_expect_tx(&bars[s], 3 * (sbytes + gbytes));   // P % 16 == 0: the three planes share lead and length
+    uint8_t* sb = stage + (size_t)s * p.stage_bytes;
+#pragma unroll
+    for (int ci = 0; ci < 3; ++ci)
+      bulk_g2s(sb + ci * p.plane_stage, reinterpret_cast<const void*>(a0 + (uintptr_t)(ci * P)), sbytes, &bars[s]);
+    if (gbytes) {
+      uint8_t* gb = sb + 3 * p.plane_stage;
+#pragma unroll
+      for (int ci = 0; ci < 3; ++ci)
+        bulk_g2s(gb + ci * p.bank_stage, reinterpret_cast<const void*>(g0 + (uintptr_t)(ci * P)), gbytes, &bars[s]);
+    }
+  };
+
+  if (tid < 2 && tid < nun) issue(tid, tid);
+  pdl_launch_dependents();
+  gather_scalars(p.sp, none);
+
+  uint32_t phase = 0;
+  for (int kk = 0; kk < nun; ++kk) {
+    const int s = kk & 1;
+    mbar_wait(&bars[s], phase);
+    const FusedMeta m = meta[s];
+    const uint8_t* sb = stage + (size_t)s * p.stage_bytes;
+    const uint8_t* gb = sb + 3 * p.plane_stage;
+    const bool do_conv = conv && m.o_aug != nullptr;
+    const int h2 = do_conv ? 1 : 0;
+    const int trows = m.rows + 2 * h2;
+    if (do_conv && tid < 81) {
+      // weights[sample][co][ci][ky][kx] / 255 -> wsm[(ci*9 + ky*3 + kx)*4 + co]
+      const int co = tid / 27, tap = tid - co * 27;
+      wsm[tap * 4 + co] = __fdiv_rn(p.weights[(int64_t)m.sample * 81 + tid], 255.0f);
+    }
+    const bool aug_sh = m.o_aug != nullptr && p.aug_shifted, aug_pl = m.o_aug != nullptr && !p.aug_shifted;
+    const bool need_bank = m.o_aug != nullptr && use_bank;
+    // ---------------- phase A: elementwise ----------------
+    for (int task = tid; task < trows * nq; task += kFThreads) {
+      const int pr = task / nq, q4 = task - pr * nq;
+      const int r = clampi(m.r0 + pr - h2, 0, H - 1);
+      const bool own = pr >= h2 && pr < h2 + m.rows;
+      uint32_t Pw[3] = {0, 0, 0}, Sw[3] = {0, 0, 0}, Gw[3] = {0, 0, 0};
+      // halo rows (not own) only feed the conv tile: they touch the source only through the chain's input
+      const bool need_plain = aug_pl || (own && m.o_plain != nullptr);
+      const bool need_shift = aug_sh || (own && m.o_shift != nullptr);
+      if (need_plain) {
+        const int a = m.koff + r * W + 4 * q4;
+#pragma unroll
+        for (int ci = 0; ci < 3; ++ci) Pw[ci] = *reinterpret_cast<const uint32_t*>(sb + ci * p.plane_stage + a);
+      }
+      if (need_shift) {
+        const int rr = clampi(r + m.dy, 0, H - 1);
+        const int cc = 4 * q4 + m.dx;
+        const int cs = clampi(cc, 0, W - 4);
+        const uint32_t sel = edge_selector(clampi(cc - cs, -4, 4));
+        const int a = m.koff + rr * W + cs;
+#pragma unroll
+        for (int ci = 0; ci < 3; ++ci) {
+          const uint32_t* wp = reinterpret_cast<const uint32_t*>(sb + ci * p.plane_stage + (a & ~3));
+          Sw[ci] = __byte_perm(__funnelshift_r(wp[0], wp[1], (uint32_t)a << 3), 0u, sel);
+        }
+      }
+      if (need_bank) {
+        const int a = m.gkoff + r * W + 4 * q4;
+#pragma unroll
+        for (int ci = 0; ci < 3; ++ci) Gw[ci] = *reinterpret_cast<const uint32_t*>(gb + ci * p.bank_stage + a);
+      }
+      const size_t oo = (size_t)r * W + 4 * q4;   // offset inside plane 0; planes are H*W apart
+      if (own) {
+        if (m.o_plain) {
+#pragma unroll
+          for (int ci = 0; ci < 3; ++ci)
+            st_global_f4(reinterpret_cast<float4*>(m.o_plain + oo + (size_t)ci * H * W), fin4(bytes_to_float4(Pw[ci]), p.normalize));
+        }
+        if (m.o_shift) {
+#pragma unroll
+          for (int ci = 0; ci < 3; ++ci)
+            st_global_f4(reinterpret_cast<float4*>(m.o_shift + oo + (size_t)ci * H * W), fin4(bytes_to_float4(Sw[ci]), p.normalize));
+        }
+      }
+      if (m.o_aug == nullptr) continue;
+      float v[3][4];
+      {
+        float a[3][4], g[3][4];
+#pragma unroll
+        for (int ci = 0; ci < 3; ++ci) {
+          const float4 t4 = bytes_to_float4(p.aug_shifted ? Sw[ci] : Pw[ci]);
+          a[ci][0] = t4.x; a[ci][1] = t4.y; a[ci][2] = t4.z; a[ci][3] = t4.w;
+          const float4 g4 = bytes_to_float4(Gw[ci]);
+          g[ci][0] = g4.x; g[ci][1] = g4.y; g[ci][2] = g4.z; g[ci][3] = g4.w;
+        }
+        if (splice) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float rn = div255(a[0][j]), gn = div255(a[1][j]), bn = div255(a[2][j]);
+            const bool keep = splice_keep(rn, gn, bn, p.thr);
+            v[0][j] = (keep ? rn : div255(g[0][j])) * 255.0f;
+            v[1][j] = (keep ? gn : div255(g[1][j])) * 255.0f;
+            v[2][j] = (keep ? bn : div255(g[2][j])) * 255.0f;
+          }
+        } else if (overlay) {
+#pragma unroll
+          for (int ci = 0; ci < 3; ++ci)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) v[ci][j] = overlay_px(a[ci][j], div255(g[ci][j]), p.oma, p.alpha);
+        } else {
+#pragma unroll
+          for (int ci = 0; ci < 3; ++ci)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) v[ci][j] = a[ci][j];
+        }
+      }
+      if (do_conv) {
+#pragma unroll
+        for (int ci = 0; ci < 3; ++ci) {
+          float* trow = tile + (ci * (kFBand + 2) + pr) * p.tile_rs;
+          *reinterpret_cast<float4*>(trow + 4 + 4 * q4) = make_float4(v[ci][0], v[ci][1], v[ci][2], v[ci][3]);
+          if (q4 == 0) trow[3] = v[ci][0];
+          if (q4 == nq - 1) trow[4 + W] = v[ci][3];
+        }
+      } else if (own) {
+#pragma unroll
+        for (int ci = 0; ci < 3; ++ci)
+          st_global_f4(reinterpret_cast<float4*>(m.o_aug + oo + (size_t)ci * H * W),
+                       fin4(make_float4(v[ci][0], v[ci][1], v[ci][2], v[ci][3]), p.normalize));
+      }
+    }
+    __syncthreads();   // stage s consumed (refill may start), tile + wsm complete
+    if (tid == 0 && kk + 2 < nun) issue(kk + 2, s);
+    // ---------------- phase B: conv on the tile ----------------
+    if (do_conv) {
+      const int ntask = ((m.rows + 1) >> 1) * nq;
+      for (int task = tid; task < ntask; task += kFThreads) {
+        const int rp = task / nq, q4 = task - rp * nq;
+        const int r = rp * 2;
+        float acc[2][3][4];
+#pragma unroll
+        for (int a = 0; a < 2; ++a)
+#pragma unroll
+          for (int co = 0; co < 3; ++co)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[a][co][j] = 0.0f;
+#pragma unroll 1
+        for (int ci = 0; ci < 3; ++ci) {
+          float x[4][6];
+#pragma unroll
+          for (int y = 0; y < 4; ++y) {
+            const float* trow = tile + (ci * (kFBand + 2) + r + y) * p.tile_rs + q4 * 4;
+            const float4 a = *reinterpret_cast<const float4*>(trow + 4);
+            x[y][0] = trow[3]; x[y][1] = a.x; x[y][2] = a.y; x[y][3] = a.z; x[y][4] = a.w; x[y][5] = trow[8];
+          }
+#pragma unroll
+          for (int ky = 0; ky < 3; ++ky) {
+#pragma unroll
+            for (int kx = 0; kx < 3; ++kx) {
+              const float4 wv = *reinterpret_cast<const float4*>(wsm + (ci * 9 + ky * 3 + kx) * 4);
+#pragma unroll
+              for (int a = 0; a < 2; ++a)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  acc[a][0][j] = fmaf(x[a + ky][j + kx], wv.x, acc[a][0][j]);
+                  acc[a][1][j] = fmaf(x[a + ky][j + kx], wv.y, acc[a][1][j]);
+                  acc[a][2][j] = fmaf(x[a + ky][j + kx], wv.z, acc[a][2][j]);
+                }
+            }
+          }
+        }
+#pragma unroll
+        for (int a = 0; a < 2; ++a) {
+          if (r + a >= m.rows) break;
+#pragma unroll
+          for (int co = 0; co < 3; ++co) {
+            float4* dst = reinterpret_cast<float4*>(m.o_aug + ((size_t)co * H + (m.r0 + r + a)) * W) + q4;
+            st_global_f4(dst, fin4(make_float4(sigmoid255(acc[a][co][0]), sigmoid255(acc[a][co][1]),
+                                               sigmoid255(acc[a][co][2]), sigmoid255(acc[a][co][3])), p.normalize));
+          }
+        }
+      }
+      __syncthreads();   // tile and wsm are free again
+    }
+    if (s == 1) phase ^= 1;
+  }
+}
+
+}  // namespace augcl
+
+using namespace augcl;
+
+extern "C" int augcl_ring_sample_fused(augcl_ring* r, const augcl_fused_desc* d, augcl_stream stream) {
+  const char* who = "augcl_ring_sample_fused";
+  AUGCL_REQUIRE(d, "%s: desc is NULL", who);
+  AUGCL_REQUIRE(d->struct_size == (int32_t)sizeof(augcl_fused_desc), "%s: desc.struct_size %d != %d (ABI mismatch)", who,
+                d->struct_size, (int)sizeof(augcl_fused_desc));
+  AUGCL_REQUIRE(r, "%s: ring is NULL", who);
+  const int B = d->B;
+  AUGCL_REQUIRE(B > 0, "%s: B must be positive (got %d)", who, B);
+  AUGCL_REQUIRE(d->idx_src == AUGCL_SRC_DEVICE || d->idx_src == AUGCL_SRC_HOST || d->idx_src == AUGCL_SRC_PHILOX,
+                "%s: unknown idx_src %d", who, d->idx_src);
+  AUGCL_REQUIRE(d->off_src == AUGCL_SRC_DEVICE || d->off_src == AUGCL_SRC_HOST || d->off_src == AUGCL_SRC_PHILOX,
+                "%s: unknown off_src %d", who, d->off_src);
+  if (d->idx_src == AUGCL_SRC_PHILOX)
+    AUGCL_REQUIRE(d->idx_hi > 0 && d->idx_hi <= r->capacity, "%s: idx_hi %lld outside (0, capacity]", who, (long long)d->idx_hi);
+  else
+    AUGCL_REQUIRE(d->idx, "%s: idx is NULL", who);
+  AUGCL_REQUIRE(d->pad >= 0 && d->pad <= 63, "%s: pad %d outside [0, 63]", who, d->pad);
+  const bool any_obs = d->out_obs || d->out_obs_shift || d->out_obs_aug;
+  const bool any_next = d->out_next || d->out_next_shift;
+  AUGCL_REQUIRE(any_obs || any_next, "%s: every image output is NULL", who);
+  const int ops = d->out_obs_aug ? d->aug_ops : 0;
+  if (d->out_obs_aug) {
+    AUGCL_REQUIRE(ops != 0 && (ops & ~15) == 0, "%s: out_obs_aug needs aug_ops out of AUGCL_OP_* (got %d)", who, ops);
+    const int pre = ops & (AUGCL_OP_SPLICE | AUGCL_OP_CS_SPLICE | AUGCL_OP_OVERLAY);
+    AUGCL_REQUIRE((pre & (pre - 1)) == 0, "%s: at most one of SPLICE / CS_SPLICE / OVERLAY per chain", who);
+    AUGCL_REQUIRE(d->aug_input == AUGCL_AUG_INPUT_PLAIN || d->aug_input == AUGCL_AUG_INPUT_SHIFTED,
+                  "%s: unknown aug_input %d", who, d->aug_input);
+    if (pre) {
+      AUGCL_REQUIRE(d->bank && d->bank_idx && d->bank_len > 0, "%s: splice / overlay need bank, bank_idx, bank_len", who);
+      if (!aligned(d->bank, 16)) AUGCL_FAIL(AUGCL_ERR_BAD_ALIGN, "%s: bank must be 16-byte aligned", who);
+    }
+    if (ops & AUGCL_OP_CONV) AUGCL_REQUIRE(d->conv_weights, "%s: CONV needs conv_weights", who);
+  }
+  if (r->cpf != 3) AUGCL_FAIL(AUGCL_ERR_UNSUPPORTED, "%s: needs RGB frames (c_per_frame == 3)", who);
+  if ((r->W & 3) || ((r->H * r->W) & 15) || r->W > 128 || r->W < 8)
+    AUGCL_FAIL(AUGCL_ERR_UNSUPPORTED, "%s: needs W %% 4 == 0, 8 <= W <= 128 and (H*W) %% 16 == 0 (got %dx%d)", who, r->H, r->W);
+  float* outs[5] = {d->out_obs, d->out_obs_shift, d->out_obs_aug, d->out_next, d->out_next_shift};
+  for (float* o : outs)
+    if (!aligned(o, 16)) AUGCL_FAIL(AUGCL_ERR_BAD_ALIGN, "%s: image outputs must be 16-byte aligned", who);
+
+  FusedParams p{};
+  SampleParams& sp = p.sp;
+  sp.store[0] = r->obs; sp.store[1] = r->next;
+  sp.idx = d->idx; sp.act = r->act; sp.rew = r->rew; sp.nd = r->nd;
+  sp.out_act = d->out_act; sp.out_rew = d->out_rew; sp.out_nd = d->out_nd;
+  sp.capacity = r->capacity;
+  sp.B = B; sp.C = r->C; sp.H = r->H; sp.W = r->W; sp.Ho = r->H; sp.Wo = r->W; sp.A = r->A;
+  sp.pad = d->pad; sp.normalize = d->normalize ? 1 : 0;
+  sp.idx_mode = d->idx_src; sp.idx_hi = (uint64_t)d->idx_hi; sp.seed = d->seed; sp.subseq = d->subsequence;
+  sp.off_range = (uint32_t)(2 * d->pad + 1);
+  // offsets: tensor 0 (obs) is shifted when out_obs_shift is written or the chain runs on the shifted tensor
+  const bool sh[2] = {d->out_obs_shift != nullptr || (d->out_obs_aug && d->aug_input == AUGCL_AUG_INPUT_SHIFTED),
+                      d->out_next_shift != nullptr};
+  const int32_t* off[2] = {d->off_obs, d->off_next};
+  for (int t = 0; t < 2; ++t) {
+    if (!sh[t]) { sp.off_mode[t] = kSrcNone; continue; }
+    if (d->off_src == AUGCL_SRC_PHILOX) { sp.off_mode[t] = off[t] ? AUGCL_SRC_DEVICE : AUGCL_SRC_PHILOX; sp.off[t] = off[t]; continue; }
+    if (!off[t]) { sp.off_mode[t] = kSrcNone; continue; }
+    sp.off_mode[t] = d->off_src; sp.off[t] = off[t];
+  }
+  p.o_plain[0] = d->out_obs; p.o_plain[1] = d->out_next;
+  p.o_shift[0] = d->out_obs_shift; p.o_shift[1] = d->out_next_shift;
+  p.o_aug = d->out_obs_aug;
+  p.bank = d->bank; p.bank_idx = d->bank_idx; p.bank_len = d->bank_len; p.weights = d->conv_weights;
+  p.thr = SpliceThr{d->hue_thres, d->sat_thres, d->val_thres, (ops & AUGCL_OP_CS_SPLICE) ? AUGCL_CS_SPLICE : AUGCL_SPLICE};
+  p.alpha = d->alpha; p.oma = (float)(1.0 - (double)d->alpha);
+  p.ops = ops; p.aug_shifted = d->aug_input == AUGCL_AUG_INPUT_SHIFTED ? 1 : 0;
+  p.k = r->k; p.bands = (r->H + kFBand - 1) / kFBand;
+  p.units_obs = any_obs ? (int64_t)B * r->k * p.bands : 0;
+  p.units_next = any_next ? (int64_t)B * r->k * p.bands : 0;
+  AUGCL_REQUIRE(p.units_obs + p.units_next < (1ll << 31), "%s: batch too large", who);
+  // cost of a unit ~ the f32 planes it writes (+ the conv's arithmetic, worth about one and a half more)
+  const int n_obs = (d->out_obs ? 1 : 0) + (d->out_obs_shift ? 1 : 0) + (d->out_obs_aug ? 1 : 0);
+  const int n_next = (d->out_next ? 1 : 0) + (d->out_next_shift ? 1 : 0);
+  p.cost_obs = g_fused_cost_obs.load() > 0 ? g_fused_cost_obs.load()
+                                          : 4 * n_obs + ((ops & AUGCL_OP_CONV) ? 6 : 0) + ((ops & 7) ? 1 : 0) + 1;
+  p.cost_next = g_fused_cost_next.load() > 0 ? g_fused_cost_next.load() : 4 * n_next + 1;
+  if (!any_obs) p.cost_obs = 1;
+  if (!any_next) p.cost_next = 1;
+  p.normalize = d->normalize ? 1 : 0;
+  const int rows_max = (kFBand + 2 + d->pad) < r->H ? (kFBand + 2 + d->pad) : r->H;
+  p.plane_stage = ((rows_max * r->W + 30 + 15) & ~15) + 16;
+  p.bank_stage = (ops & 7) ? ((((kFBand + 2) * r->W + 30 + 15) & ~15) + 16) : 0;
+  p.stage_bytes = 3 * (p.plane_stage + p.bank_stage);
+  p.tile_rs = (r->W + 8) & ~3;
+  const size_t tile_bytes = (ops & AUGCL_OP_CONV) ? 3 * (size_t)(kFBand + 2) * p.tile_rs * sizeof(float) : 0;
+  const size_t smem = 576 + 2 * (size_t)p.stage_bytes + tile_bytes;
+  if (smem > 200 * 1024) AUGCL_FAIL(AUGCL_ERR_UNSUPPORTED, "%s: geometry needs %zu B of shared memory", who, smem);
+
+  DeviceGuard g(r->device);
+  AUGCL_CUDA(g.err);
+  cudaStream_t st = (cudaStream_t)stream;
+
+  // ---- HOST draws: validate like the reference's IndexError, then stage through stream-ordered scratch
+  void* scratch = nullptr;
+  const bool host_idx = d->idx_src == AUGCL_SRC_HOST;
+  if (host_idx)
+    for (int b = 0; b < B; ++b)
+      AUGCL_REQUIRE(d->idx[b] >= 0 && d->idx[b] < r->capacity, "%s: index %lld (position %d) out of range [0, %lld)", who,
+                    (long long)d->idx[b], b, (long long)r->capacity);
+  bool host_off = false;
+  for (int t = 0; t < 2; ++t)
+    if (sp.off_mode[t] == AUGCL_SRC_HOST) {
+      host_off = true;
+      for (int e = 0; e < 2 * B; ++e)
+        AUGCL_REQUIRE(off[t][e] >= 0 && off[t][e] <= 2 * d->pad, "%s: offset %d (tensor %d, element %d) outside [0, %d]", who,
+                      off[t][e], t, e, 2 * d->pad);
+    }
+  if (host_idx || host_off) {
+    const size_t ib = (size_t)B * 8, ob = (size_t)B * 8;
+    AUGCL_CUDA(cudaMallocAsync(&scratch, ib + 2 * ob, st));
+    uint8_t* spn = static_cast<uint8_t*>(scratch);
+    cudaError_t e = cudaSuccess;
+    if (host_idx) {
+      e = cudaMemcpyAsync(spn, d->idx, ib, cudaMemcpyHostToDevice, st);
+      sp.idx = reinterpret_cast<const int64_t*>(spn);
+      sp.idx_mode = AUGCL_SRC_DEVICE;
+    }
+    for (int t = 0; t < 2 && e == cudaSuccess; ++t)
+      if (sp.off_mode[t] == AUGCL_SRC_HOST) {
+        e = cudaMemcpyAsync(spn + ib + t * ob, off[t], ob, cudaMemcpyHostToDevice, st);
+        sp.off[t] = reinterpret_cast<const int32_t*>(spn + ib + t * ob);
+        sp.off_mode[t] = AUGCL_SRC_DEVICE;
+      }
+    if (e != cudaSuccess) {
+      cudaFreeAsync(scratch, st);
+      AUGCL_FAIL(AUGCL_ERR_CUDA, "%s: staging the host draws failed: %s", who, cudaGetErrorString(e));
+    }
+  }
+
+  static std::atomic<uint64_t> configured{0};   // one bit per device
+  if (!(configured.load() >> (r->device & 63) & 1)) {
+    cudaError_t e = cudaFuncSetAttribute(ring_sample_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    if (e != cudaSuccess) {
+      if (scratch) cudaFreeAsync(scratch, st);
+      AUGCL_FAIL(AUGCL_ERR_CUDA, "%s: cudaFuncSetAttribute failed: %s", who, cudaGetErrorString(e));
+    }
+    configured.fetch_or(1ull << (r->device & 63));
+  }
+  int per_sm = g_fused_ctas_per_sm.load();
+  const int fit = (int)((228 * 1024) / (smem + 1024));
+  if (per_sm > fit) per_sm = fit < 1 ? 1 : fit;
+  int64_t grid = (int64_t)kNumSMs * per_sm;
+  const int64_t units = p.units_obs + p.units_next;
+  if (grid > units) grid = units;
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3((unsigned)grid);
+  cfg.blockDim = dim3(kFThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = g_sample_pdl.load() ? 1 : 0;
+  cudaError_t le = cudaLaunchKernelEx(&cfg, ring_sample_fused_kernel, p);
+  if (le == cudaSuccess) le = cudaGetLastError();
+  if (scratch) cudaFreeAsync(scratch, st);   // stream-ordered: released after the kernel that reads it
+  if (le != cudaSuccess) AUGCL_FAIL(AUGCL_ERR_CUDA, "%s: launch failed: %s", who, cudaGetErrorString(le));
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  return AUGCL_OK;
+}

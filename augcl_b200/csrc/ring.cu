@@ -16,138 +16,9 @@
 // 2*C*H*W (u8 read) + 2*4*C*Ho*Wo (f32 write) = 635 040 B at C=9, 84x84.
 #include "common.cuh"
 
-namespace augcl {
-extern std::atomic<int> g_sample_stages;
-extern std::atomic<int> g_sample_ctas_per_sm;
-extern std::atomic<int> g_sample_pdl;
-extern std::atomic<int> g_sample_band;
-}
-
-struct augcl_ring {
-  int device;
-  int64_t capacity;
-  int k, cpf, C, H, W, A;
-  int64_t stack_bytes;  // C*H*W
-  uint8_t* obs;
-  uint8_t* next;
-  float* act;
-  float* rew;
-  float* nd;
-  int64_t bytes;
-};
+#include "ring.cuh"
 
 namespace augcl {
-
-struct SampleParams {
-  const uint8_t* store[2];
-  float* out[2];
-  const int32_t* off[2];
-  const int64_t* idx;
-  const float* act;
-  const float* rew;
-  const float* nd;
-  float* out_act;
-  float* out_rew;
-  float* out_nd;
-  int64_t capacity;
-  int B, C, H, W, Ho, Wo, A;
-  int pad;        // SHIFT: pad; NONE/CROP: 0.  source coord = clamp(out coord + off - pad)
-  int normalize;
-  int nt;         // number of tensors written (1 or 2); slot s -> tensor tmap[s]
-  int tmap[2];
-  int stage_bytes;
-  int stages;
-  // where the draws come from (AUGCL_SRC_*; kSrcInline = by value in the launch's parameter block, kSrcNone = identity)
-  int idx_mode;
-  int off_mode[2];
-  uint32_t off_range;      // PHILOX offsets are uniform in [0, off_range)
-  uint64_t idx_hi;         // PHILOX indices are uniform in [0, idx_hi)
-  uint64_t seed, subseq;   // PHILOX streams: indices = subseq, obs offsets = subseq + 1, next_obs offsets = subseq + 2
-};
-
-constexpr int kSrcInline = 3;
-constexpr int kSrcNone = 4;
-constexpr int kInlineMax = 256;   // the reference's batch sizes: 128 (src/arguments.py:30) and 256 (soda_batch_size, :60)
-
-// Draws carried BY VALUE in the kernel's parameter block (constant bank): a host caller's indices and
-// offsets reach the GPU inside the launch itself -- no separate H2D copy, no device scratch.
-template <int NB>
-struct InlineDraws {
-  int32_t idx[NB];
-  int8_t off[2][NB][2];
-};
-template <>
-struct InlineDraws<0> {};
-
-__device__ __forceinline__ int64_t clamp_idx(int64_t i, int64_t cap) {
-  return i < 0 ? 0 : (i >= cap ? cap - 1 : i);
-}
-
-__device__ __forceinline__ uint32_t philox_word(uint64_t e, uint64_t subseq, uint64_t seed) {
-  const uint4 r = philox4x32_10(e >> 2, subseq, seed);
-  const uint32_t k = (uint32_t)e & 3u;
-  return k == 0 ? r.x : (k == 1 ? r.y : (k == 2 ? r.z : r.w));
-}
-
-// Ring slot of sample b (always clamped into [0, capacity) for memory safety).
-template <class Inl>
-__device__ __forceinline__ int64_t sample_index(const SampleParams& p, const Inl& inl, int b) {
-  int64_t i;
-  if constexpr (sizeof(Inl) > 1) {
-    if (p.idx_mode == kSrcInline) return clamp_idx((int64_t)inl.idx[b], p.capacity);
-  }
-  if (p.idx_mode == AUGCL_SRC_PHILOX)   // same values as augcl_rng_fill_indices(out, B, 0, idx_hi, seed, subseq)
-    i = (int64_t)(((uint64_t)philox_word((uint64_t)b, p.subseq, p.seed) * p.idx_hi) >> 32);
-  else
-    i = p.idx[b];
-  return clamp_idx(i, p.capacity);
-}
-
-// (dy, dx) of sample b for tensor t: source coordinate = output coordinate + (dy, dx), clamped.
-template <class Inl>
-__device__ __forceinline__ void sample_offset(const SampleParams& p, const Inl& inl, int t, int b, int& dy, int& dx) {
-  const int m = p.off_mode[t];
-  if (m == kSrcNone) { dy = 0; dx = 0; return; }
-  int oy = 0, ox = 0;
-  if (m == AUGCL_SRC_PHILOX) {          // same values as augcl_rng_fill_offsets(out, 2B, 0, off_range, seed, subseq+1+t)
-    const uint4 r = philox4x32_10((uint64_t)(b >> 1), p.subseq + 1 + t, p.seed);
-    oy = (int)__umulhi((b & 1) ? r.z : r.x, p.off_range);
-    ox = (int)__umulhi((b & 1) ? r.w : r.y, p.off_range);
-  } else {
-    bool done = false;
-    if constexpr (sizeof(Inl) > 1) {
-      if (m == kSrcInline) { oy = inl.off[t][b][0]; ox = inl.off[t][b][1]; done = true; }
-    }
-    if (!done) { oy = p.off[t][2 * b]; ox = p.off[t][2 * b + 1]; }
-  }
-  dy = oy - p.pad; dx = ox - p.pad;
-}
-
-template <class Inl>
-__device__ __forceinline__ void gather_scalars(const SampleParams& p, const Inl& inl) {
-  // actions / rewards / not_dones rows (src/utils.py:210-212): a few hundred floats, done by a grid-stride loop
-  const int per = p.A + 2;
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < p.B * per; i += gridDim.x * blockDim.x) {
-    const int b = i / per, j = i - b * per;
-    const int64_t s = sample_index(p, inl, b);
-    if (j < p.A) {
-      if (p.out_act) p.out_act[(int64_t)b * p.A + j] = p.act[s * p.A + j];
-    } else if (j == p.A) {
-      if (p.out_rew) p.out_rew[b] = p.rew[s];
-    } else {
-      if (p.out_nd) p.out_nd[b] = p.nd[s];
-    }
-  }
-}
-
-__device__ __forceinline__ float4 finish(uint32_t w, int normalize) {
-  float4 o = bytes_to_float4(w);
-  if (normalize) {
-    o.x = __fdiv_rn(o.x, 255.0f); o.y = __fdiv_rn(o.y, 255.0f);
-    o.z = __fdiv_rn(o.z, 255.0f); o.w = __fdiv_rn(o.w, 255.0f);
-  }
-  return o;
-}
 
 struct ItemMeta {
   int lead;  // byte offset of the plane inside its stage buffer (source aligned down to 16 B)

@@ -10,6 +10,9 @@ std::atomic<int> g_sample_stages{0};   // 0 = auto (4 when a CTA gets few units,
 std::atomic<int> g_sample_ctas_per_sm{6};
 std::atomic<int> g_sample_pdl{1};
 std::atomic<int> g_sample_band{1};
+extern std::atomic<int> g_fused_ctas_per_sm;   // fused.cu
+extern std::atomic<int> g_fused_cost_obs;
+extern std::atomic<int> g_fused_cost_next;
 static thread_local std::string t_error;
 void set_error(const std::string& msg) { t_error = msg; }
 }  // namespace augcl
@@ -40,6 +43,13 @@ int augcl_set_option(const char* key, const char* value) {
   }
   if (!strcmp(key, "sample_pdl")) { g_sample_pdl = atoi(value) != 0; return AUGCL_OK; }
   if (!strcmp(key, "sample_band")) { g_sample_band = atoi(value) != 0; return AUGCL_OK; }
+  if (!strcmp(key, "fused_ctas_per_sm")) {
+    int v = atoi(value);
+    AUGCL_REQUIRE(v >= 1 && v <= 16, "fused_ctas_per_sm must be in [1,16]");
+    g_fused_ctas_per_sm = v; return AUGCL_OK;
+  }
+  if (!strcmp(key, "fused_cost_obs")) { g_fused_cost_obs = atoi(value); return AUGCL_OK; }     // 0 = auto
+  if (!strcmp(key, "fused_cost_next")) { g_fused_cost_next = atoi(value); return AUGCL_OK; }
   AUGCL_FAIL(AUGCL_ERR_BAD_ARG, "augcl_set_option: unknown key '%s'", key);
 }
 

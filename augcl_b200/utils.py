@@ -313,6 +313,141 @@ class ReplayBuffer(object):
         return self._sample(idxs, n=n, aug=L.AUG_SHIFT_OBS, off_obs=offsets, pad_or_size=pad,
                             device_indices=device_indices)
 
+    # ------------------------------------------------------------------ fused per-algorithm samplers
+    _FUSED_OPS = {"splice": L.OP_SPLICE, "CS_splice": L.OP_CS_SPLICE, "overlay": L.OP_OVERLAY, "conv": L.OP_CONV}
+    _FUSED_CHAINS = {(), ("splice",), ("CS_splice",), ("overlay",), ("conv",), ("splice", "conv"), ("CS_splice", "conv"),
+                     ("overlay", "conv")}
+
+    def sample_fused(self, n=None, *, idxs=None, pad=4, data_aug="", aug_params=None, aug_input="plain",
+                     want=("obs_shift", "obs_aug", "next_obs"), offsets=None, bank_idx=None, weights=None,
+                     normalize=False, device_indices=False):
+        """ONE kernel (augcl_ring_sample_fused) for a whole update(): gather + cast + random_shift +
+        RAD.apply_aug chain, every frame read once.
+
+        data_aug   the reference's ``--data_aug`` string (src/algorithms/rad.py:9-16): "splice-conv", "overlay",
+                   "conv", "splice", "CS_splice", "CS_splice-conv", "overlay-conv" ("" / "identity" = no obs_aug).
+        aug_params the reference's ``--aug_params`` dict, e.g. {"splice": {"val_thres": 0.4}}.
+        aug_input  "plain": chain on the un-shifted obs (AugCL, src/algorithms/augcl.py:70-71);
+                   "shift": chain on random_shift(obs) (SVEA, src/algorithms/svea.py:67 + :46).
+        want       subset of {"obs", "obs_shift", "obs_aug", "next_obs", "next_obs_shift"}.
+        offsets    optional {"obs": (B,2), "next_obs": (B,2)} shift draws; bank_idx (B,), weights (B,3,3,3,3).
+        Returns a dict with the wanted tensors plus "action", "reward", "not_done".
+        Raises NotImplementedError for chains the fused kernel does not cover (use sample() + augmentations)."""
+        keys = tuple(k for k in str(data_aug).split("-") if k and k != "identity")
+        if keys not in self._FUSED_CHAINS:
+            raise NotImplementedError(f"sample_fused: chain {data_aug!r} is not fused; use sample() + augmentations.*")
+        want = set(want)
+        bad = want - {"obs", "obs_shift", "obs_aug", "next_obs", "next_obs_shift"}
+        if bad:
+            raise ValueError(f"sample_fused: unknown outputs {sorted(bad)}")
+        if "obs_aug" in want and not keys:
+            raise ValueError("sample_fused: obs_aug wanted but data_aug is empty")
+        if aug_input not in ("plain", "shift"):
+            raise ValueError(f"sample_fused: aug_input must be 'plain' or 'shift', got {aug_input!r}")
+        aug_params = aug_params or {}
+        offsets = offsets or {}
+        self._flush()
+        sub = augmentations._reserve_subsequences(3)
+        if device_indices and idxs is None:
+            B = self.batch_size if n is None else int(n)
+            i_src, i_ptr, keep_i = L.SRC_PHILOX, None, None
+            idx_hi = self.capacity if self.full else self.idx
+        else:
+            if idxs is None:
+                idxs = self._get_idxs(n)
+            i_src, i_ptr, B, keep_i = self._idx_arg(idxs)
+            idx_hi = 0
+        oo, on = self._off_arg(offsets.get("obs"), B), self._off_arg(offsets.get("next_obs"), B)
+        shift_obs = "obs_shift" in want or ("obs_aug" in want and aug_input == "shift")
+        need_draw = (shift_obs and oo is None) or ("next_obs_shift" in want and on is None)
+        kinds = {x[0] for x in (oo, on) if x is not None}
+        if need_draw or len(kinds) > 1:
+            def to_dev(x):
+                if x is None or x[0] == L.SRC_DEVICE:
+                    return x
+                t = torch.from_numpy(x[2]).to(self.device)
+                return L.SRC_DEVICE, t.data_ptr(), t
+            oo, on = to_dev(oo), to_dev(on)
+            o_src = L.SRC_PHILOX if need_draw else L.SRC_DEVICE
+        else:
+            o_src = kinds.pop() if kinds else L.SRC_DEVICE
+        c, h, w = self.obs_shape
+        dev = self.device
+        d = L.FusedDesc()
+        d.struct_size = C.sizeof(L.FusedDesc)
+        d.B, d.idx_src, d.off_src, d.idx, d.idx_hi = B, i_src, o_src, i_ptr, idx_hi
+        d.off_obs = None if oo is None else oo[1]
+        d.off_next = None if on is None else on[1]
+        d.pad, d.normalize, d.seed, d.subsequence = int(pad), 1 if normalize else 0, augmentations._seed, sub
+        with torch.cuda.device(dev):
+            order = [k for k in ("obs", "obs_shift", "obs_aug", "next_obs", "next_obs_shift") if k in want]
+            block = torch.empty((len(order), B, c, h, w), dtype=torch.float32, device=dev)
+            out = dict(zip(order, block.unbind(0)))
+            ptr = {k: v.data_ptr() for k, v in out.items()}
+            d.out_obs, d.out_obs_shift, d.out_obs_aug = ptr.get("obs"), ptr.get("obs_shift"), ptr.get("obs_aug")
+            d.out_next, d.out_next_shift = ptr.get("next_obs"), ptr.get("next_obs_shift")
+            act = torch.empty((B,) + self.actions.shape[1:], dtype=torch.float32, device=dev)
+            rew, nd = torch.empty((2, B, 1), dtype=torch.float32, device=dev).unbind(0)
+            d.out_act, d.out_rew, d.out_nd = act.data_ptr(), rew.data_ptr(), nd.data_ptr()
+            keep = [keep_i, oo, on]
+            if "obs_aug" in want:
+                ops = 0
+                for k in keys:
+                    ops |= self._FUSED_OPS[k]
+                d.aug_ops = ops
+                d.aug_input = L.AUG_INPUT_SHIFTED if aug_input == "shift" else L.AUG_INPUT_PLAIN
+                pre = next((k for k in keys if k != "conv"), None)
+                if pre is not None:
+                    prm = aug_params.get(pre, {})
+                    augmentations.load_dataloader(batch_size=B, image_size=h, dataset=prm.get("dataset", "coco"), device=dev)
+                    bank = augmentations.get_background_bank()
+                    if bank.dtype != torch.uint8 or bank.device != dev or tuple(bank.shape[2:]) != (h, w):
+                        raise NotImplementedError("sample_fused: needs a uint8 background bank of the observation size on the ring's device")
+                    rows = augmentations._bank_rows(B, bank.shape[0], bank_idx, dev)
+                    d.bank, d.bank_len, d.bank_idx = bank.data_ptr(), bank.shape[0], rows.data_ptr()
+                    keep += [bank, rows]
+                    if pre == "overlay":
+                        d.alpha = float(prm.get("alpha", 0.5))
+                    else:
+                        dflt = (0, 0, 0.6) if pre == "splice" else (3.5, 0, 0)
+                        d.hue_thres = float(prm.get("hue_thres", dflt[0]))
+                        d.sat_thres = float(prm.get("sat_thres", dflt[1]))
+                        d.val_thres = float(prm.get("val_thres", dflt[2]))
+                if "conv" in keys:
+                    if weights is None:
+                        wt = torch.empty((B, 3, 3, 3, 3), dtype=torch.float32, device=dev)
+                        L.call("augcl_rng_fill_normal", wt.data_ptr(), wt.numel(), augmentations._seed,
+                               augmentations._next_subsequence(), _raw_stream(self._dev_index))
+                    else:
+                        wt = torch.as_tensor(weights).to(device=dev, dtype=torch.float32).contiguous()
+                        if tuple(wt.shape) != (B, 3, 3, 3, 3):
+                            raise ValueError(f"sample_fused: weights must be ({B},3,3,3,3), got {tuple(wt.shape)}")
+                    d.conv_weights = wt.data_ptr()
+                    keep.append(wt)
+            rc = L.lib().augcl_ring_sample_fused(self._ring, C.byref(d), _raw_stream(self._dev_index))
+            if rc != 0:
+                e = L.lib().augcl_last_error().decode(errors="replace")
+                if rc == -5:
+                    raise NotImplementedError(e)
+                raise L.AugclError("augcl_ring_sample_fused", rc, e)
+        self._keep = keep
+        out.update(action=act, reward=rew, not_done=nd)
+        return out
+
+    def sample_augcl(self, n=None, *, data_aug="splice-conv", aug_params=None, pad=4, **kw):
+        """AugCL.update's data (src/algorithms/augcl.py:69-72) from one kernel:
+        (obs_shift, obs_aug, action, reward, next_obs, not_done), obs_aug = apply_aug(un-shifted obs)."""
+        o = self.sample_fused(n, data_aug=data_aug, aug_params=aug_params, pad=pad, aug_input="plain",
+                              want=("obs_shift", "obs_aug", "next_obs"), **kw)
+        return o["obs_shift"], o["obs_aug"], o["action"], o["reward"], o["next_obs"], o["not_done"]
+
+    def sample_svea_aug(self, n=None, *, data_aug="overlay", aug_params=None, pad=4, **kw):
+        """SVEA.update's data (src/algorithms/svea.py:66-70, :45-52) from one kernel:
+        (obs, obs_aug, action, reward, next_obs, not_done) with obs = random_shift(obs), obs_aug = apply_aug(obs)."""
+        o = self.sample_fused(n, data_aug=data_aug, aug_params=aug_params, pad=pad, aug_input="shift",
+                              want=("obs_shift", "obs_aug", "next_obs"), **kw)
+        return o["obs_shift"], o["obs_aug"], o["action"], o["reward"], o["next_obs"], o["not_done"]
+
     # ------------------------------------------------------------------ persistence (reference chunk format)
     IO_BLOCK = 2048   # transitions moved between the ring and pinned host memory per copy
 

@@ -140,6 +140,57 @@ int augcl_ring_sample_ex(augcl_ring* ring, int idx_src, const int64_t* idx, int6
                          augcl_stream stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Fused per-algorithm sampler: ONE kernel gathers the minibatch and writes every tensor an update needs.
+ * Replaces, for one update() of
+ *   SVEA   (src/algorithms/svea.py:66-70, :45-52):  sample() -> obs = random_shift(obs) -> apply_aug(obs.clone())
+ *   AugCL  (src/algorithms/augcl.py:69-72):         sample() -> obs_shift = random_shift(obs); obs_aug = apply_aug(obs)
+ *   DrQ / RAD-style updates that also want the un-augmented observation,
+ * the chain ReplayBuffer.sample (src/utils.py:272-280) + random_shift (src/augmentations.py:378-382) +
+ * RAD.apply_aug (src/algorithms/rad.py:18-22) over splice / CS_splice / random_overlay / random_conv
+ * (src/augmentations.py:253-324).  Each u8 frame is read from HBM once; no intermediate f32 tensor is written.
+ * Algorithmic bytes per sample at 9x84x84, AugCL splice-conv: 2*63 504 + 3*21 168 + 3*254 016 = 952 560.
+ *
+ * aug_ops chains (applied in this order): [SPLICE | CS_SPLICE | OVERLAY] then [CONV]; 0 = no augmented output.
+ * Requirements: W % 4 == 0, (H*W) % 16 == 0, W <= 128, u8 background bank; otherwise AUGCL_ERR_UNSUPPORTED
+ * (the caller then chains augcl_ring_sample_ex and the stand-alone kernels).
+ * ------------------------------------------------------------------------------------------ */
+enum { AUGCL_OP_SPLICE = 1, AUGCL_OP_CS_SPLICE = 2, AUGCL_OP_OVERLAY = 4, AUGCL_OP_CONV = 8 };
+enum { AUGCL_AUG_INPUT_PLAIN = 0, AUGCL_AUG_INPUT_SHIFTED = 1 };
+
+typedef struct augcl_fused_desc {
+  int32_t struct_size;        /* = sizeof(augcl_fused_desc); guards the ABI                                     */
+  int32_t B;                  /* minibatch size                                                                  */
+  int32_t idx_src;            /* AUGCL_SRC_*: where idx comes from (as in augcl_ring_sample_ex)                  */
+  int32_t off_src;            /* AUGCL_SRC_*: where off_obs / off_next come from                                 */
+  const int64_t* idx;         /* int64[B] (DEVICE or HOST); ignored for PHILOX                                   */
+  int64_t idx_hi;             /* PHILOX: indices uniform in [0, idx_hi)                                          */
+  const int32_t* off_obs;     /* int32[B,2] (row, col) in [0, 2*pad]; NULL = identity, or a draw when PHILOX     */
+  const int32_t* off_next;    /* same for out_next_shift                                                         */
+  int32_t pad;                /* random_shift pad                                                                */
+  int32_t normalize;          /* != 0: every image output is divided by 255 (IEEE)                               */
+  uint64_t seed, subsequence; /* Philox streams as in augcl_ring_sample_ex                                       */
+  float* out_obs;             /* [B,C,H,W] obs, un-augmented                                 (NULL = not wanted) */
+  float* out_obs_shift;       /* [B,C,H,W] random_shift(obs)                                 (NULL = not wanted) */
+  float* out_obs_aug;         /* [B,C,H,W] aug_ops chain applied to the aug_input tensor     (NULL = not wanted) */
+  float* out_next;            /* [B,C,H,W] next_obs, un-augmented                            (NULL = not wanted) */
+  float* out_next_shift;      /* [B,C,H,W] random_shift(next_obs)                            (NULL = not wanted) */
+  float* out_act;             /* [B,action_dim] / [B] / [B]; each may be NULL                                    */
+  float* out_rew;
+  float* out_nd;
+  int32_t aug_input;          /* AUGCL_AUG_INPUT_PLAIN (AugCL) | AUGCL_AUG_INPUT_SHIFTED (SVEA)                  */
+  int32_t aug_ops;            /* AUGCL_OP_* bitmask                                                              */
+  const uint8_t* bank;        /* device [bank_len,3,H,W] u8 background bank (SPLICE / CS_SPLICE / OVERLAY)       */
+  int64_t bank_len;
+  const int64_t* bank_idx;    /* device int64[B]: overlay uses bank_idx[s] for every frame of sample s; splice   */
+                              /* uses bank_idx[(s*k+f) mod B] for frame f (the reference's tiling quirks)        */
+  const float* conv_weights;  /* device f32 [B,3,3,3,3] (CONV)                                                   */
+  float hue_thres, sat_thres, val_thres;   /* splice thresholds (src/augmentations.py:295 / :309)               */
+  float alpha;                /* overlay alpha (0.5 in the reference)                                            */
+} augcl_fused_desc;
+
+int augcl_ring_sample_fused(augcl_ring* ring, const augcl_fused_desc* desc, augcl_stream stream);
+
+/* ------------------------------------------------------------------------------------------
  * Stand-alone augmentations on f32 NCHW batches (in and out must not alias).
  * ------------------------------------------------------------------------------------------ */
 

@@ -1,0 +1,200 @@
+"""GPU parity of the fused per-algorithm sampler (augcl_ring_sample_fused, ReplayBuffer.sample_fused /
+sample_augcl / sample_svea_aug) against the CPU oracle: oracle gather followed by the oracle's
+random_shift / splice / CS_splice / random_overlay / random_conv in the reference's order
+(src/algorithms/augcl.py:69-72, svea.py:66-70 + :45-52, rad.py:18-22).
+Bit-exact for the copies and the splice select; <= 1e-5 on the /255 scale for overlay and conv."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import TOL_NORM
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def U():
+    from augcl_b200 import utils
+    return utils
+
+
+@pytest.fixture(scope="module")
+def A():
+    from augcl_b200 import augmentations
+    return augmentations
+
+
+@pytest.fixture(scope="module")
+def O():
+    from oracle import augcl_oracle
+    return augcl_oracle
+
+
+def dmc_like_frames(rng, n, S):
+    """Frames with flat bright low-saturation background and saturated blobs, so splice keeps 20-50 % of the pixels."""
+    fr = np.empty((n, 3, S, S), dtype=np.uint8)
+    for i in range(n):
+        base = rng.randint(150, 256)
+        fr[i] = base
+        fr[i, :, : S // 3] = rng.randint(0, 120)                       # dark band: below the value threshold
+        for _ in range(4):
+            y, x = rng.randint(0, S - 6, 2)
+            hh, ww = rng.randint(3, S // 2, 2)
+            fr[i, :, y:y + hh, x:x + ww] = rng.randint(0, 256, (3, 1, 1))
+        noise = rng.rand(S, S) < 0.15
+        fr[i][:, noise] = rng.randint(0, 256, (3, int(noise.sum())))
+    return fr
+
+
+def build_pair(U, O, rng, S, k, cap, B, A_=5, steps=None):
+    steps = steps or cap + 7
+    buf = U.ReplayBuffer((3 * k, S, S), (A_,), cap, B)
+    ora = O.HostRing((3 * k, S, S), (A_,), cap, B)
+    frames = dmc_like_frames(rng, steps + k, S)
+    for t in range(steps):
+        a, r, dn = rng.randn(A_).astype(np.float32), float(rng.randn()), bool(rng.rand() < 0.2)
+        buf.add(U.LazyFrames(list(frames[t:t + k])), a, r, U.LazyFrames(list(frames[t + 1:t + 1 + k])), dn)
+        ora.add(O.LazyFrames(frames[t:t + k]), a, r, O.LazyFrames(frames[t + 1:t + 1 + k]), dn)
+    return buf, ora
+
+
+def oracle_chain(O, x, keys, imgs, wt, params):
+    for key in keys:
+        if key == "splice":
+            x = O.splice(x, imgs, **params.get("splice", {}))
+        elif key == "CS_splice":
+            x = O.cs_splice(x, imgs, **params.get("CS_splice", {}))
+        elif key == "overlay":
+            x = O.random_overlay(x, imgs, params.get("overlay", {}).get("alpha", 0.5))
+        elif key == "conv":
+            x = O.random_conv(x, wt)
+    return x
+
+
+CHAINS = ["splice-conv", "splice", "CS_splice", "overlay", "conv", "overlay-conv", "CS_splice-conv"]
+
+
+@pytest.mark.parametrize("S,k,pad", [(84, 3, 4), (100, 3, 4), (20, 2, 3), (84, 1, 4)])
+@pytest.mark.parametrize("aug_input", ["plain", "shift"])
+def test_fused_chains_against_oracle(U, A, O, S, k, pad, aug_input):
+    rng = np.random.RandomState(S * 10 + k)
+    cap, B = 40, 11
+    buf, ora = build_pair(U, O, rng, S, k, cap, B)
+    bank = torch.from_numpy(rng.randint(0, 256, (9, 3, S, S)).astype(np.uint8))
+    A.set_background_bank(bank.cuda())
+    try:
+        for chain in CHAINS:
+            keys = chain.split("-")
+            idxs = rng.randint(0, cap, size=B)
+            off = {"obs": rng.randint(0, 2 * pad + 1, (B, 2)), "next_obs": rng.randint(0, 2 * pad + 1, (B, 2))}
+            off["obs"][0] = (0, 0); off["obs"][1] = (2 * pad, 2 * pad); off["obs"][2] = (0, 2 * pad)
+            rows = rng.randint(0, 9, size=B)
+            wt = torch.from_numpy(rng.randn(B, 3, 3, 3, 3).astype(np.float32))
+            params = {"splice": {"val_thres": 0.4}} if chain == "splice" else {}
+            out = buf.sample_fused(idxs=idxs, pad=pad, data_aug=chain, aug_params=params, aug_input=aug_input,
+                                   want=("obs", "obs_shift", "obs_aug", "next_obs", "next_obs_shift"), offsets=off,
+                                   bank_idx=rows, weights=wt)
+            o_obs, o_act, o_rew, o_next, o_nd = ora.sample(idxs)
+            o_shift = O.random_shift_int(o_obs, off["obs"], pad)
+            assert torch.equal(out["obs"].cpu(), o_obs), chain
+            assert torch.equal(out["obs_shift"].cpu(), o_shift), chain
+            assert torch.equal(out["next_obs"].cpu(), o_next), chain
+            assert torch.equal(out["next_obs_shift"].cpu(), O.random_shift_int(o_next, off["next_obs"], pad)), chain
+            assert torch.equal(out["action"].cpu(), o_act) and torch.equal(out["reward"].cpu(), o_rew)
+            assert torch.equal(out["not_done"].cpu(), o_nd)
+            imgs = O.bank_rows_f32(bank, rows)
+            want = oracle_chain(O, o_shift if aug_input == "shift" else o_obs, keys, imgs, wt, params)
+            got = out["obs_aug"].cpu()
+            if chain in ("splice", "CS_splice"):
+                assert torch.equal(got, want), f"{chain}/{aug_input}: select must be bit-exact"
+            else:
+                err = (got - want).abs().max().item() / 255.0
+                assert err <= TOL_NORM, f"{chain}/{aug_input}: {err}"
+    finally:
+        A.set_background_bank(None)
+
+
+def test_fused_subset_outputs_normalize_and_wrappers(U, A, O):
+    rng = np.random.RandomState(7)
+    S, k, cap, B, pad = 84, 3, 64, 16, 4
+    buf, ora = build_pair(U, O, rng, S, k, cap, B)
+    bank = torch.from_numpy(rng.randint(0, 256, (5, 3, S, S)).astype(np.uint8))
+    A.set_background_bank(bank.cuda())
+    try:
+        idxs = rng.randint(0, cap, size=B)
+        off = rng.randint(0, 2 * pad + 1, (B, 2))
+        rows = rng.randint(0, 5, size=B)
+        wt = torch.from_numpy(rng.randn(B, 3, 3, 3, 3).astype(np.float32))
+        o_obs, o_act, o_rew, o_next, o_nd = ora.sample(idxs)
+        imgs = O.bank_rows_f32(bank, rows)
+        # AugCL wrapper (src/algorithms/augcl.py:69-72)
+        sh, aug, act, rew, nxt, nd = buf.sample_augcl(idxs=idxs, offsets={"obs": off}, bank_idx=rows, weights=wt)
+        assert torch.equal(sh.cpu(), O.random_shift_int(o_obs, off, pad)) and torch.equal(nxt.cpu(), o_next)
+        want = O.random_conv(O.splice(o_obs, imgs), wt)
+        assert (aug.cpu() - want).abs().max().item() / 255.0 <= TOL_NORM
+        assert torch.equal(act.cpu(), o_act) and torch.equal(rew.cpu(), o_rew) and torch.equal(nd.cpu(), o_nd)
+        # the unfused product path gives the same tensors as the fused one
+        plain = buf.sample(idxs=idxs)[0]
+        chain = A.random_conv(A.splice(plain, bank_idx=rows), weights=wt)
+        assert (aug - chain).abs().max().item() / 255.0 <= TOL_NORM
+        # SVEA wrapper (src/algorithms/svea.py:66-70): overlay of the SHIFTED obs
+        sh2, aug2, _, _, nxt2, _ = buf.sample_svea_aug(idxs=idxs, offsets={"obs": off}, bank_idx=rows)
+        assert torch.equal(sh2, sh) and torch.equal(nxt2, nxt)
+        want2 = O.random_overlay(O.random_shift_int(o_obs, off, pad), imgs)
+        assert (aug2.cpu() - want2).abs().max().item() / 255.0 <= TOL_NORM
+        # subsets + normalize: every output divided by 255 (IEEE)
+        out = buf.sample_fused(idxs=idxs, data_aug="splice", want=("obs_aug",), bank_idx=rows, normalize=True)
+        assert set(out) == {"obs_aug", "action", "reward", "not_done"}
+        assert torch.equal(out["obs_aug"].cpu(), O.splice(o_obs, imgs) / 255.0)
+        out = buf.sample_fused(idxs=idxs, want=("next_obs",))
+        assert torch.equal(out["next_obs"].cpu(), o_next)
+        # device-side draws: same Philox streams as sample_svea / augcl_rng_fill_offsets
+        A.seed(123)
+        a1 = buf.sample_fused(idxs=idxs, want=("obs_shift", "next_obs"))
+        A.seed(123)
+        b1 = buf.sample_svea(idxs=idxs)
+        assert torch.equal(a1["obs_shift"], b1[0]) and torch.equal(a1["next_obs"], b1[3])
+        A.seed(5)
+        a2 = buf.sample_fused(n=B, want=("obs", "next_obs"), device_indices=True)
+        A.seed(5)
+        b2 = buf.sample(n=B, device_indices=True)
+        assert torch.equal(a2["obs"], b2[0]) and torch.equal(a2["next_obs"], b2[3]) and torch.equal(a2["reward"], b2[2])
+        with pytest.raises(NotImplementedError):
+            buf.sample_fused(idxs=idxs, data_aug="conv-splice", want=("obs_aug",))
+        with pytest.raises(U.L.AugclError):
+            buf.sample_fused(idxs=np.array([cap] * B), want=("obs",))
+    finally:
+        A.set_background_bank(None)
+
+
+def test_fused_full_size_properties(U, A):
+    """BASELINE.json configs[3] size (batch 128, 100k ring): fused == unfused product chain on the same draws."""
+    cap, B, S, k = 100_000, 128, 84, 3
+    buf = U.ReplayBuffer((3 * k, S, S), (6,), cap, B)
+    buf.fill_synthetic(seed=3)
+    A.set_background_bank(None)
+    A.seed(11)
+    A.load_dataloader(B, S)
+    g = torch.Generator().manual_seed(0)
+    idxs = torch.randint(0, cap, (B,), generator=g).numpy()
+    off = torch.randint(0, 9, (B, 2), generator=g).numpy()
+    rows = torch.randint(0, A.SYNTHETIC_BANK_LEN, (B,), generator=g).numpy()
+    wt = torch.randn((B, 3, 3, 3, 3), generator=g)
+    try:
+        sh, aug, act, rew, nxt, nd = buf.sample_augcl(idxs=idxs, offsets={"obs": off}, bank_idx=rows, weights=wt)
+        obs, act2, rew2, nxt2, nd2 = buf.sample(idxs=idxs)
+        assert torch.equal(nxt, nxt2) and torch.equal(act, act2) and torch.equal(rew, rew2) and torch.equal(nd, nd2)
+        assert torch.equal(sh, A.random_shift(obs, 4, offsets=off))
+        chain = A.random_conv(A.splice(obs, bank_idx=rows), weights=wt)
+        assert (aug - chain).abs().max().item() / 255.0 <= TOL_NORM
+        sp = buf.sample_fused(idxs=idxs, data_aug="splice", want=("obs_aug",), bank_idx=rows)["obs_aug"]
+        assert torch.equal(sp, A.splice(obs, bank_idx=rows))
+        # batch 1024 exercises > 2 units per CTA on every CTA
+        idx2 = torch.randint(0, cap, (1024,), generator=g).numpy()
+        rows2 = torch.randint(0, A.SYNTHETIC_BANK_LEN, (1024,), generator=g).numpy()
+        o2 = buf.sample_fused(idxs=idx2, data_aug="overlay", aug_input="shift", want=("obs_shift", "obs_aug", "next_obs"),
+                              bank_idx=rows2, offsets={"obs": np.full((1024, 2), 3)})
+        assert (o2["obs_aug"] - A.random_overlay(o2["obs_shift"], bank_idx=rows2)).abs().max().item() / 255.0 <= TOL_NORM
+        assert torch.equal(o2["next_obs"], buf.sample(idxs=idx2)[3])
+    finally:
+        A.set_background_bank(None)
