@@ -25,6 +25,7 @@ namespace augcl {
 std::atomic<int> g_fused_ctas_per_sm{6};
 std::atomic<int> g_fused_cost_obs{0};    // 0 = auto
 std::atomic<int> g_fused_cost_next{0};
+std::atomic<int> g_fused_fast_mask{1};   // 0: always the float HSV path (A/B and the exhaustive equivalence test)
 
 constexpr int kFBand = 12;
 constexpr int kFThreads = 128;
@@ -39,6 +40,7 @@ struct FusedParams {
   const float* weights;
   int64_t bank_len;
   SpliceThr thr;
+  float thr_byte;           // kPreSpliceFast: smallest byte value b with b/255 > thr.val (256 = none)
   float oma, alpha;
   int ops;                  // AUGCL_OP_*
   int aug_shifted;          // chain input: 0 plain, 1 shifted
@@ -61,11 +63,19 @@ struct FusedMeta {
   int pad_;
 };
 
-__device__ __forceinline__ float fin(float v, int normalize) { return normalize ? __fdiv_rn(v, 255.0f) : v; }
-__device__ __forceinline__ float4 fin4(float4 v, int normalize) {
-  return make_float4(fin(v.x, normalize), fin(v.y, normalize), fin(v.z, normalize), fin(v.w, normalize));
+template <bool NORM>
+__device__ __forceinline__ float fin(float v) { return NORM ? div255(v) : v; }   // div255 == IEEE v / 255 (pixel.cuh)
+template <bool NORM>
+__device__ __forceinline__ float4 fin4(float4 v) {
+  return make_float4(fin<NORM>(v.x), fin<NORM>(v.y), fin<NORM>(v.z), fin<NORM>(v.w));
 }
 
+// chain stage before the conv
+enum { kPreNone = 0, kPreSplice = 1, kPreSpliceFast = 2, kPreOverlay = 3 };
+
+// PRE, CONV: the aug chain (compile time: every variant is straight-line code, a few hundred SASS instructions
+// instead of one 5 000-instruction kernel that thrashes the instruction cache).  WC: image width (0 = p.sp.W).
+template <int PRE, bool CONV, bool NORM, int WC>
 __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const __grid_constant__ FusedParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem);                 // 2 mbarriers
@@ -74,12 +84,11 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
   uint8_t* stage = smem + 144 + 432;                                  // 2 x stage_bytes (576 = 16 * 36: 16-B aligned)
   float* tile = reinterpret_cast<float*>(stage + 2 * p.stage_bytes);  // [3][kFBand+2][tile_rs]
   const int tid = threadIdx.x;
-  const int H = p.sp.H, W = p.sp.W, nq = W >> 2;
-  const bool conv = (p.ops & AUGCL_OP_CONV) != 0;
-  const bool splice = (p.ops & (AUGCL_OP_SPLICE | AUGCL_OP_CS_SPLICE)) != 0;
-  const bool overlay = (p.ops & AUGCL_OP_OVERLAY) != 0;
-  const bool use_bank = splice || overlay;
-  const int hal = conv ? 1 : 0;
+  const int H = p.sp.H, W = WC ? WC : p.sp.W, nq = W >> 2;
+  const int TRS = WC ? ((WC + 8) & ~3) : p.tile_rs;
+  constexpr bool kSplice = PRE == kPreSplice || PRE == kPreSpliceFast;
+  constexpr bool kBank = PRE != kPreNone;
+  constexpr int hal = CONV ? 1 : 0;
   const InlineDraws<0> none{};
 
   // ---- static partition of the cost line [0, T) over the CTAs; a CTA owns the units whose start falls in its range
@@ -87,7 +96,7 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
   const int64_t c0 = T * blockIdx.x / gridDim.x, c1 = T * (blockIdx.x + 1) / gridDim.x;
   auto first_unit_at = [&](int64_t c) -> int64_t {   // smallest unit whose start cost >= c
     const int64_t To = p.units_obs * p.cost_obs;
-    if (c <= To) return p.cost_obs ? (c + p.cost_obs - 1) / p.cost_obs : 0;
+    if (c <= To) return (c + p.cost_obs - 1) / p.cost_obs;
     return p.units_obs + (c - To + p.cost_next - 1) / p.cost_next;
   };
   const int64_t u0 = first_unit_at(c0), u1 = first_unit_at(c1);
@@ -141,8 +150,8 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
     uint32_t gbytes = 0;
     uintptr_t g0 = 0;
     m.gkoff = 0;
-    if (want_aug && use_bank) {
-      const int64_t j = splice ? ((int64_t)b * p.k + f) % p.sp.B : b;   // batch-tiled (splice) vs channel-tiled (overlay)
+    if (kBank && want_aug) {
+      const int64_t j = kSplice ? ((int64_t)b * p.k + f) % p.sp.B : b;   // batch-tiled (splice) vs channel-tiled (overlay)
       int64_t row = p.bank_idx[j];
       row = row < 0 ? 0 : (row >= p.bank_len ? p.bank_len - 1 : row);
       const uint8_t* g = p.bank + row * 3 * P;
@@ -176,112 +185,136 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
     mbar_wait(&bars[s], phase);
     const FusedMeta m = meta[s];
     const uint8_t* sb = stage + (size_t)s * p.stage_bytes;
-    const uint8_t* gb = sb + 3 * p.plane_stage;
-    const bool do_conv = conv && m.o_aug != nullptr;
-    const int h2 = do_conv ? 1 : 0;
-    const int trows = m.rows + 2 * h2;
-    if (do_conv && tid < 81) {
+    const size_t HW = (size_t)H * W;
+    const int PS = p.plane_stage;
+
+    // one 4-pixel word of each of the 3 planes: un-shifted, and shifted (2 LDS.32 + funnel shift + replicate selector)
+    auto load_plain = [&](int r, int q4, uint32_t (&w)[3]) {
+      const int a = m.koff + r * W + 4 * q4;
+#pragma unroll
+      for (int ci = 0; ci < 3; ++ci) w[ci] = *reinterpret_cast<const uint32_t*>(sb + ci * PS + a);
+    };
+    auto load_shift = [&](int r, int q4, uint32_t (&w)[3]) {
+      const int rr = clampi(r + m.dy, 0, H - 1);
+      const int cc = 4 * q4 + m.dx;
+      const int cs = clampi(cc, 0, W - 4);
+      const uint32_t sel = edge_selector(clampi(cc - cs, -4, 4));
+      const int a = m.koff + rr * W + cs;
+#pragma unroll
+      for (int ci = 0; ci < 3; ++ci) {
+        const uint32_t* wp = reinterpret_cast<const uint32_t*>(sb + ci * PS + (a & ~3));
+        w[ci] = __byte_perm(__funnelshift_r(wp[0], wp[1], (uint32_t)a << 3), 0u, sel);
+      }
+    };
+    auto store3 = [&](float* base, size_t oo, const uint32_t (&w)[3]) {
+#pragma unroll
+      for (int ci = 0; ci < 3; ++ci)
+        st_global_f4(reinterpret_cast<float4*>(base + oo + ci * HW), fin4<NORM>(bytes_to_float4(w[ci])));
+    };
+
+    if (m.o_aug == nullptr) {
+      // ---------------- copy unit (next_obs, or obs without an augmented output) ----------------
+      for (int task = tid; task < m.rows * nq; task += kFThreads) {
+        const int pr = task / nq, q4 = task - pr * nq;
+        const int r = m.r0 + pr;
+        const size_t oo = (size_t)r * W + 4 * q4;
+        uint32_t w[3];
+        if (m.o_plain) { load_plain(r, q4, w); store3(m.o_plain, oo, w); }
+        if (m.o_shift) { load_shift(r, q4, w); store3(m.o_shift, oo, w); }
+      }
+      __syncthreads();   // stage s consumed
+      if (tid == 0 && kk + 2 < nun) issue(kk + 2, s);
+      if (s == 1) phase ^= 1;
+      continue;
+    }
+
+    // ---------------- augmented obs unit, phase A: elementwise ----------------
+    const uint8_t* gb = sb + 3 * PS;
+    const int trows = m.rows + 2 * hal;
+    const bool aug_sh = p.aug_shifted != 0;
+    if (CONV && tid < 81) {
       // weights[sample][co][ci][ky][kx] / 255 -> wsm[(ci*9 + ky*3 + kx)*4 + co]
       const int co = tid / 27, tap = tid - co * 27;
       wsm[tap * 4 + co] = __fdiv_rn(p.weights[(int64_t)m.sample * 81 + tid], 255.0f);
     }
-    const bool aug_sh = m.o_aug != nullptr && p.aug_shifted, aug_pl = m.o_aug != nullptr && !p.aug_shifted;
-    const bool need_bank = m.o_aug != nullptr && use_bank;
-    // ---------------- phase A: elementwise ----------------
     for (int task = tid; task < trows * nq; task += kFThreads) {
       const int pr = task / nq, q4 = task - pr * nq;
-      const int r = clampi(m.r0 + pr - h2, 0, H - 1);
-      const bool own = pr >= h2 && pr < h2 + m.rows;
-      uint32_t Pw[3] = {0, 0, 0}, Sw[3] = {0, 0, 0}, Gw[3] = {0, 0, 0};
-      // halo rows (not own) only feed the conv tile: they touch the source only through the chain's input
-      const bool need_plain = aug_pl || (own && m.o_plain != nullptr);
-      const bool need_shift = aug_sh || (own && m.o_shift != nullptr);
-      if (need_plain) {
-        const int a = m.koff + r * W + 4 * q4;
-#pragma unroll
-        for (int ci = 0; ci < 3; ++ci) Pw[ci] = *reinterpret_cast<const uint32_t*>(sb + ci * p.plane_stage + a);
+      const int r = clampi(m.r0 + pr - hal, 0, H - 1);
+      const bool own = !CONV || (pr >= 1 && pr <= m.rows);   // halo rows only feed the conv tile
+      const size_t oo = (size_t)r * W + 4 * q4;              // offset inside plane 0; planes are H*W apart
+      uint32_t Aw[3], Ow[3];
+      if (aug_sh) {
+        load_shift(r, q4, Aw);
+        if (own && m.o_shift) store3(m.o_shift, oo, Aw);
+        if (own && m.o_plain) { load_plain(r, q4, Ow); store3(m.o_plain, oo, Ow); }
+      } else {
+        load_plain(r, q4, Aw);
+        if (own && m.o_plain) store3(m.o_plain, oo, Aw);
+        if (own && m.o_shift) { load_shift(r, q4, Ow); store3(m.o_shift, oo, Ow); }
       }
-      if (need_shift) {
-        const int rr = clampi(r + m.dy, 0, H - 1);
-        const int cc = 4 * q4 + m.dx;
-        const int cs = clampi(cc, 0, W - 4);
-        const uint32_t sel = edge_selector(clampi(cc - cs, -4, 4));
-        const int a = m.koff + rr * W + cs;
+      float a[3][4], v[3][4];
+#pragma unroll
+      for (int ci = 0; ci < 3; ++ci) {
+        const float4 t4 = bytes_to_float4(Aw[ci]);
+        a[ci][0] = t4.x; a[ci][1] = t4.y; a[ci][2] = t4.z; a[ci][3] = t4.w;
+      }
+      if (kBank) {
+        float g[3][4];
+        const int ga = m.gkoff + r * W + 4 * q4;
 #pragma unroll
         for (int ci = 0; ci < 3; ++ci) {
-          const uint32_t* wp = reinterpret_cast<const uint32_t*>(sb + ci * p.plane_stage + (a & ~3));
-          Sw[ci] = __byte_perm(__funnelshift_r(wp[0], wp[1], (uint32_t)a << 3), 0u, sel);
-        }
-      }
-      if (need_bank) {
-        const int a = m.gkoff + r * W + 4 * q4;
-#pragma unroll
-        for (int ci = 0; ci < 3; ++ci) Gw[ci] = *reinterpret_cast<const uint32_t*>(gb + ci * p.bank_stage + a);
-      }
-      const size_t oo = (size_t)r * W + 4 * q4;   // offset inside plane 0; planes are H*W apart
-      if (own) {
-        if (m.o_plain) {
-#pragma unroll
-          for (int ci = 0; ci < 3; ++ci)
-            st_global_f4(reinterpret_cast<float4*>(m.o_plain + oo + (size_t)ci * H * W), fin4(bytes_to_float4(Pw[ci]), p.normalize));
-        }
-        if (m.o_shift) {
-#pragma unroll
-          for (int ci = 0; ci < 3; ++ci)
-            st_global_f4(reinterpret_cast<float4*>(m.o_shift + oo + (size_t)ci * H * W), fin4(bytes_to_float4(Sw[ci]), p.normalize));
-        }
-      }
-      if (m.o_aug == nullptr) continue;
-      float v[3][4];
-      {
-        float a[3][4], g[3][4];
-#pragma unroll
-        for (int ci = 0; ci < 3; ++ci) {
-          const float4 t4 = bytes_to_float4(p.aug_shifted ? Sw[ci] : Pw[ci]);
-          a[ci][0] = t4.x; a[ci][1] = t4.y; a[ci][2] = t4.z; a[ci][3] = t4.w;
-          const float4 g4 = bytes_to_float4(Gw[ci]);
+          const float4 g4 = bytes_to_float4(*reinterpret_cast<const uint32_t*>(gb + ci * p.bank_stage + ga));
           g[ci][0] = g4.x; g[ci][1] = g4.y; g[ci][2] = g4.z; g[ci][3] = g4.w;
         }
-        if (splice) {
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const float rn = div255(a[0][j]), gn = div255(a[1][j]), bn = div255(a[2][j]);
-            const bool keep = splice_keep(rn, gn, bn, p.thr);
-            v[0][j] = (keep ? rn : div255(g[0][j])) * 255.0f;
-            v[1][j] = (keep ? gn : div255(g[1][j])) * 255.0f;
-            v[2][j] = (keep ? bn : div255(g[2][j])) * 255.0f;
+        for (int j = 0; j < 4; ++j) {
+          if (PRE == kPreOverlay) {
+#pragma unroll
+            for (int ci = 0; ci < 3; ++ci) v[ci][j] = overlay_px(a[ci][j], div255(g[ci][j]), p.oma, p.alpha);
+          } else {
+            bool keep;
+            if (PRE == kPreSpliceFast) {
+              // default thresholds (hue = sat = 0) on u8 pixels: the HSV test of pixel.cuh:hsv_gt only compares, and
+              // v -> v/255 is strictly increasing, so it can run on the raw byte values; thr_byte = the smallest
+              // byte whose /255 exceeds val_thres (host).  tests/: all 2^24 colours against the float path.
+              const float mx = fmaxf(fmaxf(a[0][j], a[1][j]), a[2][j]), mn = fminf(fminf(a[0][j], a[1][j]), a[2][j]);
+              keep = mx > mn && !(a[0][j] == mx && a[1][j] == a[2][j]) && mx >= p.thr_byte;
+            } else {
+              keep = splice_keep(div255(a[0][j]), div255(a[1][j]), div255(a[2][j]), p.thr);
+            }
+#pragma unroll
+            for (int ci = 0; ci < 3; ++ci) {
+              const float sel = keep ? a[ci][j] : g[ci][j];
+              // splice returns (x/255 or bg/255) * 255; as conv input the raw byte is the same value to 1 ulp
+              v[ci][j] = CONV ? sel : div255(sel) * 255.0f;
+            }
           }
-        } else if (overlay) {
-#pragma unroll
-          for (int ci = 0; ci < 3; ++ci)
-#pragma unroll
-            for (int j = 0; j < 4; ++j) v[ci][j] = overlay_px(a[ci][j], div255(g[ci][j]), p.oma, p.alpha);
-        } else {
-#pragma unroll
-          for (int ci = 0; ci < 3; ++ci)
-#pragma unroll
-            for (int j = 0; j < 4; ++j) v[ci][j] = a[ci][j];
         }
+      } else {
+#pragma unroll
+        for (int ci = 0; ci < 3; ++ci)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) v[ci][j] = a[ci][j];
       }
-      if (do_conv) {
+      if (CONV) {
 #pragma unroll
         for (int ci = 0; ci < 3; ++ci) {
-          float* trow = tile + (ci * (kFBand + 2) + pr) * p.tile_rs;
+          float* trow = tile + (ci * (kFBand + 2) + pr) * TRS;
           *reinterpret_cast<float4*>(trow + 4 + 4 * q4) = make_float4(v[ci][0], v[ci][1], v[ci][2], v[ci][3]);
           if (q4 == 0) trow[3] = v[ci][0];
           if (q4 == nq - 1) trow[4 + W] = v[ci][3];
         }
-      } else if (own) {
+      } else {
 #pragma unroll
         for (int ci = 0; ci < 3; ++ci)
-          st_global_f4(reinterpret_cast<float4*>(m.o_aug + oo + (size_t)ci * H * W),
-                       fin4(make_float4(v[ci][0], v[ci][1], v[ci][2], v[ci][3]), p.normalize));
+          st_global_f4(reinterpret_cast<float4*>(m.o_aug + oo + ci * HW),
+                       fin4<NORM>(make_float4(v[ci][0], v[ci][1], v[ci][2], v[ci][3])));
       }
     }
     __syncthreads();   // stage s consumed (refill may start), tile + wsm complete
     if (tid == 0 && kk + 2 < nun) issue(kk + 2, s);
     // ---------------- phase B: conv on the tile ----------------
-    if (do_conv) {
+    if (CONV) {
       const int ntask = ((m.rows + 1) >> 1) * nq;
       for (int task = tid; task < ntask; task += kFThreads) {
         const int rp = task / nq, q4 = task - rp * nq;
@@ -298,7 +331,7 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
           float x[4][6];
 #pragma unroll
           for (int y = 0; y < 4; ++y) {
-            const float* trow = tile + (ci * (kFBand + 2) + r + y) * p.tile_rs + q4 * 4;
+            const float* trow = tile + (ci * (kFBand + 2) + r + y) * TRS + q4 * 4;
             const float4 a = *reinterpret_cast<const float4*>(trow + 4);
             x[y][0] = trow[3]; x[y][1] = a.x; x[y][2] = a.y; x[y][3] = a.z; x[y][4] = a.w; x[y][5] = trow[8];
           }
@@ -323,9 +356,9 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
           if (r + a >= m.rows) break;
 #pragma unroll
           for (int co = 0; co < 3; ++co) {
-            float4* dst = reinterpret_cast<float4*>(m.o_aug + ((size_t)co * H + (m.r0 + r + a)) * W) + q4;
-            st_global_f4(dst, fin4(make_float4(sigmoid255(acc[a][co][0]), sigmoid255(acc[a][co][1]),
-                                               sigmoid255(acc[a][co][2]), sigmoid255(acc[a][co][3])), p.normalize));
+            float4* dst = reinterpret_cast<float4*>(m.o_aug + co * HW + (size_t)(m.r0 + r + a) * W) + q4;
+            st_global_f4(dst, fin4<NORM>(make_float4(sigmoid255(acc[a][co][0]), sigmoid255(acc[a][co][1]),
+                                                     sigmoid255(acc[a][co][2]), sigmoid255(acc[a][co][3]))));
           }
         }
       }
@@ -335,6 +368,26 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
   }
 }
 
+}  // namespace augcl
+
+namespace augcl {
+using FusedKernel = void (*)(const FusedParams);
+
+template <int PRE, bool CONV>
+static FusedKernel pick_wn(bool norm, int W) {
+  if (norm) return ring_sample_fused_kernel<PRE, CONV, true, 0>;
+  if (W == 84) return ring_sample_fused_kernel<PRE, CONV, false, 84>;
+  return ring_sample_fused_kernel<PRE, CONV, false, 0>;
+}
+
+static FusedKernel pick_kernel(int pre, bool conv, bool norm, int W) {
+  switch (pre) {
+    case kPreSplice: return conv ? pick_wn<kPreSplice, true>(norm, W) : pick_wn<kPreSplice, false>(norm, W);
+    case kPreSpliceFast: return conv ? pick_wn<kPreSpliceFast, true>(norm, W) : pick_wn<kPreSpliceFast, false>(norm, W);
+    case kPreOverlay: return conv ? pick_wn<kPreOverlay, true>(norm, W) : pick_wn<kPreOverlay, false>(norm, W);
+    default: return conv ? pick_wn<kPreNone, true>(norm, W) : pick_wn<kPreNone, false>(norm, W);
+  }
+}
 }  // namespace augcl
 
 using namespace augcl;
@@ -404,6 +457,18 @@ extern "C" int augcl_ring_sample_fused(augcl_ring* r, const augcl_fused_desc* d,
   p.o_aug = d->out_obs_aug;
   p.bank = d->bank; p.bank_idx = d->bank_idx; p.bank_len = d->bank_len; p.weights = d->conv_weights;
   p.thr = SpliceThr{d->hue_thres, d->sat_thres, d->val_thres, (ops & AUGCL_OP_CS_SPLICE) ? AUGCL_CS_SPLICE : AUGCL_SPLICE};
+  int pre = kPreNone;
+  if (ops & AUGCL_OP_OVERLAY) pre = kPreOverlay;
+  if (ops & AUGCL_OP_CS_SPLICE) pre = kPreSplice;
+  if (ops & AUGCL_OP_SPLICE) {
+    // default hue/sat thresholds: integer-exact mask on the raw bytes (kernel comment); anything else: float HSV
+    pre = (d->hue_thres == 0.0f && d->sat_thres == 0.0f && g_fused_fast_mask.load()) ? kPreSpliceFast : kPreSplice;
+    p.thr_byte = 256.0f;
+    for (int b = 255; b >= 0; --b) {
+      volatile float q = (float)b / 255.0f;      // IEEE division, as div255 / torch
+      if (q > d->val_thres) p.thr_byte = (float)b; else break;
+    }
+  }
   p.alpha = d->alpha; p.oma = (float)(1.0 - (double)d->alpha);
   p.ops = ops; p.aug_shifted = d->aug_input == AUGCL_AUG_INPUT_SHIFTED ? 1 : 0;
   p.k = r->k; p.bands = (r->H + kFBand - 1) / kFBand;
@@ -469,14 +534,13 @@ extern "C" int augcl_ring_sample_fused(augcl_ring* r, const augcl_fused_desc* d,
     }
   }
 
-  static std::atomic<uint64_t> configured{0};   // one bit per device
-  if (!(configured.load() >> (r->device & 63) & 1)) {
-    cudaError_t e = cudaFuncSetAttribute(ring_sample_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  const FusedKernel kern = pick_kernel(pre, (ops & AUGCL_OP_CONV) != 0, p.normalize != 0, r->W);
+  {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);   // idempotent, ~1 us
     if (e != cudaSuccess) {
       if (scratch) cudaFreeAsync(scratch, st);
       AUGCL_FAIL(AUGCL_ERR_CUDA, "%s: cudaFuncSetAttribute failed: %s", who, cudaGetErrorString(e));
     }
-    configured.fetch_or(1ull << (r->device & 63));
   }
   int per_sm = g_fused_ctas_per_sm.load();
   const int fit = (int)((228 * 1024) / (smem + 1024));
@@ -494,7 +558,7 @@ extern "C" int augcl_ring_sample_fused(augcl_ring* r, const augcl_fused_desc* d,
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = g_sample_pdl.load() ? 1 : 0;
-  cudaError_t le = cudaLaunchKernelEx(&cfg, ring_sample_fused_kernel, p);
+  cudaError_t le = cudaLaunchKernelEx(&cfg, kern, p);
   if (le == cudaSuccess) le = cudaGetLastError();
   if (scratch) cudaFreeAsync(scratch, st);   // stream-ordered: released after the kernel that reads it
   if (le != cudaSuccess) AUGCL_FAIL(AUGCL_ERR_CUDA, "%s: launch failed: %s", who, cudaGetErrorString(le));

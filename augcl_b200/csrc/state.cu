@@ -13,6 +13,7 @@ std::atomic<int> g_sample_band{1};
 extern std::atomic<int> g_fused_ctas_per_sm;   // fused.cu
 extern std::atomic<int> g_fused_cost_obs;
 extern std::atomic<int> g_fused_cost_next;
+extern std::atomic<int> g_fused_fast_mask;
 static thread_local std::string t_error;
 void set_error(const std::string& msg) { t_error = msg; }
 }  // namespace augcl
@@ -49,6 +50,7 @@ int augcl_set_option(const char* key, const char* value) {
     g_fused_ctas_per_sm = v; return AUGCL_OK;
   }
   if (!strcmp(key, "fused_cost_obs")) { g_fused_cost_obs = atoi(value); return AUGCL_OK; }     // 0 = auto
+  if (!strcmp(key, "fused_fast_mask")) { g_fused_fast_mask = atoi(value) != 0; return AUGCL_OK; }
   if (!strcmp(key, "fused_cost_next")) { g_fused_cost_next = atoi(value); return AUGCL_OK; }
   AUGCL_FAIL(AUGCL_ERR_BAD_ARG, "augcl_set_option: unknown key '%s'", key);
 }

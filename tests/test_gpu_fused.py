@@ -198,3 +198,42 @@ def test_fused_full_size_properties(U, A):
         assert torch.equal(o2["next_obs"], buf.sample(idxs=idx2)[3])
     finally:
         A.set_background_bank(None)
+
+
+def test_fast_splice_mask_equals_float_hsv_on_all_colours(U, A):
+    """The default-threshold splice mask of the fused kernel runs on raw bytes (fused.cu, kPreSpliceFast); it must
+    select exactly like the float kornia-HSV path (stand-alone augcl_splice, bit-exact vs the oracle) on every one of
+    the 2^24 u8 colours, for the reference's val_thres 0.6 (default) and 0.4, and like the general fused path."""
+    from augcl_b200 import _lib as L
+    S, P = 84, 84 * 84
+    n = (1 << 24 + 0) // P + 1
+    col = np.arange(n * P, dtype=np.int64) & 0xFFFFFF
+    frames = np.stack([(col >> 16) & 255, (col >> 8) & 255, col & 255], axis=0).astype(np.uint8)   # [3, n*P]
+    frames = np.ascontiguousarray(frames.reshape(3, n, S, S).transpose(1, 0, 2, 3))                 # [n,3,S,S]
+    buf = U.ReplayBuffer((3, S, S), (1,), n, 64)
+    z = np.zeros((n, 1), dtype=np.float32)
+    L.call("augcl_ring_put", buf._ring, 0, n, frames.ctypes.data, frames.ctypes.data, z.ctypes.data, z.ctypes.data,
+           z.ctypes.data, None)
+    torch.cuda.synchronize()
+    buf.idx, buf.full = 0, True
+    rng = np.random.RandomState(0)
+    bank = torch.from_numpy(rng.randint(0, 256, (4, 3, S, S)).astype(np.uint8)).cuda()
+    A.set_background_bank(bank)
+    try:
+        idxs = np.arange(n)
+        rows = rng.randint(0, 4, size=n)
+        plain = buf.sample(idxs=idxs)[0]
+        assert torch.equal(plain.cpu().to(torch.uint8), torch.from_numpy(frames))
+        for vt in (0.6, 0.4):
+            prm = {"splice": {"val_thres": vt}}
+            fast = buf.sample_fused(idxs=idxs, data_aug="splice", aug_params=prm, want=("obs_aug",), bank_idx=rows)["obs_aug"]
+            ref = A.splice(plain, val_thres=vt, bank_idx=rows)
+            assert torch.equal(fast, ref), f"val_thres {vt}: {(fast != ref).sum().item()} elements differ"
+            L.set_option("fused_fast_mask", "0")
+            try:
+                slow = buf.sample_fused(idxs=idxs, data_aug="splice", aug_params=prm, want=("obs_aug",), bank_idx=rows)["obs_aug"]
+            finally:
+                L.set_option("fused_fast_mask", "1")
+            assert torch.equal(slow, ref)
+    finally:
+        A.set_background_bank(None)
