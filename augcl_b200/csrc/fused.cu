@@ -27,8 +27,9 @@ std::atomic<int> g_fused_cost_obs{0};    // 0 = auto
 std::atomic<int> g_fused_cost_next{0};
 std::atomic<int> g_fused_fast_mask{1};   // 0: always the float HSV path (A/B and the exhaustive equivalence test)
 
-constexpr int kFBand = 12;
-constexpr int kFThreads = 128;
+constexpr int kFBand = 12;        // conv chains: 12 rows + 2 halo rows = 14 tile rows = two rounds of 7 rows
+constexpr int kFBandNoConv = 14;  // every other chain: 14 rows = two full rounds, 84 = 6 bands
+constexpr int kFThreads = 160;   // 147 = 7 rows x 21 quads work at W = 84: a 14-row tile is exactly two rounds
 
 struct FusedParams {
   SampleParams sp;          // stores, draw sources, scalar gather (sp.out unused)
@@ -84,7 +85,11 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
   uint8_t* stage = smem + 144 + 432;                                  // 2 x stage_bytes (576 = 16 * 36: 16-B aligned)
   float* tile = reinterpret_cast<float*>(stage + 2 * p.stage_bytes);  // [3][kFBand+2][tile_rs]
   const int tid = threadIdx.x;
-  const int H = p.sp.H, W = WC ? WC : p.sp.W, nq = W >> 2;
+  const int H = WC ? WC : p.sp.H, W = WC ? WC : p.sp.W, nq = W >> 2;   // WC != 0: square WC x WC frames
+  // fixed thread -> (row slot, 4-pixel group) mapping: no per-task division, constant address increments
+  const int RPR = kFThreads / nq;            // rows per round (7 at W = 84)
+  const int row0 = tid / nq, q4 = tid - row0 * nq;
+  const bool active = row0 < RPR;
   const int TRS = WC ? ((WC + 8) & ~3) : p.tile_rs;
   constexpr bool kSplice = PRE == kPreSplice || PRE == kPreSpliceFast;
   constexpr bool kBank = PRE != kPreNone;
@@ -111,13 +116,14 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
   pdl_wait();
 
   auto issue = [&](int kk, int s) {   // one lane: decode unit u0+kk, write its meta, start its copies into stage s
-    int64_t u = u0 + kk;
-    const int t = u >= p.units_obs ? 1 : 0;
-    if (t) u -= p.units_obs;
-    const int band = (int)(u % p.bands);
-    const int64_t fr = u / p.bands;            // frame row of x.reshape(B*k, 3, H, W)
-    const int f = (int)(fr % p.k), b = (int)(fr / p.k);
-    const int r0 = band * kFBand, rows = min(kFBand, H - r0);
+    uint32_t u = (uint32_t)(u0 + kk);          // host: units_obs + units_next < 2^31 -> 32-bit divisions
+    const int t = u >= (uint32_t)p.units_obs ? 1 : 0;
+    if (t) u -= (uint32_t)p.units_obs;
+    const uint32_t fr = u / (uint32_t)p.bands;  // frame row of x.reshape(B*k, 3, H, W)
+    const int band = (int)(u - fr * (uint32_t)p.bands);
+    const int b = (int)(fr / (uint32_t)p.k), f = (int)(fr - (uint32_t)b * (uint32_t)p.k);
+    constexpr int BAND = CONV ? kFBand : kFBandNoConv;
+    const int r0 = band * BAND, rows = min(BAND, H - r0);
     const int64_t slot = sample_index(p.sp, none, b);
     int dy, dx;
     sample_offset(p.sp, none, t, b, dy, dx);
@@ -151,7 +157,7 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
     uintptr_t g0 = 0;
     m.gkoff = 0;
     if (kBank && want_aug) {
-      const int64_t j = kSplice ? ((int64_t)b * p.k + f) % p.sp.B : b;   // batch-tiled (splice) vs channel-tiled (overlay)
+      const int64_t j = kSplice ? (int64_t)(fr % (uint32_t)p.sp.B) : b;   // batch-tiled (splice) vs channel-tiled (overlay)
       int64_t row = p.bank_idx[j];
       row = row < 0 ? 0 : (row >= p.bank_len ? p.bank_len - 1 : row);
       const uint8_t* g = p.bank + row * 3 * P;
@@ -214,8 +220,7 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
 
     if (m.o_aug == nullptr) {
       // ---------------- copy unit (next_obs, or obs without an augmented output) ----------------
-      for (int task = tid; task < m.rows * nq; task += kFThreads) {
-        const int pr = task / nq, q4 = task - pr * nq;
+      for (int pr = active ? row0 : m.rows; pr < m.rows; pr += RPR) {
         const int r = m.r0 + pr;
         const size_t oo = (size_t)r * W + 4 * q4;
         uint32_t w[3];
@@ -237,8 +242,7 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
       const int co = tid / 27, tap = tid - co * 27;
       wsm[tap * 4 + co] = __fdiv_rn(p.weights[(int64_t)m.sample * 81 + tid], 255.0f);
     }
-    for (int task = tid; task < trows * nq; task += kFThreads) {
-      const int pr = task / nq, q4 = task - pr * nq;
+    for (int pr = active ? row0 : trows; pr < trows; pr += RPR) {
       const int r = clampi(m.r0 + pr - hal, 0, H - 1);
       const bool own = !CONV || (pr >= 1 && pr <= m.rows);   // halo rows only feed the conv tile
       const size_t oo = (size_t)r * W + 4 * q4;              // offset inside plane 0; planes are H*W apart
@@ -315,9 +319,8 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
     if (tid == 0 && kk + 2 < nun) issue(kk + 2, s);
     // ---------------- phase B: conv on the tile ----------------
     if (CONV) {
-      const int ntask = ((m.rows + 1) >> 1) * nq;
-      for (int task = tid; task < ntask; task += kFThreads) {
-        const int rp = task / nq, q4 = task - rp * nq;
+      const int npair = (m.rows + 1) >> 1;
+      for (int rp = active ? row0 : npair; rp < npair; rp += RPR) {
         const int r = rp * 2;
         float acc[2][3][4];
 #pragma unroll
@@ -471,7 +474,8 @@ extern "C" int augcl_ring_sample_fused(augcl_ring* r, const augcl_fused_desc* d,
   }
   p.alpha = d->alpha; p.oma = (float)(1.0 - (double)d->alpha);
   p.ops = ops; p.aug_shifted = d->aug_input == AUGCL_AUG_INPUT_SHIFTED ? 1 : 0;
-  p.k = r->k; p.bands = (r->H + kFBand - 1) / kFBand;
+  const int band = (ops & AUGCL_OP_CONV) ? kFBand : kFBandNoConv;
+  p.k = r->k; p.bands = (r->H + band - 1) / band;
   p.units_obs = any_obs ? (int64_t)B * r->k * p.bands : 0;
   p.units_next = any_next ? (int64_t)B * r->k * p.bands : 0;
   AUGCL_REQUIRE(p.units_obs + p.units_next < (1ll << 31), "%s: batch too large", who);
@@ -484,9 +488,9 @@ extern "C" int augcl_ring_sample_fused(augcl_ring* r, const augcl_fused_desc* d,
   if (!any_obs) p.cost_obs = 1;
   if (!any_next) p.cost_next = 1;
   p.normalize = d->normalize ? 1 : 0;
-  const int rows_max = (kFBand + 2 + d->pad) < r->H ? (kFBand + 2 + d->pad) : r->H;
+  const int rows_max = (band + 2 + d->pad) < r->H ? (band + 2 + d->pad) : r->H;
   p.plane_stage = ((rows_max * r->W + 30 + 15) & ~15) + 16;
-  p.bank_stage = (ops & 7) ? ((((kFBand + 2) * r->W + 30 + 15) & ~15) + 16) : 0;
+  p.bank_stage = (ops & 7) ? ((((band + 2) * r->W + 30 + 15) & ~15) + 16) : 0;
   p.stage_bytes = 3 * (p.plane_stage + p.bank_stage);
   p.tile_rs = (r->W + 8) & ~3;
   const size_t tile_bytes = (ops & AUGCL_OP_CONV) ? 3 * (size_t)(kFBand + 2) * p.tile_rs * sizeof(float) : 0;
@@ -534,7 +538,7 @@ extern "C" int augcl_ring_sample_fused(augcl_ring* r, const augcl_fused_desc* d,
     }
   }
 
-  const FusedKernel kern = pick_kernel(pre, (ops & AUGCL_OP_CONV) != 0, p.normalize != 0, r->W);
+  const FusedKernel kern = pick_kernel(pre, (ops & AUGCL_OP_CONV) != 0, p.normalize != 0, (r->H == 84 && r->W == 84) ? 84 : 0);
   {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);   // idempotent, ~1 us
     if (e != cudaSuccess) {
