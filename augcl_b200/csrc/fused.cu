@@ -22,11 +22,13 @@
 
 namespace augcl {
 
-std::atomic<int> g_fused_ctas_per_sm{6};
+std::atomic<int> g_fused_ctas_per_sm{0};   // 0 = auto
 std::atomic<int> g_fused_cost_obs{0};    // 0 = auto
 std::atomic<int> g_fused_cost_next{0};
+std::atomic<int> g_fused_stages{0};      // 0 = auto
 std::atomic<int> g_fused_fast_mask{1};   // 0: always the float HSV path (A/B and the exhaustive equivalence test)
 
+constexpr int kFHeader = 256 + 432;   // mbarriers + metas + conv weights
 constexpr int kFBand = 12;        // conv chains: 12 rows + 2 halo rows = 14 tile rows = two rounds of 7 rows
 constexpr int kFBandNoConv = 14;  // every other chain: 14 rows = two full rounds, 84 = 6 bands
 constexpr int kFThreads = 160;   // 147 = 7 rows x 21 quads work at W = 84: a 14-row tile is exactly two rounds
@@ -48,7 +50,7 @@ struct FusedParams {
   int k, bands;             // frames per stack, bands per frame
   int64_t units_obs, units_next;
   int cost_obs, cost_next;
-  int plane_stage, bank_stage, stage_bytes, tile_rs;
+  int plane_stage, bank_stage, stage_bytes, tile_rs, stages;
   int normalize;
 };
 
@@ -79,11 +81,12 @@ enum { kPreNone = 0, kPreSplice = 1, kPreSpliceFast = 2, kPreOverlay = 3 };
 template <int PRE, bool CONV, bool NORM, int WC>
 __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const __grid_constant__ FusedParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem);                 // 2 mbarriers
-  FusedMeta* meta = reinterpret_cast<FusedMeta*>(smem + 16);          // 2 metas (2 x 56 B -> 128 B reserved)
-  float* wsm = reinterpret_cast<float*>(smem + 144);                  // [27][4] conv weights / 255
-  uint8_t* stage = smem + 144 + 432;                                  // 2 x stage_bytes (576 = 16 * 36: 16-B aligned)
-  float* tile = reinterpret_cast<float*>(stage + 2 * p.stage_bytes);  // [3][kFBand+2][tile_rs]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem);                 // <= 4 mbarriers
+  FusedMeta* meta = reinterpret_cast<FusedMeta*>(smem + 32);          // <= 4 metas (4 x 56 B = 224 B)
+  float* wsm = reinterpret_cast<float*>(smem + 256);                  // [27][4] conv weights / 255
+  uint8_t* stage = smem + kFHeader;                                   // NS x stage_bytes (688 = 16 * 43: 16-B aligned)
+  const int NS = p.stages;
+  float* tile = reinterpret_cast<float*>(stage + NS * p.stage_bytes); // [3][kFBand+2][tile_rs]
   const int tid = threadIdx.x;
   const int H = WC ? WC : p.sp.H, W = WC ? WC : p.sp.W, nq = W >> 2;   // WC != 0: square WC x WC frames
   // fixed thread -> (row slot, 4-pixel group) mapping: no per-task division, constant address increments
@@ -108,8 +111,7 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
   const int nun = (int)(u1 - u0);
 
   if (tid == 0) {
-    mbar_init(&bars[0], 1);
-    mbar_init(&bars[1], 1);
+    for (int s = 0; s < NS; ++s) mbar_init(&bars[s], 1);
     mbar_fence_init();
   }
   __syncthreads();
@@ -181,13 +183,14 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
     }
   };
 
-  if (tid < 2 && tid < nun) issue(tid, tid);
+  if (tid < NS && tid < nun) issue(tid, tid);   // the prologue copies are prepared by NS lanes in parallel
   pdl_launch_dependents();
   gather_scalars(p.sp, none);
 
   uint32_t phase = 0;
+  int s = 0;
+  auto next_stage = [&]() { if (++s == NS) { s = 0; phase ^= 1; } };
   for (int kk = 0; kk < nun; ++kk) {
-    const int s = kk & 1;
     mbar_wait(&bars[s], phase);
     const FusedMeta m = meta[s];
     const uint8_t* sb = stage + (size_t)s * p.stage_bytes;
@@ -228,8 +231,8 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
         if (m.o_shift) { load_shift(r, q4, w); store3(m.o_shift, oo, w); }
       }
       __syncthreads();   // stage s consumed
-      if (tid == 0 && kk + 2 < nun) issue(kk + 2, s);
-      if (s == 1) phase ^= 1;
+      if (tid == 0 && kk + NS < nun) issue(kk + NS, s);
+      next_stage();
       continue;
     }
 
@@ -316,7 +319,7 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
       }
     }
     __syncthreads();   // stage s consumed (refill may start), tile + wsm complete
-    if (tid == 0 && kk + 2 < nun) issue(kk + 2, s);
+    if (tid == 0 && kk + NS < nun) issue(kk + NS, s);
     // ---------------- phase B: conv on the tile ----------------
     if (CONV) {
       const int npair = (m.rows + 1) >> 1;
@@ -367,7 +370,7 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
       }
       __syncthreads();   // tile and wsm are free again
     }
-    if (s == 1) phase ^= 1;
+    next_stage();
   }
 }
 
@@ -488,13 +491,19 @@ extern "C" int augcl_ring_sample_fused(augcl_ring* r, const augcl_fused_desc* d,
   if (!any_obs) p.cost_obs = 1;
   if (!any_next) p.cost_next = 1;
   p.normalize = d->normalize ? 1 : 0;
-  const int rows_max = (band + 2 + d->pad) < r->H ? (band + 2 + d->pad) : r->H;
+  const bool has_conv = (ops & AUGCL_OP_CONV) != 0;
+  const int halo2 = has_conv ? 2 : 0;
+  const int rows_max = (band + halo2 + d->pad) < r->H ? (band + halo2 + d->pad) : r->H;
   p.plane_stage = ((rows_max * r->W + 30 + 15) & ~15) + 16;
-  p.bank_stage = (ops & 7) ? ((((band + 2) * r->W + 30 + 15) & ~15) + 16) : 0;
+  p.bank_stage = (ops & 7) ? ((((band + halo2) * r->W + 30 + 15) & ~15) + 16) : 0;
   p.stage_bytes = 3 * (p.plane_stage + p.bank_stage);
   p.tile_rs = (r->W + 8) & ~3;
-  const size_t tile_bytes = (ops & AUGCL_OP_CONV) ? 3 * (size_t)(kFBand + 2) * p.tile_rs * sizeof(float) : 0;
-  const size_t smem = 576 + 2 * (size_t)p.stage_bytes + tile_bytes;
+  const size_t tile_bytes = has_conv ? 3 * (size_t)(kFBand + 2) * p.tile_rs * sizeof(float) : 0;
+  // conv chains are issue / barrier bound: 2 stages and the smaller footprint; elementwise chains wait on HBM: deeper
+  // (measured, scripts/bench_fused.py --opts: 4 stages x 6 CTAs/SM with a bank, 3 x 7 for plain copies)
+  p.stages = g_fused_stages.load() > 0 ? g_fused_stages.load() : (has_conv ? 2 : ((ops & 7) ? 4 : 3));
+  while (p.stages > 1 && kFHeader + (size_t)p.stages * p.stage_bytes + tile_bytes > 100 * 1024) --p.stages;
+  const size_t smem = kFHeader + (size_t)p.stages * p.stage_bytes + tile_bytes;
   if (smem > 200 * 1024) AUGCL_FAIL(AUGCL_ERR_UNSUPPORTED, "%s: geometry needs %zu B of shared memory", who, smem);
 
   DeviceGuard g(r->device);
@@ -547,6 +556,7 @@ extern "C" int augcl_ring_sample_fused(augcl_ring* r, const augcl_fused_desc* d,
     }
   }
   int per_sm = g_fused_ctas_per_sm.load();
+  if (per_sm <= 0) per_sm = ops == 0 ? 7 : 6;
   const int fit = (int)((228 * 1024) / (smem + 1024));
   if (per_sm > fit) per_sm = fit < 1 ? 1 : fit;
   int64_t grid = (int64_t)kNumSMs * per_sm;

@@ -14,6 +14,7 @@ extern std::atomic<int> g_fused_ctas_per_sm;   // fused.cu
 extern std::atomic<int> g_fused_cost_obs;
 extern std::atomic<int> g_fused_cost_next;
 extern std::atomic<int> g_fused_fast_mask;
+extern std::atomic<int> g_fused_stages;
 static thread_local std::string t_error;
 void set_error(const std::string& msg) { t_error = msg; }
 }  // namespace augcl
@@ -46,10 +47,15 @@ int augcl_set_option(const char* key, const char* value) {
   if (!strcmp(key, "sample_band")) { g_sample_band = atoi(value) != 0; return AUGCL_OK; }
   if (!strcmp(key, "fused_ctas_per_sm")) {
     int v = atoi(value);
-    AUGCL_REQUIRE(v >= 1 && v <= 16, "fused_ctas_per_sm must be in [1,16]");
+    AUGCL_REQUIRE(v >= 0 && v <= 16, "fused_ctas_per_sm must be in [0,16] (0 = auto)");
     g_fused_ctas_per_sm = v; return AUGCL_OK;
   }
   if (!strcmp(key, "fused_cost_obs")) { g_fused_cost_obs = atoi(value); return AUGCL_OK; }     // 0 = auto
+  if (!strcmp(key, "fused_stages")) {
+    int v = atoi(value);
+    AUGCL_REQUIRE(v >= 0 && v <= 4, "fused_stages must be in [0,4] (0 = auto)");
+    g_fused_stages = v; return AUGCL_OK;
+  }
   if (!strcmp(key, "fused_fast_mask")) { g_fused_fast_mask = atoi(value) != 0; return AUGCL_OK; }
   if (!strcmp(key, "fused_cost_next")) { g_fused_cost_next = atoi(value); return AUGCL_OK; }
   AUGCL_FAIL(AUGCL_ERR_BAD_ARG, "augcl_set_option: unknown key '%s'", key);

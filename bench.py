@@ -340,6 +340,68 @@ def batch_sweep(res, batches=(128, 256, 512, 1024, 2048, 4096, 8192, 16384)):
     return out
 
 
+def fused_configs(res):
+    """BASELINE.json configs[2] and configs[3] through the fused per-algorithm sampler (augcl_ring_sample_fused):
+    device-timed extras next to the bench line (configs[1] stays the headline workload)."""
+    import ctypes
+    import torch
+    from augcl_b200 import _lib as L, augmentations as A
+    buf, dev = res["buf"], res["dev"]
+    peak = load_peaks()[0]
+    A.load_dataloader(128, S, device=dev)
+    bank = A.get_background_bank()
+    F = 3 * S * S
+    cases = [("configs[2]: SVEA sample + random_shift + random_overlay(alpha 0.5) of the shifted obs, batch 256, "
+              "4096-row u8 background bank", 256, L.OP_OVERLAY, L.AUG_INPUT_SHIFTED, 2 * S8 + F + 3 * 4 * S8),
+             ("configs[3]: AugCL sample + random_shift + random_conv(splice(obs)), batch 128", 128,
+              L.OP_SPLICE | L.OP_CONV, L.AUG_INPUT_PLAIN, 2 * S8 + 3 * F + 3 * 4 * S8)]
+    g = torch.Generator().manual_seed(7)
+    stream = torch.cuda.current_stream(dev)
+    fn = L.lib().augcl_ring_sample_fused
+    out = []
+    for name, B, ops, aug_in, abytes in cases:
+        iters, n_sets, n_idx = 400, 8, 16
+        o = [torch.empty((3, B, C, S, S), device=dev) for _ in range(n_sets)]
+        idx = [torch.randint(0, CAP, (B,), generator=g).to(dev) for _ in range(n_idx)]
+        off = torch.randint(0, 2 * PAD + 1, (B, 2), generator=g, dtype=torch.int32).to(dev)
+        rows = torch.randint(0, bank.shape[0], (B,), generator=g).to(dev)
+        wts = torch.randn((B, 3, 3, 3, 3), generator=g).to(dev)
+        sc = torch.empty((B, A_DIM + 2), device=dev)
+        descs = []
+        for i in range(n_sets * n_idx):
+            d = L.FusedDesc()
+            d.struct_size = ctypes.sizeof(L.FusedDesc)
+            d.B, d.idx_src, d.off_src, d.idx = B, L.SRC_DEVICE, L.SRC_DEVICE, idx[i % n_idx].data_ptr()
+            d.off_obs, d.pad = off.data_ptr(), PAD
+            t = o[i % n_sets]
+            d.out_obs_shift, d.out_obs_aug, d.out_next = t[0].data_ptr(), t[1].data_ptr(), t[2].data_ptr()
+            d.out_act, d.out_rew, d.out_nd = sc.data_ptr(), sc.data_ptr() + 4 * B * A_DIM, sc.data_ptr() + 4 * B * (A_DIM + 1)
+            d.aug_input, d.aug_ops = aug_in, ops
+            d.bank, d.bank_len, d.bank_idx, d.conv_weights = bank.data_ptr(), bank.shape[0], rows.data_ptr(), wts.data_ptr()
+            d.hue_thres, d.sat_thres, d.val_thres, d.alpha = 0.0, 0.0, 0.6, 0.5
+            descs.append(d)
+
+        def step(t):
+            if fn(buf._ring, ctypes.byref(descs[t % len(descs)]), stream.cuda_stream):
+                raise RuntimeError(L.lib().augcl_last_error().decode())
+        for t in range(5):
+            step(t)
+        torch.cuda.synchronize(dev)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for t in range(iters):
+            step(t)
+        e1.record(stream)
+        torch.cuda.synchronize(dev)
+        us = e0.elapsed_time(e1) * 1e3 / iters
+        gbs = B * abytes / us / 1e3
+        out.append({"workload": name, "batch": B, "us_per_step": round(us, 2), "samples_per_s": round(B / us * 1e6),
+                    "algorithmic_bytes_per_sample": abytes, "GB/s": round(gbs, 1), "frac": round(gbs / peak, 4),
+                    "kernel": "ring_sample_fused_kernel", "launches_per_step": 1})
+        del o
+    return out
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.isfile(p):
@@ -375,6 +437,7 @@ def main():
         }
         if world == 1 and not args.no_sweep:
             line["batch_sweep"] = batch_sweep(res)
+            line["fused_configs"] = fused_configs(res)
         if world == 1 and not args.no_cpu_baseline:
             cores = os.cpu_count() or 1
             torch.set_num_threads(cores)
