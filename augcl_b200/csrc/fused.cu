@@ -150,7 +150,7 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
     m.o_shift = want_shift ? p.o_shift[t] + fo : nullptr;
     m.o_aug = want_aug ? p.o_aug + fo : nullptr;
     m.dy = dy; m.dx = dx; m.r0 = r0; m.rows = rows; m.sample = b; m.pad_ = 0;
-    const uint8_t* src = p.sp.store[t] + (slot * p.sp.C + (int64_t)f * 3) * P;   // plane 0 of the frame
+    const uint8_t* src = plane_ptr(p.sp, t, slot, f * 3, P);   // plane 0 of the frame (its 3 planes are contiguous)
     const uintptr_t a0 = reinterpret_cast<uintptr_t>(src + (int64_t)lo * W) & ~(uintptr_t)15;
     const uintptr_t a1 = (reinterpret_cast<uintptr_t>(src + (int64_t)(hi + 1) * W) + 15) & ~(uintptr_t)15;
     m.koff = (int)((intptr_t)reinterpret_cast<uintptr_t>(src) - (intptr_t)a0);
@@ -440,7 +440,7 @@ extern "C" int augcl_ring_sample_fused(augcl_ring* r, const augcl_fused_desc* d,
 
   FusedParams p{};
   SampleParams& sp = p.sp;
-  sp.store[0] = r->obs; sp.store[1] = r->next;
+  sp.store[0] = r->obs; sp.store[1] = r->next; sp.refs = r->dedup ? r->refs : nullptr; sp.k = r->k; sp.cpf = r->cpf;
   sp.idx = d->idx; sp.act = r->act; sp.rew = r->rew; sp.nd = r->nd;
   sp.out_act = d->out_act; sp.out_rew = d->out_rew; sp.out_nd = d->out_nd;
   sp.capacity = r->capacity;

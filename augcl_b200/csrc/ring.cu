@@ -54,7 +54,7 @@ __global__ void __launch_bounds__(256, 6) ring_sample_tma_kernel(const SamplePar
     const int slot = bt % p.nt, b = bt / p.nt;
     const int t = p.tmap[slot];
     const int64_t row = sample_index(p, none, b);
-    const uint8_t* src = p.store[t] + (row * p.C + ch) * (int64_t)P;
+    const uint8_t* src = plane_ptr(p, t, row, ch, (int64_t)P);
     const uintptr_t a = reinterpret_cast<uintptr_t>(src);
     const int lead = (int)(a & 15);
     const uint32_t bytes = (uint32_t)((lead + P + 15) & ~15);
@@ -169,7 +169,7 @@ __global__ void __launch_bounds__(256, 6) ring_sample_band_kernel(const SamplePa
     const int64_t rem = u1 - plane * NIT;
     const int it_hi = rem < NIT ? (int)rem : NIT;
     const int row_lo = clampi(it_lo * RPI + dy, 0, H - 1), row_hi = clampi(it_hi * RPI - 1 + dy, 0, H - 1);
-    const uint8_t* src = p.store[t] + (row * p.C + ch) * (int64_t)P;
+    const uint8_t* src = plane_ptr(p, t, row, ch, (int64_t)P);
     const uintptr_t a0 = reinterpret_cast<uintptr_t>(src + row_lo * W) & ~(uintptr_t)15;
     const uintptr_t a1 = (reinterpret_cast<uintptr_t>(src + (row_hi + 1) * W) + 15) & ~(uintptr_t)15;
     BandMeta m;
@@ -233,7 +233,7 @@ __global__ void __launch_bounds__(256) ring_sample_generic_kernel(const SamplePa
     sample_offset(p, none, t, b, dy, dx);
     const int rr = clampi(r + dy, 0, p.H - 1), cc = clampi(q + dx, 0, p.W - 1);
     const int64_t row = sample_index(p, none, b);
-    float v = (float)p.store[t][((row * p.C + ch) * p.H + rr) * (int64_t)p.W + cc];
+    float v = (float)plane_ptr(p, t, row, ch, (int64_t)p.H * p.W)[rr * p.W + cc];
     if (p.normalize) v = __fdiv_rn(v, 255.0f);
     p.out[t][(((int64_t)b * p.C + ch) * p.Ho + r) * p.Wo + q] = v;
   }
@@ -243,6 +243,14 @@ __global__ void __launch_bounds__(256) ring_sample_generic_kernel(const SamplePa
 __global__ void __launch_bounds__(256) fill_bytes_kernel(uint4* dst, int64_t nblk, uint64_t seed, uint64_t subseq) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nblk; i += (int64_t)gridDim.x * blockDim.x)
     dst[i] = philox4x32_10((uint64_t)i, subseq, seed);
+}
+
+__global__ void __launch_bounds__(256) fill_refs_window_kernel(int32_t* refs, int64_t count, int k, int64_t pool) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count * 2 * k; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t slot = i / (2 * k);
+    const int j = (int)(i - slot * 2 * k), t = j / k, f = j - t * k;
+    refs[i] = (int32_t)((slot + t + f) % pool);
+  }
 }
 
 __global__ void __launch_bounds__(256) fill_scalars_kernel(float* act, float* rew, float* nd, int64_t count, int A,
@@ -264,45 +272,63 @@ using namespace augcl;
 
 extern "C" {
 
-int augcl_ring_create(augcl_ring** out, int device, int64_t capacity, int k, int c_per_frame, int H, int W,
-                      int action_dim) {
-  AUGCL_REQUIRE(out, "augcl_ring_create: out is NULL");
+static int ring_create_impl(const char* who, augcl_ring** out, int device, int64_t capacity, int k, int c_per_frame, int H,
+                            int W, int action_dim, int64_t pool_frames) {
+  AUGCL_REQUIRE(out, "%s: out is NULL", who);
   *out = nullptr;
   AUGCL_REQUIRE(capacity > 0 && k > 0 && c_per_frame > 0 && H > 0 && W > 0 && action_dim > 0,
-                "augcl_ring_create: capacity, k, c_per_frame, H, W, action_dim must be positive");
-  AUGCL_REQUIRE((int64_t)H * W < (1 << 24), "augcl_ring_create: frame plane too large");
+                "%s: capacity, k, c_per_frame, H, W, action_dim must be positive", who);
+  AUGCL_REQUIRE((int64_t)H * W < (1 << 24), "%s: frame plane too large", who);
+  const bool dedup = pool_frames >= 0;
+  if (dedup) AUGCL_REQUIRE(pool_frames > k && pool_frames < (1ll << 31), "%s: pool_frames must be in (k, 2^31)", who);
   int ndev = 0;
   AUGCL_CUDA(cudaGetDeviceCount(&ndev));
-  AUGCL_REQUIRE(device >= 0 && device < ndev, "augcl_ring_create: device %d out of range (%d devices)", device, ndev);
+  AUGCL_REQUIRE(device >= 0 && device < ndev, "%s: device %d out of range (%d devices)", who, device, ndev);
   DeviceGuard g(device);
   AUGCL_CUDA(g.err);
   augcl_ring* r = new augcl_ring();
   r->device = device; r->capacity = capacity; r->k = k; r->cpf = c_per_frame;
   r->C = k * c_per_frame; r->H = H; r->W = W; r->A = action_dim;
   r->stack_bytes = (int64_t)r->C * H * W;
-  const int64_t store = ((capacity * r->stack_bytes + 255) / 256) * 256 + 256;  // slack: bulk copies round up to 16 B
+  r->dedup = dedup ? 1 : 0; r->pool = dedup ? pool_frames : 0;
+  const int64_t frame_bytes = (int64_t)c_per_frame * H * W;
+  const int64_t payload = dedup ? pool_frames * frame_bytes : capacity * r->stack_bytes;
+  const int64_t store = ((payload + 255) / 256) * 256 + 256;  // slack: bulk copies round up to 16 B
   const int64_t fbytes = capacity * (int64_t)sizeof(float);
-  r->bytes = 2 * store + fbytes * (action_dim + 2);
+  const int64_t rbytes = dedup ? capacity * 2 * k * (int64_t)sizeof(int32_t) : 0;
+  r->bytes = (dedup ? 1 : 2) * store + rbytes + fbytes * (action_dim + 2);
   cudaError_t e = cudaMalloc(&r->obs, store);
-  if (e == cudaSuccess) e = cudaMalloc(&r->next, store);
+  if (e == cudaSuccess && !dedup) e = cudaMalloc(&r->next, store);
+  if (e == cudaSuccess && dedup) e = cudaMalloc(&r->refs, rbytes);
+  if (e == cudaSuccess && dedup) e = cudaMemset(r->refs, 0, rbytes);     // every slot points at pool frame 0 until written
   if (e == cudaSuccess) e = cudaMalloc(&r->act, fbytes * action_dim);
   if (e == cudaSuccess) e = cudaMalloc(&r->rew, fbytes);
   if (e == cudaSuccess) e = cudaMalloc(&r->nd, fbytes);
   if (e != cudaSuccess) {
-    cudaFree(r->obs); cudaFree(r->next); cudaFree(r->act); cudaFree(r->rew); cudaFree(r->nd);
+    cudaFree(r->obs); cudaFree(r->next); cudaFree(r->refs); cudaFree(r->act); cudaFree(r->rew); cudaFree(r->nd);
     delete r;
     cudaGetLastError();
-    AUGCL_FAIL(AUGCL_ERR_OOM, "augcl_ring_create: cudaMalloc of %lld bytes failed: %s", (long long)(2 * store),
+    AUGCL_FAIL(AUGCL_ERR_OOM, "%s: cudaMalloc of %lld bytes failed: %s", who, (long long)((dedup ? 1 : 2) * store + rbytes),
                cudaGetErrorString(e));
   }
   *out = r;
   return AUGCL_OK;
 }
 
+int augcl_ring_create(augcl_ring** out, int device, int64_t capacity, int k, int c_per_frame, int H, int W,
+                      int action_dim) {
+  return ring_create_impl("augcl_ring_create", out, device, capacity, k, c_per_frame, H, W, action_dim, -1);
+}
+
+int augcl_ring_create_dedup(augcl_ring** out, int device, int64_t capacity, int k, int c_per_frame, int H, int W,
+                            int action_dim, int64_t pool_frames) {
+  return ring_create_impl("augcl_ring_create_dedup", out, device, capacity, k, c_per_frame, H, W, action_dim, pool_frames);
+}
+
 int augcl_ring_destroy(augcl_ring* r) {
   if (!r) return AUGCL_OK;
   DeviceGuard g(r->device);
-  cudaFree(r->obs); cudaFree(r->next); cudaFree(r->act); cudaFree(r->rew); cudaFree(r->nd);
+  cudaFree(r->obs); cudaFree(r->next); cudaFree(r->refs); cudaFree(r->act); cudaFree(r->rew); cudaFree(r->nd);
   delete r;
   return AUGCL_OK;
 }
@@ -316,6 +342,9 @@ static int ring_copy(augcl_ring* r, int64_t slot0, int64_t count, bool put, uint
                 "%s: slots [%lld, %lld) outside capacity %lld", who, (long long)slot0, (long long)(slot0 + count),
                 (long long)r->capacity);
   if (count == 0) return AUGCL_OK;
+  if (r->dedup && (obs || next))
+    AUGCL_FAIL(AUGCL_ERR_UNSUPPORTED, "%s: a de-duplicated ring holds frames, not stacks: use augcl_ring_put_frames / "
+               "augcl_ring_put_refs (writes) or augcl_ring_sample (reads)", who);
   DeviceGuard g(r->device);
   AUGCL_CUDA(g.err);
   auto cp = [&](void* ring_ptr, void* user, size_t bytes) -> cudaError_t {
@@ -323,8 +352,10 @@ static int ring_copy(augcl_ring* r, int64_t slot0, int64_t count, bool put, uint
     return put ? cudaMemcpyAsync(ring_ptr, user, bytes, cudaMemcpyDefault, st)
                : cudaMemcpyAsync(user, ring_ptr, bytes, cudaMemcpyDefault, st);
   };
-  AUGCL_CUDA(cp(r->obs + slot0 * r->stack_bytes, obs, (size_t)(count * r->stack_bytes)));
-  AUGCL_CUDA(cp(r->next + slot0 * r->stack_bytes, next, (size_t)(count * r->stack_bytes)));
+  if (!r->dedup) {
+    AUGCL_CUDA(cp(r->obs + slot0 * r->stack_bytes, obs, (size_t)(count * r->stack_bytes)));
+    AUGCL_CUDA(cp(r->next + slot0 * r->stack_bytes, next, (size_t)(count * r->stack_bytes)));
+  }
   AUGCL_CUDA(cp(r->act + slot0 * r->A, act, (size_t)(count * r->A) * sizeof(float)));
   AUGCL_CUDA(cp(r->rew + slot0, rew, (size_t)count * sizeof(float)));
   AUGCL_CUDA(cp(r->nd + slot0, nd, (size_t)count * sizeof(float)));
@@ -344,6 +375,45 @@ int augcl_ring_get(augcl_ring* r, int64_t slot0, int64_t count, uint8_t* obs, ui
                    "augcl_ring_get");
 }
 
+int augcl_ring_put_frames(augcl_ring* r, int64_t frame0, int64_t count, const uint8_t* frames, augcl_stream stream) {
+  AUGCL_REQUIRE(r && r->dedup, "augcl_ring_put_frames: needs a ring made by augcl_ring_create_dedup");
+  AUGCL_REQUIRE(frame0 >= 0 && count >= 0 && frame0 + count <= r->pool, "augcl_ring_put_frames: frames [%lld, %lld) outside the pool of %lld",
+                (long long)frame0, (long long)(frame0 + count), (long long)r->pool);
+  if (count == 0) return AUGCL_OK;
+  AUGCL_REQUIRE(frames, "augcl_ring_put_frames: frames is NULL");
+  DeviceGuard g(r->device);
+  AUGCL_CUDA(g.err);
+  const int64_t fb = (int64_t)r->cpf * r->H * r->W;
+  AUGCL_CUDA(cudaMemcpyAsync(r->obs + frame0 * fb, frames, (size_t)(count * fb), cudaMemcpyDefault, (cudaStream_t)stream));
+  return AUGCL_OK;
+}
+
+int augcl_ring_put_refs(augcl_ring* r, int64_t slot0, int64_t count, const int32_t* refs, const float* actions,
+                        const float* rewards, const float* not_dones, augcl_stream stream) {
+  AUGCL_REQUIRE(r && r->dedup, "augcl_ring_put_refs: needs a ring made by augcl_ring_create_dedup");
+  AUGCL_REQUIRE(slot0 >= 0 && count >= 0 && slot0 + count <= r->capacity, "augcl_ring_put_refs: slots [%lld, %lld) outside capacity %lld",
+                (long long)slot0, (long long)(slot0 + count), (long long)r->capacity);
+  if (count == 0) return AUGCL_OK;
+  DeviceGuard g(r->device);
+  AUGCL_CUDA(g.err);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (refs) {
+    cudaPointerAttributes at{};
+    const bool host = cudaPointerGetAttributes(&at, refs) != cudaSuccess || at.type == cudaMemoryTypeUnregistered ||
+                      at.type == cudaMemoryTypeHost;
+    cudaGetLastError();
+    if (host)
+      for (int64_t e = 0; e < count * 2 * r->k; ++e)
+        AUGCL_REQUIRE(refs[e] >= 0 && refs[e] < r->pool, "augcl_ring_put_refs: frame reference %d (element %lld) outside the pool of %lld",
+                      refs[e], (long long)e, (long long)r->pool);
+    AUGCL_CUDA(cudaMemcpyAsync(r->refs + slot0 * 2 * r->k, refs, (size_t)(count * 2 * r->k) * sizeof(int32_t), cudaMemcpyDefault, st));
+  }
+  if (actions) AUGCL_CUDA(cudaMemcpyAsync(r->act + slot0 * r->A, actions, (size_t)(count * r->A) * sizeof(float), cudaMemcpyDefault, st));
+  if (rewards) AUGCL_CUDA(cudaMemcpyAsync(r->rew + slot0, rewards, (size_t)count * sizeof(float), cudaMemcpyDefault, st));
+  if (not_dones) AUGCL_CUDA(cudaMemcpyAsync(r->nd + slot0, not_dones, (size_t)count * sizeof(float), cudaMemcpyDefault, st));
+  return AUGCL_OK;
+}
+
 int augcl_ring_fill_synthetic(augcl_ring* r, int64_t count, uint64_t seed, augcl_stream stream) {
   AUGCL_REQUIRE(r, "augcl_ring_fill_synthetic: ring is NULL");
   AUGCL_REQUIRE(count >= 0 && count <= r->capacity, "augcl_ring_fill_synthetic: count out of range");
@@ -351,11 +421,21 @@ int augcl_ring_fill_synthetic(augcl_ring* r, int64_t count, uint64_t seed, augcl
   DeviceGuard g(r->device);
   AUGCL_CUDA(g.err);
   cudaStream_t st = (cudaStream_t)stream;
-  const int64_t nblk = (count * r->stack_bytes + 15) / 16;  // store has >= 256 B of slack
-  fill_bytes_kernel<<<kNumSMs * 8, 256, 0, st>>>(reinterpret_cast<uint4*>(r->obs), nblk, seed, 0);
-  AUGCL_LAUNCHED();
-  fill_bytes_kernel<<<kNumSMs * 8, 256, 0, st>>>(reinterpret_cast<uint4*>(r->next), nblk, seed, 1);
-  AUGCL_LAUNCHED();
+  if (r->dedup) {
+    // the whole pool gets Philox bytes; slot i references frames i .. i+k-1 (obs) and i+1 .. i+k (next_obs), modulo the
+    // pool: the sliding window a FrameStack environment produces
+    const int64_t nblk = (r->pool * r->cpf * r->H * r->W + 15) / 16;
+    fill_bytes_kernel<<<kNumSMs * 8, 256, 0, st>>>(reinterpret_cast<uint4*>(r->obs), nblk, seed, 0);
+    AUGCL_LAUNCHED();
+    fill_refs_window_kernel<<<kNumSMs * 2, 256, 0, st>>>(r->refs, count, r->k, r->pool);
+    AUGCL_LAUNCHED();
+  } else {
+    const int64_t nblk = (count * r->stack_bytes + 15) / 16;  // store has >= 256 B of slack
+    fill_bytes_kernel<<<kNumSMs * 8, 256, 0, st>>>(reinterpret_cast<uint4*>(r->obs), nblk, seed, 0);
+    AUGCL_LAUNCHED();
+    fill_bytes_kernel<<<kNumSMs * 8, 256, 0, st>>>(reinterpret_cast<uint4*>(r->next), nblk, seed, 1);
+    AUGCL_LAUNCHED();
+  }
   fill_scalars_kernel<<<kNumSMs * 2, 256, 0, st>>>(r->act, r->rew, r->nd, count, r->A, seed);
   AUGCL_LAUNCHED();
   return AUGCL_OK;
@@ -382,7 +462,7 @@ static int sample_impl(const char* who, augcl_ring* r, int idx_src, const int64_
   else
     AUGCL_REQUIRE(idx, "%s: idx is NULL", who);
   SampleParams p{};
-  p.store[0] = r->obs; p.store[1] = r->next;
+  p.store[0] = r->obs; p.store[1] = r->next; p.refs = r->dedup ? r->refs : nullptr; p.k = r->k; p.cpf = r->cpf;
   p.out[0] = out_obs; p.out[1] = out_next;
   p.idx = idx; p.act = r->act; p.rew = r->rew; p.nd = r->nd;
   p.out_act = out_act; p.out_rew = out_rew; p.out_nd = out_nd;

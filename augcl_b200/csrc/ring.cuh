@@ -21,12 +21,19 @@ struct augcl_ring {
   float* rew;
   float* nd;
   int64_t bytes;
+  // "v2" (de-duplicated) layout: obs = frame pool [pool][cpf][H][W] u8, next = NULL,
+  // refs[capacity][2][k] = pool slot of every frame of (obs, next_obs)
+  int dedup;
+  int64_t pool;
+  int32_t* refs;
 };
 
 namespace augcl {
 
 struct SampleParams {
-  const uint8_t* store[2];
+  const uint8_t* store[2];   // v1: obs / next_obs stacks; v2: store[0] = frame pool
+  const int32_t* refs;       // v2: [capacity][2][k] pool slots (NULL = v1)
+  int k, cpf;
   float* out[2];
   const int32_t* off[2];
   const int64_t* idx;
@@ -125,6 +132,16 @@ __device__ __forceinline__ void gather_scalars(const SampleParams& p, const Inl&
       if (p.out_nd) p.out_nd[b] = p.nd[s];
     }
   }
+}
+
+// First byte of u8 plane `ch` of tensor t (0 obs, 1 next_obs) of ring slot `row`; P = H*W.
+__device__ __forceinline__ const uint8_t* plane_ptr(const SampleParams& p, int t, int64_t row, int ch, int64_t P) {
+  if (p.refs) {   // v2: one dependent 4-byte load (L2-resident table) resolves the frame
+    const int f = ch / p.cpf;
+    const int64_t fs = p.refs[(row * 2 + t) * p.k + f];
+    return p.store[0] + (fs * p.cpf + (ch - f * p.cpf)) * P;
+  }
+  return p.store[t] + (row * p.C + ch) * P;
 }
 
 __device__ __forceinline__ float4 finish(uint32_t w, int normalize) {

@@ -11,6 +11,7 @@ shift / crop on the way out.  No CPU path: the CUDA library is required.
 """
 from __future__ import annotations
 
+import collections
 import ctypes as C
 import os
 
@@ -76,7 +77,7 @@ class ReplayBuffer(object):
     STAGE = 256  # transitions staged in pinned host memory between flushes to the ring
 
     def __init__(self, obs_shape, action_shape, capacity, batch_size, prefill=True, *, device=None,
-                 frame_channels=3):
+                 frame_channels=3, dedup=False, pool_factor=1.25):
         # `prefill` only reserved host memory in the reference (src/utils.py:127-133,143-145); the ring
         # is allocated up front, so the flag is accepted and has nothing left to do.
         if not torch.cuda.is_available():
@@ -103,15 +104,38 @@ class ReplayBuffer(object):
         self.refilled = False
 
         h_ring = C.c_void_p()
-        L.call("augcl_ring_create", C.byref(h_ring), self._dev_index, self.capacity, c // frame_channels,
-               frame_channels, h, w, self.action_dim)
+        k = c // frame_channels
+        self._k = k
+        self.dedup = bool(dedup)
+        n = min(self.STAGE, self.capacity)
+        if self.dedup:
+            # "v2" layout (include/augcl_b200.h): one copy of every distinct frame + 2k references per transition,
+            # the sharing LazyFrames / FrameStack have on the host (src/utils.py:283-322, src/env/wrappers.py:183-203)
+            self._pool = int(self.capacity * float(pool_factor)) + 4 * k + 16
+            L.call("augcl_ring_create_dedup", C.byref(h_ring), self._dev_index, self.capacity, k, frame_channels, h, w,
+                   self.action_dim, self._pool)
+            self._pool_cur = 0                 # next pool slot to allocate
+            self._adds = 0                     # transitions added so far
+            self._slot_last_use = np.full(self._pool, -(1 << 62), dtype=np.int64)   # add number of the newest referrer
+            self._recent = collections.OrderedDict()   # id(frame) -> (frame, pool slot): the last few distinct frames
+            self._recent_max = 4 * k + 8
+            self._sealed = False
+            self._st_frames = torch.empty((n * 2 * k, frame_channels, h, w), dtype=torch.uint8).pin_memory()
+            self._st_frames_np = self._st_frames.numpy()
+            self._st_refs = torch.empty((n, 2, k), dtype=torch.int32).pin_memory()
+            self._st_refs_np = self._st_refs.numpy()
+            self._st_nframes = 0
+            self._st_frame0 = 0                # pool slot of staged frame 0
+        else:
+            L.call("augcl_ring_create", C.byref(h_ring), self._dev_index, self.capacity, k, frame_channels, h, w,
+                   self.action_dim)
+            self._st_obs = torch.empty((n, c, h, w), dtype=torch.uint8).pin_memory()
+            self._st_next = torch.empty((n, c, h, w), dtype=torch.uint8).pin_memory()
+            self._st_obs_np, self._st_next_np = self._st_obs.numpy(), self._st_next.numpy()
+        self._st_cap = n
         self._ring = h_ring
         self._fn_sample = L.lib().augcl_ring_sample_ex
         self._stack_bytes = c * h * w
-        n = min(self.STAGE, self.capacity)
-        self._st_obs = torch.empty((n, c, h, w), dtype=torch.uint8).pin_memory()
-        self._st_next = torch.empty((n, c, h, w), dtype=torch.uint8).pin_memory()
-        self._st_obs_np, self._st_next_np = self._st_obs.numpy(), self._st_next.numpy()
         self._st_start = 0      # ring slot of staged transition 0
         self._st_count = 0
         self._st_event = None   # completion of the last flush (staging must not be overwritten before)
@@ -133,16 +157,74 @@ class ReplayBuffer(object):
                 self._st_event = None
             self._st_start = self.idx
         j = self._st_count
-        self._st_obs_np[j] = np.asarray(obs)
-        self._st_next_np[j] = np.asarray(next_obs)
+        if self.dedup:
+            self._stage_frames(j, obs, next_obs)
+        else:
+            self._st_obs_np[j] = np.asarray(obs)
+            self._st_next_np[j] = np.asarray(next_obs)
         np.copyto(self.actions[self.idx], action)
         np.copyto(self.rewards[self.idx], reward)
         np.copyto(self.not_dones[self.idx], not done)
         self._st_count += 1
         self.idx = (self.idx + 1) % self.capacity
         self.full = self.full or self.idx == 0
-        if self._st_count == self._st_obs.shape[0] or self.idx == 0:   # staging full, or about to wrap
+        if self._st_count == self._st_cap or self.idx == 0:   # staging full, or about to wrap
             self._flush()
+
+    # ---- de-duplicated ingest -------------------------------------------------------------------------
+    def _frames_of(self, x):
+        """The k frame arrays of an observation.  LazyFrames hands out its (shared) frame objects; anything else is
+        split into k views, which are never shared (every add then uploads 2k frames)."""
+        fr = getattr(x, "_frames", None)
+        if fr is not None and len(fr) == self._k:
+            return fr
+        a = np.asarray(x)
+        cpf = self._frame_channels
+        return [a[i * cpf:(i + 1) * cpf] for i in range(self._k)]
+
+    def _stage_frames(self, j, obs, next_obs):
+        """Resolve the 2k frames of one transition to pool slots (frames seen in the last few adds are shared BY OBJECT
+        IDENTITY, like the reference's LazyFrames), stage the new ones, record the references."""
+        if self._sealed:
+            raise RuntimeError("ReplayBuffer(dedup=True): add() after fill_synthetic() is not supported")
+        k = self._k
+        if self._pool_cur + 2 * k > self._pool:      # keep the staged frames one contiguous pool range
+            self._flush_frames()
+            self._pool_cur = 0
+        refs = self._st_refs_np[j]
+        recent = self._recent
+        for t, x in enumerate((obs, next_obs)):
+            for f, fr in enumerate(self._frames_of(x)):
+                ent = recent.get(id(fr))
+                if ent is not None and ent[0] is fr:
+                    slot = ent[1]
+                else:
+                    slot = self._pool_cur
+                    if self._slot_last_use[slot] > self._adds - self.capacity:
+                        raise RuntimeError(
+                            f"ReplayBuffer(dedup=True): frame pool of {self._pool} exhausted (consecutive adds share too few "
+                            "frame objects); raise pool_factor or use dedup=False")
+                    if self._st_nframes == 0:
+                        self._st_frame0 = slot
+                    self._st_frames_np[self._st_nframes] = fr
+                    self._st_nframes += 1
+                    self._pool_cur += 1
+                    recent[id(fr)] = (fr, slot)
+                    if len(recent) > self._recent_max:
+                        recent.popitem(last=False)
+                refs[t, f] = slot
+                self._slot_last_use[slot] = self._adds
+        self._adds += 1
+
+    def _flush_frames(self):
+        n = self._st_nframes
+        if n:
+            L.call("augcl_ring_put_frames", self._ring, self._st_frame0, n, self._st_frames.data_ptr(), self._stream())
+            self._st_nframes = 0
+            # frames staged from here on must not overwrite pinned memory the copy above still reads
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream(self.device))
+            ev.synchronize()
 
     def _stream(self):
         return torch.cuda.current_stream(self.device).cuda_stream
@@ -154,9 +236,17 @@ class ReplayBuffer(object):
             return
         s0 = self._st_start
         a = np.ascontiguousarray(self.actions[s0:s0 + n]).reshape(n, -1)
-        L.call("augcl_ring_put", self._ring, s0, n, self._st_obs.data_ptr(), self._st_next.data_ptr(),
-               a.ctypes.data, self.rewards[s0:s0 + n].ctypes.data, self.not_dones[s0:s0 + n].ctypes.data,
-               self._stream())
+        if self.dedup:
+            if self._st_nframes:
+                L.call("augcl_ring_put_frames", self._ring, self._st_frame0, self._st_nframes, self._st_frames.data_ptr(),
+                       self._stream())
+                self._st_nframes = 0
+            L.call("augcl_ring_put_refs", self._ring, s0, n, self._st_refs.data_ptr(), a.ctypes.data,
+                   self.rewards[s0:s0 + n].ctypes.data, self.not_dones[s0:s0 + n].ctypes.data, self._stream())
+        else:
+            L.call("augcl_ring_put", self._ring, s0, n, self._st_obs.data_ptr(), self._st_next.data_ptr(),
+                   a.ctypes.data, self.rewards[s0:s0 + n].ctypes.data, self.not_dones[s0:s0 + n].ctypes.data,
+                   self._stream())
         # the scalar sources are pageable (copied synchronously by the driver); the frame staging is pinned
         ev = torch.cuda.Event()
         ev.record(torch.cuda.current_stream(self.device))
@@ -457,6 +547,13 @@ class ReplayBuffer(object):
         n = end - start
         obs = np.empty((n, c, h, w), dtype=np.uint8)
         nxt = np.empty((n, c, h, w), dtype=np.uint8)
+        if self.dedup:      # no stacks in HBM to copy out: gather them with the sample kernel (exact u8 -> f32 -> u8)
+            for s0 in range(0, n, 256):
+                m = min(256, n - s0)
+                o, _, _, no, _ = self._sample(np.arange(start + s0, start + s0 + m), scalars=False)
+                obs[s0:s0 + m] = o.to(torch.uint8).cpu().numpy()
+                nxt[s0:s0 + m] = no.to(torch.uint8).cpu().numpy()
+            return obs, nxt
         blk = min(self.IO_BLOCK, max(n, 1))
         po = torch.empty((blk, c, h, w), dtype=torch.uint8).pin_memory()
         pn = torch.empty((blk, c, h, w), dtype=torch.uint8).pin_memory()
@@ -511,6 +608,24 @@ class ReplayBuffer(object):
             self.actions[start:end] = payload[1]
             self.rewards[start:end] = payload[2]
             self.not_dones[start:end] = payload[3]
+            if self.dedup:
+                # the chunk's LazyFrames share frame objects exactly as they did when saved (pickle keeps identity):
+                # replay them through the ingest path, which de-duplicates by identity
+                for i, (o, no) in enumerate(pairs):
+                    if self._st_count == 0:
+                        if self._st_event is not None:
+                            self._st_event.synchronize()
+                            self._st_event = None
+                        self._st_start = start + i
+                    self._stage_frames(self._st_count, o, no)
+                    self._st_count += 1
+                    if self._st_count == self._st_cap:
+                        self._flush()
+                self._flush()
+                self.idx = end
+                if end == end_step:
+                    break
+                continue
             blk = min(self.IO_BLOCK, max(n, 1))
             po = torch.empty((blk, c, h, w), dtype=torch.uint8).pin_memory()
             pn = torch.empty((blk, c, h, w), dtype=torch.uint8).pin_memory()
@@ -535,6 +650,10 @@ class ReplayBuffer(object):
         """Benchmarks/tests: fill slots [0,count) with Philox frames and scalars on the device."""
         count = self.capacity if count is None else int(count)
         self._flush()
+        if self.dedup:
+            if count + self._k > self._pool:
+                raise ValueError("fill_synthetic: the frame pool is smaller than count + k")
+            self._sealed = True        # the pool now holds a synthetic sliding window the host bookkeeping does not track
         L.call("augcl_ring_fill_synthetic", self._ring, count, int(seed), self._stream())
         n = count
         a = np.empty((n, self.action_dim), dtype=np.float32)

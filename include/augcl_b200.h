@@ -91,6 +91,26 @@ int augcl_ring_put(augcl_ring* ring, int64_t slot0, int64_t count, const uint8_t
 /* Inverse of put (drain for ReplayBuffer.save, src/utils.py:156-170).  NULL pointers are skipped. */
 int augcl_ring_get(augcl_ring* ring, int64_t slot0, int64_t count, uint8_t* obs, uint8_t* next_obs,
                    float* actions, float* rewards, float* not_dones, augcl_stream stream);
+/* De-duplicated ring ("v2" layout).  The reference stores transitions as (LazyFrames, LazyFrames) whose frame arrays are
+ * SHARED between obs / next_obs and between consecutive steps (FrameStack, src/env/wrappers.py:183-203; LazyFrames,
+ * src/utils.py:283-322): 2k references per transition, ~1 new frame.  This layout keeps that sharing on the device:
+ *   frames[pool_frames][c_per_frame][H][W] u8   (one copy of every distinct frame)
+ *   refs[capacity][2][k] int32                   (pool slot of each frame of obs / next_obs)
+ * 100 000 transitions of 9x84x84 take ~2.1 GB instead of 12.7 GB and an env step uploads one 21 KB frame instead of two
+ * 63 KB stacks; a sample reads k+1 distinct frames (the second read of a shared frame hits L2): compulsory traffic
+ * 592 704 B per sample instead of 635 040 B.  augcl_ring_sample* / augcl_ring_sample_fused work on both layouts.
+ * The caller owns the pool cursor and must not overwrite a frame a live transition still references
+ * (augcl_b200.utils.ReplayBuffer(dedup=True) does that bookkeeping).  augcl_ring_put / _get of image stacks return
+ * AUGCL_ERR_UNSUPPORTED on such a ring (scalars still work). */
+int augcl_ring_create_dedup(augcl_ring** out, int device, int64_t capacity, int k, int c_per_frame, int H, int W,
+                            int action_dim, int64_t pool_frames);
+/* Store `count` frames (count*c_per_frame*H*W bytes, host or device) at pool slots [frame0, frame0+count) (no wrap). */
+int augcl_ring_put_frames(augcl_ring* ring, int64_t frame0, int64_t count, const uint8_t* frames, augcl_stream stream);
+/* Store the frame references (int32 [count][2][k]: obs frames then next_obs frames, oldest first) and the scalars of
+ * transitions [slot0, slot0+count).  Host references are range-checked.  NULL pointers leave that field untouched. */
+int augcl_ring_put_refs(augcl_ring* ring, int64_t slot0, int64_t count, const int32_t* refs, const float* actions,
+                        const float* rewards, const float* not_dones, augcl_stream stream);
+
 /* Fill slots [0, count) with Philox bytes / normals (benchmarks and tests; no reference analogue). */
 int augcl_ring_fill_synthetic(augcl_ring* ring, int64_t count, uint64_t seed, augcl_stream stream);
 
