@@ -402,6 +402,48 @@ def fused_configs(res):
     return out
 
 
+def dedup_ring(res):
+    """configs[1] step on the de-duplicated ring (v2 layout: frame pool + references): same kernel, reads resolve
+    through the reference table; compulsory traffic (k+1)*F + 2*S32 = 592 704 B per sample."""
+    import torch
+    from augcl_b200 import _lib as L, utils as U
+    dev, B = res["dev"], 128
+    peak = load_peaks()[0]
+    buf = U.ReplayBuffer((C, S, S), (A_DIM,), CAP, B, device=dev, dedup=True)
+    buf.fill_synthetic(seed=5)
+    g = torch.Generator().manual_seed(17)
+    stream = torch.cuda.current_stream(dev)
+    iters, n_sets = 2000, 8
+    o = [(torch.empty((B, C, S, S), device=dev), torch.empty((B, C, S, S), device=dev)) for _ in range(n_sets)]
+    idx = torch.randint(0, CAP, (iters + 5, B), generator=g).to(dev)
+    off = torch.randint(0, 2 * PAD + 1, (iters + 5, 2, B, 2), generator=g, dtype=torch.int32).to(dev)
+    fn, ring, sp = L.lib().augcl_ring_sample, buf._ring, stream.cuda_stream
+    ip, op = idx.data_ptr(), off.data_ptr()
+    ptrs = [(a.data_ptr(), b.data_ptr()) for a, b in o]
+
+    def step(t):
+        a, b = ptrs[t % n_sets]
+        if fn(ring, ip + t * B * 8, B, a, b, None, None, None, L.AUG_SHIFT, op + t * 16 * B, op + t * 16 * B + 8 * B, PAD, 0, sp):
+            raise RuntimeError(L.lib().augcl_last_error().decode())
+    for t in range(5):
+        step(t)
+    torch.cuda.synchronize(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for t in range(5, iters + 5):
+        step(t)
+    e1.record(stream)
+    torch.cuda.synchronize(dev)
+    us = e0.elapsed_time(e1) * 1e3 / iters
+    ab = (K_FRAMES + 1) * 3 * S * S + 2 * 4 * S8
+    gbs = B * ab / us / 1e3
+    out = {"workload": "configs[1] on ReplayBuffer(dedup=True)", "batch": B, "us_per_step": round(us, 2),
+           "samples_per_s": round(B / us * 1e6), "algorithmic_bytes_per_sample": ab, "GB/s": round(gbs, 1),
+           "frac": round(gbs / peak, 4), "ring_bytes": buf.ring_bytes(), "ring_bytes_full_stacks": res["buf"].ring_bytes()}
+    del buf
+    return out
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.isfile(p):
@@ -438,6 +480,7 @@ def main():
         if world == 1 and not args.no_sweep:
             line["batch_sweep"] = batch_sweep(res)
             line["fused_configs"] = fused_configs(res)
+            line["dedup_ring"] = dedup_ring(res)
         if world == 1 and not args.no_cpu_baseline:
             cores = os.cpu_count() or 1
             torch.set_num_threads(cores)
