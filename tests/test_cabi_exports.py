@@ -59,6 +59,33 @@ def test_argument_validation_without_device(lib):
     assert torch.equal(torch.tensor(list(buf), dtype=torch.float32), want)
 
 
+def test_fused_desc_abi_and_validation_without_device(lib):
+    """The ctypes mirror of augcl_fused_desc has the C struct's size (struct_size guards the ABI), and the fused /
+    de-duplicated entry points reject bad arguments before touching a device."""
+    d = lib.FusedDesc()
+    d.struct_size = ctypes.sizeof(lib.FusedDesc)
+    h = lib.lib()
+    assert h.augcl_ring_sample_fused(None, ctypes.byref(d), None) == -1
+    assert "ring is NULL" in h.augcl_last_error().decode()          # the size check passed, the ring check failed
+    d.struct_size -= 8
+    assert h.augcl_ring_sample_fused(None, ctypes.byref(d), None) == -1
+    assert "ABI mismatch" in h.augcl_last_error().decode()
+    assert h.augcl_ring_sample_fused(None, None, None) == -1
+    with pytest.raises(lib.AugclError):
+        lib.call("augcl_ring_put_frames", None, 0, 1, None, None)
+    with pytest.raises(lib.AugclError):
+        lib.call("augcl_ring_put_refs", None, 0, 1, None, None, None, None, None)
+    out = ctypes.c_void_p()
+    with pytest.raises(lib.AugclError) as e:
+        lib.call("augcl_ring_create_dedup", ctypes.byref(out), 0, 10, 3, 3, 84, 84, 6, 2)     # pool <= k
+    assert e.value.status == -1 and "pool_frames" in str(e.value)
+    for key in ("fused_stages", "fused_ctas_per_sm", "fused_cost_obs", "fused_cost_next"):
+        lib.set_option(key, "0")
+    lib.set_option("fused_fast_mask", "1")
+    with pytest.raises(lib.AugclError):
+        lib.set_option("fused_stages", "9")
+
+
 def test_product_has_no_cpu_path_and_never_imports_oracle():
     import torch
     from augcl_b200 import augmentations as A
