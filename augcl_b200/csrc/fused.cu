@@ -28,7 +28,7 @@ std::atomic<int> g_fused_cost_next{0};
 std::atomic<int> g_fused_stages{0};      // 0 = auto
 std::atomic<int> g_fused_fast_mask{1};   // 0: always the float HSV path (A/B and the exhaustive equivalence test)
 
-constexpr int kFHeader = 256 + 864;   // mbarriers + metas + conv weights [27][8] (each weight twice: FFMA2 operand)
+constexpr int kFHeader = 256 + 432;   // mbarriers + metas + conv weights
 constexpr int kFBand = 12;        // conv chains: 12 rows + 2 halo rows = 14 tile rows = two rounds of 7 rows
 constexpr int kFBandNoConv = 14;  // every other chain: 14 rows = two full rounds, 84 = 6 bands
 constexpr int kFThreads = 160;   // 147 = 7 rows x 21 quads work at W = 84: a 14-row tile is exactly two rounds
@@ -73,17 +73,6 @@ __device__ __forceinline__ float4 fin4(float4 v) {
   return make_float4(fin<NORM>(v.x), fin<NORM>(v.y), fin<NORM>(v.z), fin<NORM>(v.w));
 }
 
-// Packed pair of f32 in a 64-bit register + FFMA2 (fma.rn.f32x2): two FMAs per issue slot.  Same FMA-pipe rate as scalar
-// FFMA (scripts/microbench/ffma2.cu) but half the issue slots, and the fused conv chains are issue-bound.
-typedef unsigned long long u64;
-__device__ __forceinline__ u64 pack2(float lo, float hi) {
-  u64 r;
-  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
-  return r;
-}
-__device__ __forceinline__ void unpack2(u64 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
-__device__ __forceinline__ void ffma2(u64& d, u64 a, u64 b) { asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(d) : "l"(a), "l"(b)); }
-
 // chain stage before the conv
 enum { kPreNone = 0, kPreSplice = 1, kPreSpliceFast = 2, kPreOverlay = 3 };
 
@@ -94,8 +83,8 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
   extern __shared__ __align__(128) uint8_t smem[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem);                 // <= 4 mbarriers
   FusedMeta* meta = reinterpret_cast<FusedMeta*>(smem + 32);          // <= 4 metas (4 x 56 B = 224 B)
-  float* wsm = reinterpret_cast<float*>(smem + 256);                  // [27][8] conv weights / 255: (w0,w0,w1,w1,w2,w2,-,-)
-  uint8_t* stage = smem + kFHeader;                                   // NS x stage_bytes (1120 = 16 * 70: 16-B aligned)
+  float* wsm = reinterpret_cast<float*>(smem + 256);                  // [27][4] conv weights / 255
+  uint8_t* stage = smem + kFHeader;                                   // NS x stage_bytes (688 = 16 * 43: 16-B aligned)
   const int NS = p.stages;
   float* tile = reinterpret_cast<float*>(stage + NS * p.stage_bytes); // [3][kFBand+2][tile_rs]
   const int tid = threadIdx.x;
@@ -252,13 +241,11 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
     const int trows = m.rows + 2 * hal;
     const bool aug_sh = p.aug_shifted != 0;
     if (CONV && tid < 81) {
-      // weights[sample][co][ci][ky][kx] / 255 -> wsm[(ci*9 + ky*3 + kx)*8 + 2*co + {0,1}]
+      // weights[sample][co][ci][ky][kx] / 255 -> wsm[(ci*9 + ky*3 + kx)*4 + co]
       const int co = tid / 27, tap = tid - co * 27;
-      const float wq = __fdiv_rn(p.weights[(int64_t)m.sample * 81 + tid], 255.0f);
-      *reinterpret_cast<float2*>(wsm + tap * 8 + 2 * co) = make_float2(wq, wq);
+      wsm[tap * 4 + co] = __fdiv_rn(p.weights[(int64_t)m.sample * 81 + tid], 255.0f);
     }
-    // one tile row of this thread's 4-pixel group: direct outputs (plain / shifted copies) and the chain's value v
-    auto row_values = [&](int pr, float (&v)[3][4], size_t& oo_out) {
+    for (int pr = active ? row0 : trows; pr < trows; pr += RPR) {
       const int r = clampi(m.r0 + pr - hal, 0, H - 1);
       const bool own = !CONV || (pr >= 1 && pr <= m.rows);   // halo rows only feed the conv tile
       const size_t oo = (size_t)r * W + 4 * q4;              // offset inside plane 0; planes are H*W apart
@@ -272,7 +259,7 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
         if (own && m.o_plain) store3(m.o_plain, oo, Aw);
         if (own && m.o_shift) { load_shift(r, q4, Ow); store3(m.o_shift, oo, Ow); }
       }
-      float a[3][4];
+      float a[3][4], v[3][4];
 #pragma unroll
       for (int ci = 0; ci < 3; ++ci) {
         const float4 t4 = bytes_to_float4(Aw[ci]);
@@ -316,32 +303,15 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
 #pragma unroll
           for (int j = 0; j < 4; ++j) v[ci][j] = a[ci][j];
       }
-      oo_out = oo;
-    };
-    if (CONV) {
-      // the conv tile is ROW-INTERLEAVED: element (channel ci, tile row pr, column idx) sits at
-      //   ((ci * 7 + pr / 2) * TRS + idx) * 2 + (pr & 1)
-      // so the pair (row 2i, row 2i+1) of a column is one aligned 64-bit word -- the operand FFMA2 wants in phase B.
-      // A thread fills both rows of a pair: the 14 tile rows are ONE round of 7 row pairs x 21 quads.
-      for (int i = active ? row0 : trows; 2 * i < trows; i += RPR) {
-        float v0[3][4], v1[3][4];
-        size_t oo;
-        row_values(2 * i, v0, oo);
-        row_values(2 * i + 1, v1, oo);     // pr == trows (odd tile heights) recomputes the clamped last row: harmless
+      if (CONV) {
 #pragma unroll
         for (int ci = 0; ci < 3; ++ci) {
-          float* tp = tile + ((ci * ((kFBand + 2) / 2) + i) * TRS) * 2;
-          *reinterpret_cast<float4*>(tp + (4 + 4 * q4) * 2) = make_float4(v0[ci][0], v1[ci][0], v0[ci][1], v1[ci][1]);
-          *reinterpret_cast<float4*>(tp + (6 + 4 * q4) * 2) = make_float4(v0[ci][2], v1[ci][2], v0[ci][3], v1[ci][3]);
-          if (q4 == 0) *reinterpret_cast<float2*>(tp + 3 * 2) = make_float2(v0[ci][0], v1[ci][0]);
-          if (q4 == nq - 1) *reinterpret_cast<float2*>(tp + (4 + W) * 2) = make_float2(v0[ci][3], v1[ci][3]);
+          float* trow = tile + (ci * (kFBand + 2) + pr) * TRS;
+          *reinterpret_cast<float4*>(trow + 4 + 4 * q4) = make_float4(v[ci][0], v[ci][1], v[ci][2], v[ci][3]);
+          if (q4 == 0) trow[3] = v[ci][0];
+          if (q4 == nq - 1) trow[4 + W] = v[ci][3];
         }
-      }
-    } else {
-      for (int pr = active ? row0 : trows; pr < trows; pr += RPR) {
-        float v[3][4];
-        size_t oo;
-        row_values(pr, v, oo);
+      } else {
 #pragma unroll
         for (int ci = 0; ci < 3; ++ci)
           st_global_f4(reinterpret_cast<float4*>(m.o_aug + oo + ci * HW),
@@ -354,63 +324,48 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
     if (CONV) {
       const int npair = (m.rows + 1) >> 1;
       for (int rp = active ? row0 : npair; rp < npair; rp += RPR) {
-        const int r = rp * 2;                 // output rows r, r+1 of the band <- tile rows r .. r+3 = row pairs rp, rp+1
-        u64 acc[3][4];                        // [out channel][pixel]: (row r, row r+1)
+        const int r = rp * 2;
+        float acc[2][3][4];
 #pragma unroll
-        for (int co = 0; co < 3; ++co)
+        for (int a = 0; a < 2; ++a)
 #pragma unroll
-          for (int j = 0; j < 4; ++j) acc[co][j] = 0ull;
+          for (int co = 0; co < 3; ++co)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[a][co][j] = 0.0f;
 #pragma unroll 1
         for (int ci = 0; ci < 3; ++ci) {
-          // the 6-column window of both row pairs, every element already a (row 2i, row 2i+1) pair
-          u64 P0[6], P1[6];
-          {
-            const float* t0 = tile + ((ci * ((kFBand + 2) / 2) + rp) * TRS + 3 + 4 * q4) * 2;
-            const float* t1 = t0 + TRS * 2;
-            const ulonglong2 a0 = *reinterpret_cast<const ulonglong2*>(t0 + 2), b0 = *reinterpret_cast<const ulonglong2*>(t0 + 6);
-            const ulonglong2 a1 = *reinterpret_cast<const ulonglong2*>(t1 + 2), b1 = *reinterpret_cast<const ulonglong2*>(t1 + 6);
-            P0[0] = *reinterpret_cast<const u64*>(t0); P0[1] = a0.x; P0[2] = a0.y; P0[3] = b0.x; P0[4] = b0.y;
-            P0[5] = *reinterpret_cast<const u64*>(t0 + 10);
-            P1[0] = *reinterpret_cast<const u64*>(t1); P1[1] = a1.x; P1[2] = a1.y; P1[3] = b1.x; P1[4] = b1.y;
-            P1[5] = *reinterpret_cast<const u64*>(t1 + 10);
+          float x[4][6];
+#pragma unroll
+          for (int y = 0; y < 4; ++y) {
+            const float* trow = tile + (ci * (kFBand + 2) + r + y) * TRS + q4 * 4;
+            const float4 a = *reinterpret_cast<const float4*>(trow + 4);
+            x[y][0] = trow[3]; x[y][1] = a.x; x[y][2] = a.y; x[y][3] = a.z; x[y][4] = a.w; x[y][5] = trow[8];
           }
-          auto taps = [&](int ky, const u64 (&X)[6]) {
+#pragma unroll
+          for (int ky = 0; ky < 3; ++ky) {
 #pragma unroll
             for (int kx = 0; kx < 3; ++kx) {
-              const float* wp = wsm + (ci * 9 + ky * 3 + kx) * 8;
-              const ulonglong2 w01 = *reinterpret_cast<const ulonglong2*>(wp);
-              const u64 w2 = *reinterpret_cast<const u64*>(wp + 4);
+              const float4 wv = *reinterpret_cast<const float4*>(wsm + (ci * 9 + ky * 3 + kx) * 4);
 #pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                ffma2(acc[0][j], X[j + kx], w01.x);
-                ffma2(acc[1][j], X[j + kx], w01.y);
-                ffma2(acc[2][j], X[j + kx], w2);
-              }
-            }
-          };
-          taps(0, P0);                        // ky = 0: tile rows (r, r+1)
-          {
-            u64 M[6];                         // ky = 1: tile rows (r+1, r+2) straddle the two pairs: 2 moves per column
+              for (int a = 0; a < 2; ++a)
 #pragma unroll
-            for (int c = 0; c < 6; ++c) {
-              float l0, h0, l1, h1;
-              unpack2(P0[c], l0, h0);
-              unpack2(P1[c], l1, h1);
-              M[c] = pack2(h0, l1);
+                for (int j = 0; j < 4; ++j) {
+                  acc[a][0][j] = fmaf(x[a + ky][j + kx], wv.x, acc[a][0][j]);
+                  acc[a][1][j] = fmaf(x[a + ky][j + kx], wv.y, acc[a][1][j]);
+                  acc[a][2][j] = fmaf(x[a + ky][j + kx], wv.z, acc[a][2][j]);
+                }
             }
-            taps(1, M);
           }
-          taps(2, P1);                        // ky = 2: tile rows (r+2, r+3)
         }
 #pragma unroll
-        for (int co = 0; co < 3; ++co) {
-          float lo[4], hi[4];
+        for (int a = 0; a < 2; ++a) {
+          if (r + a >= m.rows) break;
 #pragma unroll
-          for (int j = 0; j < 4; ++j) unpack2(acc[co][j], lo[j], hi[j]);
-          float4* dst = reinterpret_cast<float4*>(m.o_aug + co * HW + (size_t)(m.r0 + r) * W) + q4;
-          st_global_f4(dst, fin4<NORM>(make_float4(sigmoid255(lo[0]), sigmoid255(lo[1]), sigmoid255(lo[2]), sigmoid255(lo[3]))));
-          if (r + 1 < m.rows)
-            st_global_f4(dst + nq, fin4<NORM>(make_float4(sigmoid255(hi[0]), sigmoid255(hi[1]), sigmoid255(hi[2]), sigmoid255(hi[3]))));
+          for (int co = 0; co < 3; ++co) {
+            float4* dst = reinterpret_cast<float4*>(m.o_aug + co * HW + (size_t)(m.r0 + r + a) * W) + q4;
+            st_global_f4(dst, fin4<NORM>(make_float4(sigmoid255(acc[a][co][0]), sigmoid255(acc[a][co][1]),
+                                                     sigmoid255(acc[a][co][2]), sigmoid255(acc[a][co][3]))));
+          }
         }
       }
       __syncthreads();   // tile and wsm are free again
