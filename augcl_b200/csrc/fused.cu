@@ -26,6 +26,7 @@ std::atomic<int> g_fused_ctas_per_sm{0};   // 0 = auto
 std::atomic<int> g_fused_cost_obs{0};    // 0 = auto
 std::atomic<int> g_fused_cost_next{0};
 std::atomic<int> g_fused_stages{0};      // 0 = auto
+std::atomic<int> g_fused_band{0};        // 0 = auto (non-conv chains: 14 or 7 rows)
 std::atomic<int> g_fused_fast_mask{1};   // 0: always the float HSV path (A/B and the exhaustive equivalence test)
 
 constexpr int kFHeader = 256 + 432;   // mbarriers + metas + conv weights
@@ -47,7 +48,7 @@ struct FusedParams {
   float oma, alpha;
   int ops;                  // AUGCL_OP_*
   int aug_shifted;          // chain input: 0 plain, 1 shifted
-  int k, bands;             // frames per stack, bands per frame
+  int k, bands, band;       // frames per stack, bands per frame, rows per band
   int64_t units_obs, units_next;
   int cost_obs, cost_next;
   int plane_stage, bank_stage, stage_bytes, tile_rs, stages;
@@ -124,7 +125,7 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
     const uint32_t fr = u / (uint32_t)p.bands;  // frame row of x.reshape(B*k, 3, H, W)
     const int band = (int)(u - fr * (uint32_t)p.bands);
     const int b = (int)(fr / (uint32_t)p.k), f = (int)(fr - (uint32_t)b * (uint32_t)p.k);
-    constexpr int BAND = CONV ? kFBand : kFBandNoConv;
+    const int BAND = CONV ? kFBand : p.band;
     const int r0 = band * BAND, rows = min(BAND, H - r0);
     const int64_t slot = sample_index(p.sp, none, b);
     int dy, dx;
@@ -477,7 +478,11 @@ extern "C" int augcl_ring_sample_fused(augcl_ring* r, const augcl_fused_desc* d,
   }
   p.alpha = d->alpha; p.oma = (float)(1.0 - (double)d->alpha);
   p.ops = ops; p.aug_shifted = d->aug_input == AUGCL_AUG_INPUT_SHIFTED ? 1 : 0;
-  const int band = (ops & AUGCL_OP_CONV) ? kFBand : kFBandNoConv;
+  // non-conv chains: 14-row bands = two full rounds of 7 rows.  (7-row bands were measured for short launches, where a CTA
+  // only gets ~5 units: the finer partition does not pay for the doubled per-unit cost -- 27.0 vs 24.6 us at batch 128.)
+  int band = (ops & AUGCL_OP_CONV) ? kFBand : kFBandNoConv;
+  if (!(ops & AUGCL_OP_CONV) && g_fused_band.load() > 0) band = g_fused_band.load();
+  p.band = band;
   p.k = r->k; p.bands = (r->H + band - 1) / band;
   p.units_obs = any_obs ? (int64_t)B * r->k * p.bands : 0;
   p.units_next = any_next ? (int64_t)B * r->k * p.bands : 0;
