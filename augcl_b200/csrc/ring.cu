@@ -54,7 +54,7 @@ __global__ void __launch_bounds__(256, 6) ring_sample_tma_kernel(const SamplePar
     const int slot = bt % p.nt, b = bt / p.nt;
     const int t = p.tmap[slot];
     const int64_t row = sample_index(p, none, b);
-    const uint8_t* src = plane_ptr(p, t, row, ch, (int64_t)P);
+    const uint8_t* src = plane_ptr(p, p.vsrc[t], row, ch, (int64_t)P);
     const uintptr_t a = reinterpret_cast<uintptr_t>(src);
     const int lead = (int)(a & 15);
     const uint32_t bytes = (uint32_t)((lead + P + 15) & ~15);
@@ -169,7 +169,7 @@ __global__ void __launch_bounds__(256, 6) ring_sample_band_kernel(const SamplePa
     const int64_t rem = u1 - plane * NIT;
     const int it_hi = rem < NIT ? (int)rem : NIT;
     const int row_lo = clampi(it_lo * RPI + dy, 0, H - 1), row_hi = clampi(it_hi * RPI - 1 + dy, 0, H - 1);
-    const uint8_t* src = plane_ptr(p, t, row, ch, (int64_t)P);
+    const uint8_t* src = plane_ptr(p, p.vsrc[t], row, ch, (int64_t)P);
     const uintptr_t a0 = reinterpret_cast<uintptr_t>(src + row_lo * W) & ~(uintptr_t)15;
     const uintptr_t a1 = (reinterpret_cast<uintptr_t>(src + (row_hi + 1) * W) + 15) & ~(uintptr_t)15;
     BandMeta m;
@@ -233,7 +233,7 @@ __global__ void __launch_bounds__(256) ring_sample_generic_kernel(const SamplePa
     sample_offset(p, none, t, b, dy, dx);
     const int rr = clampi(r + dy, 0, p.H - 1), cc = clampi(q + dx, 0, p.W - 1);
     const int64_t row = sample_index(p, none, b);
-    float v = (float)plane_ptr(p, t, row, ch, (int64_t)p.H * p.W)[rr * p.W + cc];
+    float v = (float)plane_ptr(p, p.vsrc[t], row, ch, (int64_t)p.H * p.W)[rr * p.W + cc];
     if (p.normalize) v = __fdiv_rn(v, 255.0f);
     p.out[t][(((int64_t)b * p.C + ch) * p.Ho + r) * p.Wo + q] = v;
   }
@@ -445,10 +445,11 @@ int augcl_ring_fill_synthetic(augcl_ring* r, int64_t count, uint64_t seed, augcl
 static int sample_impl(const char* who, augcl_ring* r, int idx_src, const int64_t* idx, int64_t idx_hi, int B,
                        float* out_obs, float* out_next, float* out_act, float* out_rew, float* out_nd, int aug_mode,
                        int off_src, const int32_t* off_obs, const int32_t* off_next, int pad_or_size, int normalize,
-                       uint64_t seed, uint64_t subsequence, cudaStream_t st) {
+                       uint64_t seed, uint64_t subsequence, cudaStream_t st, float* out_pos = nullptr,
+                       const int32_t* off_pos = nullptr) {
   AUGCL_REQUIRE(r, "%s: ring is NULL", who);
   AUGCL_REQUIRE(B > 0, "%s: B must be positive (got %d)", who, B);
-  AUGCL_REQUIRE(out_obs || out_next, "%s: both image outputs are NULL", who);
+  AUGCL_REQUIRE(out_obs || out_next || out_pos, "%s: every image output is NULL", who);
   AUGCL_REQUIRE(aug_mode == AUGCL_AUG_NONE || aug_mode == AUGCL_AUG_SHIFT || aug_mode == AUGCL_AUG_CROP ||
                     aug_mode == AUGCL_AUG_SHIFT_OBS, "%s: unknown aug_mode %d", who, aug_mode);
   const bool obs_only = aug_mode == AUGCL_AUG_SHIFT_OBS;
@@ -463,15 +464,16 @@ static int sample_impl(const char* who, augcl_ring* r, int idx_src, const int64_
     AUGCL_REQUIRE(idx, "%s: idx is NULL", who);
   SampleParams p{};
   p.store[0] = r->obs; p.store[1] = r->next; p.refs = r->dedup ? r->refs : nullptr; p.k = r->k; p.cpf = r->cpf;
-  p.out[0] = out_obs; p.out[1] = out_next;
+  p.out[0] = out_obs; p.out[1] = out_next; p.out[2] = out_pos;
+  p.vsrc[0] = 0; p.vsrc[1] = 1; p.vsrc[2] = 0;
   p.idx = idx; p.act = r->act; p.rew = r->rew; p.nd = r->nd;
   p.out_act = out_act; p.out_rew = out_rew; p.out_nd = out_nd;
   p.capacity = r->capacity;
   p.B = B; p.C = r->C; p.H = r->H; p.W = r->W; p.A = r->A;
   p.Ho = r->H; p.Wo = r->W; p.pad = 0; p.normalize = normalize ? 1 : 0;
   p.idx_mode = idx_src; p.idx_hi = (uint64_t)idx_hi; p.seed = seed; p.subseq = subsequence;
-  const int32_t* off[2] = {off_obs, off_next};
-  float* outs[2] = {out_obs, out_next};
+  const int32_t* off[3] = {off_obs, off_next, off_pos};
+  float* outs[3] = {out_obs, out_next, out_pos};
   int hi_row = 0, hi_col = 0;   // valid offsets: row in [0, hi_row], col in [0, hi_col]
   if (aug_mode == AUGCL_AUG_SHIFT) {
     AUGCL_REQUIRE(pad_or_size >= 0 && pad_or_size < (1 << 15), "%s: bad pad %d", who, pad_or_size);
@@ -487,7 +489,7 @@ static int sample_impl(const char* who, augcl_ring* r, int idx_src, const int64_
     if (off_src == AUGCL_SRC_PHILOX)
       AUGCL_REQUIRE(r->H == r->W && p.off_range > 0, "%s: PHILOX crop offsets need a square image larger than the crop", who);
   }
-  for (int t = 0; t < 2; ++t) {
+  for (int t = 0; t < 3; ++t) {
     if (aug_mode == AUGCL_AUG_NONE || !outs[t] || (obs_only && t == 1)) { p.off_mode[t] = kSrcNone; continue; }
     if (off_src == AUGCL_SRC_PHILOX) { p.off_mode[t] = off[t] ? AUGCL_SRC_DEVICE : AUGCL_SRC_PHILOX; p.off[t] = off[t]; continue; }
     if (!off[t]) {
@@ -501,6 +503,7 @@ static int sample_impl(const char* who, augcl_ring* r, int idx_src, const int64_
   p.nt = 0;
   if (out_obs) p.tmap[p.nt++] = 0;
   if (out_next) p.tmap[p.nt++] = 1;
+  if (out_pos) p.tmap[p.nt++] = 2;
   AUGCL_REQUIRE((int64_t)B * p.nt * p.C < (1ll << 31), "%s: batch too large", who);
   DeviceGuard g(r->device);
   AUGCL_CUDA(g.err);
@@ -508,13 +511,14 @@ static int sample_impl(const char* who, augcl_ring* r, int idx_src, const int64_
   // ---- HOST draws: validate (the reference raises IndexError on a bad index), then carry them by value
   //      in the launch (small batches, band geometries) or stage them through stream-ordered scratch.
   const bool host_idx = idx_src == AUGCL_SRC_HOST;
-  const bool host_off = off_src == AUGCL_SRC_HOST && (p.off_mode[0] == AUGCL_SRC_HOST || p.off_mode[1] == AUGCL_SRC_HOST);
+  const bool host_off = off_src == AUGCL_SRC_HOST &&
+                        (p.off_mode[0] == AUGCL_SRC_HOST || p.off_mode[1] == AUGCL_SRC_HOST || p.off_mode[2] == AUGCL_SRC_HOST);
   if (host_idx)
     for (int b = 0; b < B; ++b)
       AUGCL_REQUIRE(idx[b] >= 0 && idx[b] < r->capacity, "%s: index %lld (position %d) out of range [0, %lld)", who,
                     (long long)idx[b], b, (long long)r->capacity);
   if (host_off)
-    for (int t = 0; t < 2; ++t)
+    for (int t = 0; t < 3; ++t)
       if (p.off_mode[t] == AUGCL_SRC_HOST)
         for (int e = 0; e < 2 * B; ++e)
           AUGCL_REQUIRE(off[t][e] >= 0 && off[t][e] <= ((e & 1) ? hi_col : hi_row),
@@ -524,7 +528,7 @@ static int sample_impl(const char* who, augcl_ring* r, int idx_src, const int64_
   const int P = p.H * p.W;
   p.stage_bytes = ((P + 15) & ~15) + 32;
   const int kHeader = 64 + 8 * (int)sizeof(BandMeta);   // mbarriers + per-stage metas (both kernels fit in it)
-  const bool vec_ok = (p.Wo % 4 == 0) && aligned(out_obs, 16) && aligned(out_next, 16) &&
+  const bool vec_ok = (p.Wo % 4 == 0) && aligned(out_obs, 16) && aligned(out_next, 16) && aligned(out_pos, 16) &&
                       kHeader + p.stage_bytes <= kMaxSmem;
   const bool staged = g_staging.load() == 0 && vec_ok;
   int geom = 0;   // compile-time geometries of the reference's two image sizes (src/arguments.py:155-163)
@@ -544,15 +548,15 @@ static int sample_impl(const char* who, augcl_ring* r, int idx_src, const int64_
         for (int b = 0; b < B; ++b) inl.idx[b] = (int32_t)idx[b];
         p.idx_mode = kSrcInline;
       }
-      for (int t = 0; t < 2; ++t)
+      for (int t = 0; t < 3; ++t)
         if (p.off_mode[t] == AUGCL_SRC_HOST) {
           for (int b = 0; b < B; ++b) { inl.off[t][b][0] = (int8_t)off[t][2 * b]; inl.off[t][b][1] = (int8_t)off[t][2 * b + 1]; }
           p.off_mode[t] = kSrcInline;
         }
     } else {
-      // stream-ordered scratch: [idx int64 B][off_obs int32 2B][off_next int32 2B]
+      // stream-ordered scratch: [idx int64 B][off_obs int32 2B][off_next int32 2B][off_pos int32 2B]
       const size_t ib = (size_t)B * 8, ob = (size_t)B * 8;
-      AUGCL_CUDA(cudaMallocAsync(&scratch, ib + 2 * ob, st));
+      AUGCL_CUDA(cudaMallocAsync(&scratch, ib + 3 * ob, st));
       uint8_t* sp = static_cast<uint8_t*>(scratch);
       cudaError_t e = cudaSuccess;
       if (host_idx) {
@@ -560,7 +564,7 @@ static int sample_impl(const char* who, augcl_ring* r, int idx_src, const int64_
         p.idx = reinterpret_cast<const int64_t*>(sp);
         p.idx_mode = AUGCL_SRC_DEVICE;
       }
-      for (int t = 0; t < 2 && e == cudaSuccess; ++t)
+      for (int t = 0; t < 3 && e == cudaSuccess; ++t)
         if (p.off_mode[t] == AUGCL_SRC_HOST) {
           e = cudaMemcpyAsync(sp + ib + t * ob, off[t], ob, cudaMemcpyHostToDevice, st);
           p.off[t] = reinterpret_cast<const int32_t*>(sp + ib + t * ob);
@@ -650,6 +654,15 @@ int augcl_ring_sample_ex(augcl_ring* r, int idx_src, const int64_t* idx, int64_t
                          uint64_t subsequence, augcl_stream stream) {
   return sample_impl("augcl_ring_sample_ex", r, idx_src, idx, idx_hi, B, out_obs, out_next, out_act, out_rew, out_nd,
                      aug_mode, off_src, off_obs, off_next, pad_or_size, normalize, seed, subsequence, (cudaStream_t)stream);
+}
+
+int augcl_ring_sample_curl(augcl_ring* r, int idx_src, const int64_t* idx, int64_t idx_hi, int B, float* out_obs,
+                           float* out_next, float* out_pos, float* out_act, float* out_rew, float* out_nd, int off_src,
+                           const int32_t* off_obs, const int32_t* off_next, const int32_t* off_pos, int size, int normalize,
+                           uint64_t seed, uint64_t subsequence, augcl_stream stream) {
+  return sample_impl("augcl_ring_sample_curl", r, idx_src, idx, idx_hi, B, out_obs, out_next, out_act, out_rew, out_nd,
+                     AUGCL_AUG_CROP, off_src, off_obs, off_next, size, normalize, seed, subsequence, (cudaStream_t)stream,
+                     out_pos, off_pos);
 }
 
 }  // extern "C"

@@ -34,8 +34,10 @@ struct SampleParams {
   const uint8_t* store[2];   // v1: obs / next_obs stacks; v2: store[0] = frame pool
   const int32_t* refs;       // v2: [capacity][2][k] pool slots (NULL = v1)
   int k, cpf;
-  float* out[2];
-  const int32_t* off[2];
+  // output "views": 0 = obs, 1 = next_obs, 2 = a second, independently cropped copy of obs (sample_curl's `pos`)
+  float* out[3];
+  const int32_t* off[3];
+  int vsrc[3];               // ring tensor a view reads: {0, 1, 0}
   const int64_t* idx;
   const float* act;
   const float* rew;
@@ -48,12 +50,12 @@ struct SampleParams {
   int pad;        // SHIFT: pad; NONE/CROP: 0.  source coord = clamp(out coord + off - pad)
   int normalize;
   int nt;         // number of tensors written (1 or 2); slot s -> tensor tmap[s]
-  int tmap[2];
+  int tmap[3];
   int stage_bytes;
   int stages;
   // where the draws come from (AUGCL_SRC_*; kSrcInline = by value in the launch's parameter block, kSrcNone = identity)
   int idx_mode;
-  int off_mode[2];
+  int off_mode[3];
   uint32_t off_range;      // PHILOX offsets are uniform in [0, off_range)
   uint64_t idx_hi;         // PHILOX indices are uniform in [0, idx_hi)
   uint64_t seed, subseq;   // PHILOX streams: indices = subseq, obs offsets = subseq + 1, next_obs offsets = subseq + 2
@@ -68,7 +70,7 @@ constexpr int kInlineMax = 256;   // the reference's batch sizes: 128 (src/argum
 template <int NB>
 struct InlineDraws {
   int32_t idx[NB];
-  int8_t off[2][NB][2];
+  int8_t off[3][NB][2];
 };
 template <>
 struct InlineDraws<0> {};

@@ -292,12 +292,12 @@ class ReplayBuffer(object):
         return L.SRC_HOST, a.ctypes.data, a
 
     def _sample(self, idxs=None, *, n=None, obs=True, next_obs=True, scalars=True, aug=L.AUG_NONE, off_obs=None,
-                off_next=None, pad_or_size=0, normalize=False, device_indices=False):
+                off_next=None, pad_or_size=0, normalize=False, device_indices=False, pos=False, off_pos=None):
         """One augcl_ring_sample_ex launch.  Returns (obs, actions, rewards, next_obs, not_dones); entries
         that were not requested are None.  Host indices / offsets travel inside the launch (no extra H2D);
         offsets that are not supplied are drawn inside the kernel (Philox stream of augmentations.seed())."""
         self._flush()
-        sub = augmentations._reserve_subsequences(3)
+        sub = augmentations._reserve_subsequences(4 if pos else 3)
         if device_indices and idxs is None:
             B = self.batch_size if n is None else int(n)
             i_src, i_ptr, keep_i = L.SRC_PHILOX, None, None
@@ -308,9 +308,10 @@ class ReplayBuffer(object):
             i_src, i_ptr, B, keep_i = self._idx_arg(idxs)
             idx_hi = 0
         oo, on = self._off_arg(off_obs, B), self._off_arg(off_next, B)
-        need_draw = aug in (L.AUG_SHIFT, L.AUG_CROP) and ((obs and oo is None) or (next_obs and on is None))
+        op = self._off_arg(off_pos, B) if pos else None
+        need_draw = aug in (L.AUG_SHIFT, L.AUG_CROP) and ((obs and oo is None) or (next_obs and on is None) or (pos and op is None))
         need_draw = need_draw or (aug == L.AUG_SHIFT_OBS and obs and oo is None)
-        kinds = {x[0] for x in (oo, on) if x is not None}
+        kinds = {x[0] for x in (oo, on, op) if x is not None}
         if need_draw or len(kinds) > 1:
             # PHILOX draws for the missing tensors; supplied arrays must then be DEVICE arrays
             def to_dev(x):
@@ -318,7 +319,7 @@ class ReplayBuffer(object):
                     return x
                 t = torch.from_numpy(x[2]).to(self.device, non_blocking=False)
                 return L.SRC_DEVICE, t.data_ptr(), t
-            oo, on = to_dev(oo), to_dev(on)
+            oo, on, op = to_dev(oo), to_dev(on), to_dev(op)
             o_src = L.SRC_PHILOX if need_draw else L.SRC_DEVICE
         else:
             o_src = kinds.pop() if kinds else L.SRC_DEVICE
@@ -347,15 +348,24 @@ class ReplayBuffer(object):
                 rew, nd = torch.empty((2, B, 1), dtype=torch.float32, device=dev).unbind(0)
                 pa, pr = act.data_ptr(), rew.data_ptr()
                 pd = pr + 4 * B
-            rc = self._fn_sample(self._ring, i_src, i_ptr, idx_hi, B, po, pn, pa, pr, pd, aug, o_src,
-                                 None if oo is None else oo[1], None if on is None else on[1], int(pad_or_size),
-                                 1 if normalize else 0, augmentations._seed, sub, _raw_stream(self._dev_index))
+            if pos:     # sample_curl: a third, independently cropped view of obs from the same launch
+                ps = torch.empty((B, c, ho, wo), dtype=torch.float32, device=dev)
+                rc = L.lib().augcl_ring_sample_curl(
+                    self._ring, i_src, i_ptr, idx_hi, B, po, pn, ps.data_ptr(), pa, pr, pd, o_src,
+                    None if oo is None else oo[1], None if on is None else on[1], None if op is None else op[1],
+                    int(pad_or_size), 1 if normalize else 0, augmentations._seed, sub, _raw_stream(self._dev_index))
+                self._pos = ps
+            else:
+                rc = self._fn_sample(self._ring, i_src, i_ptr, idx_hi, B, po, pn, pa, pr, pd, aug, o_src,
+                                     None if oo is None else oo[1], None if on is None else on[1], int(pad_or_size),
+                                     1 if normalize else 0, augmentations._seed, sub, _raw_stream(self._dev_index))
             if rc != 0:
-                raise L.AugclError("augcl_ring_sample_ex", rc, L.lib().augcl_last_error().decode(errors="replace"))
+                raise L.AugclError("augcl_ring_sample_curl" if pos else "augcl_ring_sample_ex", rc,
+                                   L.lib().augcl_last_error().decode(errors="replace"))
         finally:
             if guard is not None:
                 guard.__exit__(None, None, None)
-        self._keep = (keep_i, oo, on)   # page-locked host sources of a staged (B > 256) call must outlive the copy
+        self._keep = (keep_i, oo, on, op)   # page-locked host sources of a staged (B > 256) call must outlive the copy
         return o, act, rew, no, nd
 
     # ------------------------------------------------------------------ reference API
@@ -385,9 +395,9 @@ class ReplayBuffer(object):
             return obs, actions, rewards, next_obs, not_dones, obs.clone()
         offsets = offsets or {}
         obs, actions, rewards, next_obs, not_dones = self._sample(
-            idxs, aug=L.AUG_CROP, off_obs=offsets.get("obs"), off_next=offsets.get("next_obs"), pad_or_size=size)
-        pos = self._sample(idxs, next_obs=False, scalars=False, aug=L.AUG_CROP, off_obs=offsets.get("pos"),
-                           pad_or_size=size)[0]
+            idxs, aug=L.AUG_CROP, off_obs=offsets.get("obs"), off_next=offsets.get("next_obs"), pad_or_size=size,
+            pos=True, off_pos=offsets.get("pos"))
+        pos, self._pos = self._pos, None
         return obs, actions, rewards, next_obs, not_dones, pos
 
     def sample_drq(self, n=None, pad=4, *, idxs=None, offsets=None, device_indices=False):

@@ -159,6 +159,15 @@ int augcl_ring_sample_ex(augcl_ring* ring, int idx_src, const int64_t* idx, int6
                          int pad_or_size, int normalize, uint64_t seed, uint64_t subsequence,
                          augcl_stream stream);
 
+/* ReplayBuffer.sample_curl (src/utils.py:247-258) in ONE launch: three independent random crops of the same gather --
+ * obs, next_obs and pos = random_crop(obs.clone()) (src/augmentations.py:385-413) -- each with its own (w1, h1) offsets
+ * (int32[B,2]; PHILOX draws use subsequence + 1 / + 2 / + 3).  Any of the three outputs may be NULL.  Other arguments as
+ * in augcl_ring_sample_ex with aug_mode = CROP. */
+int augcl_ring_sample_curl(augcl_ring* ring, int idx_src, const int64_t* idx, int64_t idx_hi, int B, float* out_obs,
+                           float* out_next, float* out_pos, float* out_act, float* out_rew, float* out_nd, int off_src,
+                           const int32_t* off_obs, const int32_t* off_next, const int32_t* off_pos, int size,
+                           int normalize, uint64_t seed, uint64_t subsequence, augcl_stream stream);
+
 /* ------------------------------------------------------------------------------------------
  * Fused per-algorithm sampler: ONE kernel gathers the minibatch and writes every tensor an update needs.
  * Replaces, for one update() of

@@ -236,7 +236,7 @@ def test_fused_philox_draws_equal_explicit_draws(U, O, S, B):
         cm = S - 84
         oo = O.rng_randint(2 * B, 0, cm, 4242, sub + 1).reshape(B, 2)
         on = O.rng_randint(2 * B, 0, cm, 4242, sub + 2).reshape(B, 2)
-        op = O.rng_randint(2 * B, 0, cm, 4242, sub + 4).reshape(B, 2)     # second launch: (sub+3, +4, +5)
+        op = O.rng_randint(2 * B, 0, cm, 4242, sub + 3).reshape(B, 2)     # one launch: (indices, obs, next_obs, pos)
         want = buf.sample_curl(idxs=idx, size=84, offsets={"obs": oo, "next_obs": on, "pos": op})
         for g, w in zip(got, want):
             assert torch.equal(g, w)
@@ -254,3 +254,69 @@ def test_host_draws_are_validated(U):
         buf.sample_drq(pad=4, idxs=np.array([1, 2]), offsets={"obs": np.array([[0, 9], [0, 0]]), "next_obs": np.zeros((2, 2))})
     with pytest.raises(ValueError):
         buf.sample_drq(pad=4, idxs=np.array([1, 2]), offsets={"obs": np.zeros((3, 2)), "next_obs": np.zeros((2, 2))})
+
+
+def test_sweep_sizes_and_edge_batches(U):
+    """BASELINE.json configs[4] sizes: the batch-16384 launch (the sweep's maximum) equals the same draws taken 128 at a
+    time; batch 1, repeated indices and the ring's first / last slot behave like any other."""
+    cap, S = 100_000, 84
+    buf = U.ReplayBuffer((9, S, S), (6,), cap, 128)
+    buf.fill_synthetic(seed=9)
+    g = torch.Generator().manual_seed(4)
+    B = 16384
+    idxs = torch.randint(0, cap, (B,), generator=g).numpy()
+    idxs[:4] = (0, cap - 1, 0, cap - 1)
+    idxs[100:164] = idxs[100]                                   # 64 copies of one transition
+    off = {"obs": torch.randint(0, 9, (B, 2), generator=g).numpy(), "next_obs": torch.randint(0, 9, (B, 2), generator=g).numpy()}
+    big = buf.sample_drq(idxs=idxs, offsets=off)
+    assert big[0].shape == (B, 9, S, S) and big[1].shape == (B, 6) and big[2].shape == (B, 1)
+    assert torch.equal(big[0][100], big[0][101]) is (bool((off["obs"][100] == off["obs"][101]).all()))
+    for lo in (0, 128, 8192, B - 128):
+        sl = slice(lo, lo + 128)
+        part = buf.sample_drq(idxs=idxs[sl], offsets={"obs": off["obs"][sl], "next_obs": off["next_obs"][sl]})
+        for a, b in zip(big, part):
+            assert torch.equal(a[sl], b)
+    one = buf.sample_drq(idxs=idxs[:1], offsets={"obs": off["obs"][:1], "next_obs": off["next_obs"][:1]})
+    assert one[0].shape == (1, 9, S, S) and torch.equal(one[0][0], big[0][0]) and torch.equal(one[3][0], big[3][0])
+    plain = buf.sample(idxs=idxs[:300])                          # > 256: the staged (not by-value) host-draw path
+    ident = buf.sample_drq(idxs=idxs[:300], offsets={"obs": np.full((300, 2), 4), "next_obs": np.full((300, 2), 4)})
+    assert torch.equal(plain[0], ident[0]) and torch.equal(plain[3], ident[3])      # offset == pad is the identity
+    dev = buf.sample(idxs=torch.from_numpy(idxs[:300]).cuda())   # device-resident indices
+    assert torch.equal(plain[0], dev[0]) and torch.equal(plain[2], dev[2])
+    with pytest.raises(U.L.AugclError):
+        buf.sample(idxs=np.array([0, cap]))
+    with pytest.raises(U.L.AugclError):
+        buf.sample(idxs=np.array([-1]))
+
+
+def test_sample_curl_is_one_launch_with_three_independent_crops(U, O):
+    """sample_curl (src/utils.py:247-258): obs, next_obs and pos come out of ONE kernel launch; offsets that are not
+    supplied are drawn in the kernel from three distinct Philox subsequences (the same values augcl_rng_fill_offsets gives)."""
+    from augcl_b200 import _lib as L, augmentations as A
+    rng = np.random.RandomState(11)
+    S, size, k, cap, B = 100, 84, 3, 32, 10
+    buf = U.ReplayBuffer((3 * k, S, S), (2,), cap, B)
+    ora = O.HostRing((3 * k, S, S), (2,), cap, B)
+    frames = rng.randint(0, 256, (cap + k, 3, S, S)).astype(np.uint8)
+    for t in range(cap):
+        a = rng.randn(2).astype(np.float32)
+        buf.add(U.LazyFrames(list(frames[t:t + k])), a, 1.0, U.LazyFrames(list(frames[t + 1:t + 1 + k])), False)
+        ora.add(O.LazyFrames(frames[t:t + k]), a, 1.0, O.LazyFrames(frames[t + 1:t + 1 + k]), False)
+    idxs = rng.randint(0, cap, size=B)
+    o_obs, _, _, o_next, _ = ora.sample(idxs)
+    A.seed(77)
+    n0 = L.launch_count()
+    obs, act, rew, nxt, nd, pos = buf.sample_curl(idxs=idxs, size=size)
+    assert L.launch_count() - n0 == 1
+    draws = [O.rng_randint(2 * B, 0, S - size, 77, sub).reshape(B, 2) for sub in (1, 2, 3)]
+    assert torch.equal(obs.cpu(), O.random_crop(o_obs, size, draws[0][:, 0], draws[0][:, 1]))
+    assert torch.equal(nxt.cpu(), O.random_crop(o_next, size, draws[1][:, 0], draws[1][:, 1]))
+    assert torch.equal(pos.cpu(), O.random_crop(o_obs, size, draws[2][:, 0], draws[2][:, 1]))
+    assert not np.array_equal(draws[0], draws[2])
+    # mixed: one supplied (host) offset array, the other two drawn
+    A.seed(78)
+    mine = rng.randint(0, S - size, (B, 2))
+    obs2, _, _, nxt2, _, pos2 = buf.sample_curl(idxs=idxs, size=size, offsets={"pos": mine})
+    assert torch.equal(pos2.cpu(), O.random_crop(o_obs, size, mine[:, 0], mine[:, 1]))
+    d1 = O.rng_randint(2 * B, 0, S - size, 78, 1).reshape(B, 2)
+    assert torch.equal(obs2.cpu(), O.random_crop(o_obs, size, d1[:, 0], d1[:, 1]))
