@@ -28,7 +28,8 @@ from . import _lib as L
 
 __all__ = ["random_shift", "random_crop", "random_conv", "random_overlay", "splice", "CS_splice",
            "random_grayscale", "random_flip", "random_rotation", "random_cutout_color",
-           "identity", "aug_to_func", "seed", "set_background_bank", "load_dataloader"]
+           "identity", "aug_to_func", "seed", "set_background_bank", "load_dataloader", "create_hsv_mask",
+           "view_as_windows_cuda", "color_jitter"]
 
 # --------------------------------------------------------------------------------------------
 # process-global state (the reference keeps `dataloader` / `data_iter` globals, :11-12)
@@ -263,6 +264,28 @@ def _splice(x, thr, variant, who, bank_idx, dataset):
         L.call("augcl_splice", x.data_ptr(), out.data_ptr(), n, c, h, w, bank.data_ptr(), bdt, bank.shape[0],
                rows.data_ptr(), float(thr[0]), float(thr[1]), float(thr[2]), variant, _stream(x))
     return out
+
+
+def create_hsv_mask(x_rgb, hue_thres, sat_thres, val_thres):
+    """src/augmentations.py:277-284: boolean mask (n,3,h,w) of the pixels of an RGB batch IN [0,1] whose kornia-HSV hue,
+    saturation and value all exceed the thresholds (splice evaluates the same test inside its kernel)."""
+    x = _prep(x_rgb, "create_hsv_mask")
+    n, c, h, w = x.shape
+    if c != 3:
+        raise ValueError(f"create_hsv_mask: expected (n,3,h,w), got {tuple(x.shape)}")
+    with torch.cuda.device(x.device):
+        m = torch.empty((n, h, w), dtype=torch.uint8, device=x.device)
+        L.call("augcl_hsv_mask", x.data_ptr(), m.data_ptr(), n, h, w, float(hue_thres), float(sat_thres), float(val_thres),
+               _stream(x))
+    return m.bool().unsqueeze(1).repeat(1, 3, 1, 1)
+
+
+def view_as_windows_cuda(x, window_shape):
+    """src/augmentations.py:416-433: strided view of every window (pure metadata; random_crop itself is a kernel)."""
+    assert isinstance(window_shape, tuple) and len(window_shape) == len(x.shape), \
+        "window_shape must be a tuple with same number of dimensions as x"
+    win_indices_shape = [x.size(0), x.size(1) - int(window_shape[1]), x.size(2) - int(window_shape[2]), x.size(3)]
+    return x.as_strided(tuple(win_indices_shape + list(window_shape)), tuple(list(x.stride()) + list(x.stride())))
 
 
 def splice(x, hue_thres=0, sat_thres=0, val_thres=0.6, *, bank_idx=None, dataset="coco"):

@@ -6,6 +6,7 @@
 // These functions came from RAD, where images are in [0,1]; the reference applies them to its 0..255 tensors
 // unchanged, and so do these kernels (e.g. grayscale's x*255 -> uint8 wraps modulo 256 exactly like torch's CPU cast).
 #include "common.cuh"
+#include "pixel.cuh"
 
 namespace augcl {
 
@@ -84,11 +85,35 @@ static int check_args(const char* who, const float* in, float* out, int n, int c
   return AUGCL_OK;
 }
 
+// create_hsv_mask (/root/reference/src/augmentations.py:277-284): kornia HSV of an RGB image already in [0,1], all three
+// channels strictly above their thresholds.  One thread per pixel; mask[n][h*w] = 0 / 1.
+__global__ void __launch_bounds__(256) hsv_mask_kernel(const float* __restrict__ rgb, uint8_t* __restrict__ mask, int64_t npix,
+                                                       int hw, float ht, float st, float vt) {
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < npix; e += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t i = e / hw;
+    const int px = (int)(e - i * hw);
+    const float* b = rgb + i * 3 * hw + px;
+    mask[e] = hsv_gt(__ldg(b), __ldg(b + hw), __ldg(b + 2 * (int64_t)hw), ht, st, vt) ? 1 : 0;
+  }
+}
+
 }  // namespace augcl
 
 using namespace augcl;
 
 extern "C" {
+
+int augcl_hsv_mask(const float* rgb, uint8_t* mask, int n, int h, int w, float hue_thres, float sat_thres, float val_thres,
+                   augcl_stream stream) {
+  AUGCL_REQUIRE(rgb && mask, "augcl_hsv_mask: rgb/mask is NULL");
+  AUGCL_REQUIRE(n > 0 && h > 0 && w > 0, "augcl_hsv_mask: n, h, w must be positive");
+  const int64_t npix = (int64_t)n * h * w;
+  int64_t blocks = (npix + 255) / 256;
+  if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
+  hsv_mask_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(rgb, mask, npix, h * w, hue_thres, sat_thres, val_thres);
+  AUGCL_LAUNCHED();
+  return AUGCL_OK;
+}
 
 int augcl_random_grayscale(const float* in, float* out, int n, int c, int h, int w, const uint8_t* mask,
                            augcl_stream stream) {

@@ -259,6 +259,11 @@ int augcl_splice(const float* in, float* out, int n, int c, int h, int w, const 
                  int bank_dtype, int64_t bank_len, const int64_t* bank_idx, float hue_thres,
                  float sat_thres, float val_thres, int variant, augcl_stream stream);
 
+/* create_hsv_mask (src/augmentations.py:277-284): rgb f32 [n,3,h,w] ALREADY in [0,1] (the reference passes x/255);
+ * mask u8 [n,h,w] = 1 where kornia-HSV hue, saturation and value all exceed their thresholds (strictly). */
+int augcl_hsv_mask(const float* rgb, uint8_t* mask, int n, int h, int w, float hue_thres, float sat_thres, float val_thres,
+                   augcl_stream stream);
+
 /* ------------------------------------------------------------------------------------------
  * The remaining aug_to_func entries (src/augmentations.py:436-449).  Inherited from RAD, where images are
  * in [0,1]; the reference applies them to its 0..255 tensors unchanged and so do these.

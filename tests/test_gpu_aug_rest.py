@@ -52,3 +52,25 @@ def test_rest_draws_follow_numpy_like_the_reference():
     assert A.aug_to_func["rotate"] is A.random_rotation and A.aug_to_func["cutout_color"] is A.random_cutout_color
     with pytest.raises(Exception):
         A.random_rotation(torch.zeros(2, 3, 8, 10, device="cuda"))      # non-square
+
+
+def test_create_hsv_mask_and_view_as_windows():
+    """The two helpers splice / random_crop are built from in the reference (src/augmentations.py:277-284, :416-433)."""
+    from augcl_b200 import augmentations as A
+    from oracle import augcl_oracle as O
+    g = torch.Generator().manual_seed(5)
+    u8 = torch.randint(0, 256, (6, 3, 84, 84), generator=g, dtype=torch.uint8)
+    u8[0, :, :10] = u8[0, 0:1, :10]                       # grey rows: saturation 0
+    u8[1, 1, :20] = u8[1, 2, :20]                         # g == b where r may be the maximum: hue 0
+    x = u8.float() / 255.0
+    for thr in ((0, 0, 0.6), (0, 0, 0.4), (3.5, 0, 0), (1.0, 0.3, 0.2)):
+        got = A.create_hsv_mask(x.cuda(), *thr)
+        want = O.hsv_mask(x, *thr)
+        assert got.dtype == torch.bool and got.shape == (6, 3, 84, 84)
+        assert torch.equal(got.cpu(), want.unsqueeze(1).repeat(1, 3, 1, 1)), thr
+    # used the way the reference's random_crop does (:401-408): NHWC view, windows[arange(n), w1, h1]
+    y = torch.randint(0, 256, (4, 9, 20, 20), generator=g).float()
+    w1, h1 = torch.tensor([0, 3, 7, 2]), torch.tensor([7, 0, 1, 5])
+    win = A.view_as_windows_cuda(y.cuda().permute(0, 2, 3, 1), (1, 12, 12, 1))[..., 0, :, :, 0]
+    assert win.shape == (4, 8, 8, 9, 12, 12)
+    assert torch.equal(win[torch.arange(4), w1, h1].cpu(), O.random_crop(y, 12, w1.numpy(), h1.numpy()))

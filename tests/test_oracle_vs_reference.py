@@ -74,3 +74,18 @@ def test_live_remaining_augs(unit_range):
     assert torch.equal(R.ref_random_rotation(x, rot), O.random_rotation(x, rot))
     w1, h1, ci = rng.randint(1, 15, n), rng.randint(1, 15, n), rng.randint(0, 255, (n, 9))
     assert torch.equal(R.ref_random_cutout_color(x, w1, h1, ci), O.random_cutout_color(x, w1, h1, ci / 255.0))
+
+
+def test_live_view_as_windows_and_hsv_mask():
+    """The product's pure-metadata view_as_windows_cuda equals the reference's (src/augmentations.py:416-433); the oracle's
+    hsv_mask equals the reference's create_hsv_mask (:277-284) run with the kornia restatement of ref_harness."""
+    from augcl_b200 import augmentations as A
+    aug, _ = R.load_reference()
+    g = torch.Generator().manual_seed(9)
+    y = torch.rand(3, 20, 20, 9, generator=g)
+    assert torch.equal(aug.view_as_windows_cuda(y, (1, 12, 12, 1)), A.view_as_windows_cuda(y, (1, 12, 12, 1)))
+    x = torch.randint(0, 256, (4, 3, 16, 16), generator=g).float() / 255.0
+    with R.cpu_shims():
+        for thr in ((0, 0, 0.6), (3.5, 0, 0), (1.0, 0.3, 0.2)):
+            want = aug.create_hsv_mask(x, *thr)
+            assert torch.equal(O.hsv_mask(x, *thr).unsqueeze(1).repeat(1, 3, 1, 1), want), thr
