@@ -26,10 +26,11 @@ std::atomic<int> g_fused_ctas_per_sm{0};   // 0 = auto
 std::atomic<int> g_fused_cost_obs{0};    // 0 = auto
 std::atomic<int> g_fused_cost_next{0};
 std::atomic<int> g_fused_stages{0};      // 0 = auto
+std::atomic<int> g_fused_dynamic{1};     // 1: atomic-ticket unit schedule, 0: static cost partition
 std::atomic<int> g_fused_band{0};        // 0 = auto (non-conv chains: 14 or 7 rows)
 std::atomic<int> g_fused_fast_mask{1};   // 0: always the float HSV path (A/B and the exhaustive equivalence test)
 
-constexpr int kFHeader = 256 + 432;   // mbarriers + metas + conv weights
+constexpr int kFHeader = 256 + 432 + 16;   // mbarriers + metas + conv weights + per-stage "holds a unit" flags
 constexpr int kFBand = 12;        // conv chains: 12 rows + 2 halo rows = 14 tile rows = two rounds of 7 rows
 constexpr int kFBandNoConv = 14;  // every other chain: 14 rows = two full rounds, 84 = 6 bands
 constexpr int kFThreads = 160;   // 147 = 7 rows x 21 quads work at W = 84: a 14-row tile is exactly two rounds
@@ -52,6 +53,7 @@ struct FusedParams {
   int64_t units_obs, units_next;
   int cost_obs, cost_next;
   int plane_stage, bank_stage, stage_bytes, tile_rs, stages;
+  uint32_t* sched;          // dynamic schedule: {next ticket, CTAs done}; NULL = static cost partition
   int normalize;
 };
 
@@ -85,7 +87,8 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem);                 // <= 4 mbarriers
   FusedMeta* meta = reinterpret_cast<FusedMeta*>(smem + 32);          // <= 4 metas (4 x 56 B = 224 B)
   float* wsm = reinterpret_cast<float*>(smem + 256);                  // [27][4] conv weights / 255
-  uint8_t* stage = smem + kFHeader;                                   // NS x stage_bytes (688 = 16 * 43: 16-B aligned)
+  int* valid = reinterpret_cast<int*>(smem + 256 + 432);              // [4]: stage holds a unit (dynamic schedule)
+  uint8_t* stage = smem + kFHeader;                                   // NS x stage_bytes (704 = 16 * 44: 16-B aligned)
   const int NS = p.stages;
   float* tile = reinterpret_cast<float*>(stage + NS * p.stage_bytes); // [3][kFBand+2][tile_rs]
   const int tid = threadIdx.x;
@@ -108,8 +111,12 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
     if (c <= To) return (c + p.cost_obs - 1) / p.cost_obs;
     return p.units_obs + (c - To + p.cost_next - 1) / p.cost_next;
   };
+  const bool dyn = p.sched != nullptr;
   const int64_t u0 = first_unit_at(c0), u1 = first_unit_at(c1);
-  const int nun = (int)(u1 - u0);
+  // dynamic schedule: units are handed out one at a time, in order (heavy obs units first, next_obs copies fill the
+  // tail), by an atomic ticket counter; the loop below then runs until a stage comes back empty
+  const int nun = dyn ? 0x7fffffff : (int)(u1 - u0);
+  const uint32_t total_units = (uint32_t)(p.units_obs + p.units_next);
 
   if (tid == 0) {
     for (int s = 0; s < NS; ++s) mbar_init(&bars[s], 1);
@@ -118,8 +125,15 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
   __syncthreads();
   pdl_wait();
 
-  auto issue = [&](int kk, int s) {   // one lane: decode unit u0+kk, write its meta, start its copies into stage s
+  constexpr uint32_t kFetch = 0xffffffffu;
+  // one lane: decode unit u0+kk (static) / the next ticket (dynamic), write its meta, start its copies into stage s
+  auto issue = [&](int kk, int s, uint32_t ticket) {
     uint32_t u = (uint32_t)(u0 + kk);          // host: units_obs + units_next < 2^31 -> 32-bit divisions
+    if (dyn) {
+      u = ticket != kFetch ? ticket : atomicAdd(p.sched, 1u);
+      valid[s] = u < total_units;
+      if (u >= total_units) return;
+    }
     const int t = u >= (uint32_t)p.units_obs ? 1 : 0;
     if (t) u -= (uint32_t)p.units_obs;
     const uint32_t fr = u / (uint32_t)p.bands;  // frame row of x.reshape(B*k, 3, H, W)
@@ -184,7 +198,15 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
     }
   };
 
-  if (tid < NS && tid < nun) issue(tid, tid);   // the prologue copies are prepared by NS lanes in parallel
+  if (tid < 32) {   // the prologue copies are prepared by NS lanes in parallel (dynamic: NS consecutive tickets, in stage order)
+    uint32_t base = 0;
+    if (dyn) {
+      if (tid == 0) base = atomicAdd(p.sched, (uint32_t)NS);
+      base = __shfl_sync(0xffffffffu, base, 0);
+    }
+    if (tid < NS && tid < nun) issue(tid, tid, base + tid);
+  }
+  if (dyn) __syncthreads();                     // valid[] of the prologue stages
   pdl_launch_dependents();
   gather_scalars(p.sp, none);
 
@@ -192,6 +214,7 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
   int s = 0;
   auto next_stage = [&]() { if (++s == NS) { s = 0; phase ^= 1; } };
   for (int kk = 0; kk < nun; ++kk) {
+    if (dyn && !valid[s]) break;   // written >= one __syncthreads ago (NS >= 2 in this mode)
     mbar_wait(&bars[s], phase);
     const FusedMeta m = meta[s];
     const uint8_t* sb = stage + (size_t)s * p.stage_bytes;
@@ -232,7 +255,7 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
         if (m.o_shift) { load_shift(r, q4, w); store3(m.o_shift, oo, w); }
       }
       __syncthreads();   // stage s consumed
-      if (tid == 0 && kk + NS < nun) issue(kk + NS, s);
+      if (tid == 0 && kk + NS < nun) issue(kk + NS, s, kFetch);
       next_stage();
       continue;
     }
@@ -320,7 +343,7 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
       }
     }
     __syncthreads();   // stage s consumed (refill may start), tile + wsm complete
-    if (tid == 0 && kk + NS < nun) issue(kk + NS, s);
+    if (tid == 0 && kk + NS < nun) issue(kk + NS, s, kFetch);
     // ---------------- phase B: conv on the tile ----------------
     if (CONV) {
       const int npair = (m.rows + 1) >> 1;
@@ -372,6 +395,16 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
       __syncthreads();   // tile and wsm are free again
     }
     next_stage();
+  }
+  if (dyn && tid == 0) {
+    // the last CTA to run out of units re-arms the counters for the next launch on this ring (launches of one ring
+    // are stream-ordered, and a PDL successor takes its first ticket only after griddepcontrol.wait)
+    __threadfence();
+    if (atomicAdd(p.sched + 1, 1u) == gridDim.x - 1) {
+      p.sched[0] = 0;
+      p.sched[1] = 0;
+      __threadfence();
+    }
   }
 }
 
@@ -509,6 +542,7 @@ extern "C" int augcl_ring_sample_fused(augcl_ring* r, const augcl_fused_desc* d,
   p.stages = g_fused_stages.load() > 0 ? g_fused_stages.load() : (has_conv ? 2 : ((ops & 7) ? 4 : 3));
   while (p.stages > 1 && kFHeader + (size_t)p.stages * p.stage_bytes + tile_bytes > 100 * 1024) --p.stages;
   const size_t smem = kFHeader + (size_t)p.stages * p.stage_bytes + tile_bytes;
+  p.sched = (g_fused_dynamic.load() && p.stages >= 2) ? r->sched : nullptr;
   if (smem > 200 * 1024) AUGCL_FAIL(AUGCL_ERR_UNSUPPORTED, "%s: geometry needs %zu B of shared memory", who, smem);
 
   DeviceGuard g(r->device);

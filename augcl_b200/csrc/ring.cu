@@ -304,7 +304,10 @@ static int ring_create_impl(const char* who, augcl_ring** out, int device, int64
   if (e == cudaSuccess) e = cudaMalloc(&r->act, fbytes * action_dim);
   if (e == cudaSuccess) e = cudaMalloc(&r->rew, fbytes);
   if (e == cudaSuccess) e = cudaMalloc(&r->nd, fbytes);
+  if (e == cudaSuccess) e = cudaMalloc(&r->sched, 64);
+  if (e == cudaSuccess) e = cudaMemset(r->sched, 0, 64);
   if (e != cudaSuccess) {
+    cudaFree(r->sched);
     cudaFree(r->obs); cudaFree(r->next); cudaFree(r->refs); cudaFree(r->act); cudaFree(r->rew); cudaFree(r->nd);
     delete r;
     cudaGetLastError();
@@ -329,6 +332,7 @@ int augcl_ring_destroy(augcl_ring* r) {
   if (!r) return AUGCL_OK;
   DeviceGuard g(r->device);
   cudaFree(r->obs); cudaFree(r->next); cudaFree(r->refs); cudaFree(r->act); cudaFree(r->rew); cudaFree(r->nd);
+  cudaFree(r->sched);
   delete r;
   return AUGCL_OK;
 }

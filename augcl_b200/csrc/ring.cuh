@@ -23,6 +23,7 @@ struct augcl_ring {
   int64_t bytes;
   // "v2" (de-duplicated) layout: obs = frame pool [pool][cpf][H][W] u8, next = NULL,
   // refs[capacity][2][k] = pool slot of every frame of (obs, next_obs)
+  uint32_t* sched;   // {ticket, done} counters of the fused sampler's dynamic unit schedule (zero between launches)
   int dedup;
   int64_t pool;
   int32_t* refs;

@@ -16,6 +16,7 @@ extern std::atomic<int> g_fused_cost_next;
 extern std::atomic<int> g_fused_fast_mask;
 extern std::atomic<int> g_fused_stages;
 extern std::atomic<int> g_fused_band;
+extern std::atomic<int> g_fused_dynamic;
 static thread_local std::string t_error;
 void set_error(const std::string& msg) { t_error = msg; }
 }  // namespace augcl
@@ -57,6 +58,7 @@ int augcl_set_option(const char* key, const char* value) {
     AUGCL_REQUIRE(v >= 0 && v <= 4, "fused_stages must be in [0,4] (0 = auto)");
     g_fused_stages = v; return AUGCL_OK;
   }
+  if (!strcmp(key, "fused_dynamic")) { g_fused_dynamic = atoi(value) != 0; return AUGCL_OK; }
   if (!strcmp(key, "fused_band")) {
     int v = atoi(value);
     AUGCL_REQUIRE(v >= 0 && v <= 14, "fused_band must be in [0,14] (0 = auto)");
