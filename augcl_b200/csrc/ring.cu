@@ -466,6 +466,26 @@ static int sample_impl(const char* who, augcl_ring* r, int idx_src, const int64_
     AUGCL_REQUIRE(idx_hi > 0 && idx_hi <= r->capacity, "%s: idx_hi %lld outside (0, capacity]", who, (long long)idx_hi);
   else
     AUGCL_REQUIRE(idx, "%s: idx is NULL", who);
+  // Larger batches go through the band-of-frames kernel of fused.cu (same outputs bit for bit, same draws): its dynamic
+  // unit schedule is 5-8 % faster from batch 256 up (scripts/bench_fused.py drq_shift_both vs this kernel); the plane
+  // kernel below keeps the short launches (batch 128: 15.8 vs 18.2 us).
+  {
+    const int min_b = g_sample_fused_min_batch.load();
+    if (min_b > 0 && B >= min_b && aug_mode != AUGCL_AUG_CROP && !out_pos && g_staging.load() == 0 && r->cpf == 3 &&
+        (r->W & 3) == 0 && ((r->H * r->W) & 15) == 0 && r->W <= 128 && r->W >= 8 && pad_or_size <= 63 &&
+        aligned(out_obs, 16) && aligned(out_next, 16)) {
+      augcl_fused_desc d{};
+      d.struct_size = (int32_t)sizeof(d);
+      d.B = B; d.idx_src = idx_src; d.off_src = off_src; d.idx = idx; d.idx_hi = idx_hi;
+      d.pad = aug_mode == AUGCL_AUG_NONE ? 0 : pad_or_size; d.normalize = normalize; d.seed = seed; d.subsequence = subsequence;
+      d.out_act = out_act; d.out_rew = out_rew; d.out_nd = out_nd;
+      const bool sh_obs = aug_mode != AUGCL_AUG_NONE && (off_obs || off_src == AUGCL_SRC_PHILOX);
+      const bool sh_next = aug_mode == AUGCL_AUG_SHIFT && !obs_only && (off_next || off_src == AUGCL_SRC_PHILOX);
+      if (sh_obs) { d.out_obs_shift = out_obs; d.off_obs = off_obs; } else d.out_obs = out_obs;
+      if (sh_next) { d.out_next_shift = out_next; d.off_next = off_next; } else d.out_next = out_next;
+      return augcl_ring_sample_fused(r, &d, (augcl_stream)st);
+    }
+  }
   SampleParams p{};
   p.store[0] = r->obs; p.store[1] = r->next; p.refs = r->dedup ? r->refs : nullptr; p.k = r->k; p.cpf = r->cpf;
   p.out[0] = out_obs; p.out[1] = out_next; p.out[2] = out_pos;

@@ -8,6 +8,7 @@ extern std::atomic<int> g_sample_stages;
 extern std::atomic<int> g_sample_ctas_per_sm;
 extern std::atomic<int> g_sample_pdl;
 extern std::atomic<int> g_sample_band;
+extern std::atomic<int> g_sample_fused_min_batch;
 }
 
 struct augcl_ring {

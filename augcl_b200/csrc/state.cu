@@ -10,6 +10,7 @@ std::atomic<int> g_sample_stages{0};   // 0 = auto (4 when a CTA gets few units,
 std::atomic<int> g_sample_ctas_per_sm{6};
 std::atomic<int> g_sample_pdl{1};
 std::atomic<int> g_sample_band{1};
+std::atomic<int> g_sample_fused_min_batch{256};   // augcl_ring_sample*: batches >= this use the fused.cu kernel (0 = never)
 extern std::atomic<int> g_fused_ctas_per_sm;   // fused.cu
 extern std::atomic<int> g_fused_cost_obs;
 extern std::atomic<int> g_fused_cost_next;
@@ -46,6 +47,7 @@ int augcl_set_option(const char* key, const char* value) {
     g_sample_ctas_per_sm = v; return AUGCL_OK;
   }
   if (!strcmp(key, "sample_pdl")) { g_sample_pdl = atoi(value) != 0; return AUGCL_OK; }
+  if (!strcmp(key, "sample_fused_min_batch")) { g_sample_fused_min_batch = atoi(value); return AUGCL_OK; }
   if (!strcmp(key, "sample_band")) { g_sample_band = atoi(value) != 0; return AUGCL_OK; }
   if (!strcmp(key, "fused_ctas_per_sm")) {
     int v = atoi(value);
