@@ -56,6 +56,7 @@ SIGNATURES = {
     "augcl_ring_sample": (_i, [_p, _p, _i, _p, _p, _p, _p, _p, _i, _p, _p, _i, _i, _p]),
     "augcl_ring_sample_ex": (_i, [_p, _i, _p, _i64, _i, _p, _p, _p, _p, _p, _i, _i, _p, _p, _i, _i, _u64, _u64, _p]),
     "augcl_ring_sample_curl": (_i, [_p, _i, _p, _i64, _i, _p, _p, _p, _p, _p, _p, _i, _p, _p, _p, _i, _i, _u64, _u64, _p]),
+    "augcl_ring_sample_views": (_i, [_p, _i, _p, _i64, _i, _i, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _u64, _u64, _p]),
     "augcl_ring_sample_fused": (_i, [_p, C.POINTER(FusedDesc), _p]),
     "augcl_random_shift": (_i, [_p, _p, _i, _i, _i, _i, _i, _p, _i, _p, _p]),
     "augcl_drq_base_grid": (_i, [_i, _i, C.POINTER(_f)]),

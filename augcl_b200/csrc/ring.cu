@@ -449,15 +449,27 @@ int augcl_ring_fill_synthetic(augcl_ring* r, int64_t count, uint64_t seed, augcl
 static int sample_impl(const char* who, augcl_ring* r, int idx_src, const int64_t* idx, int64_t idx_hi, int B,
                        float* out_obs, float* out_next, float* out_act, float* out_rew, float* out_nd, int aug_mode,
                        int off_src, const int32_t* off_obs, const int32_t* off_next, int pad_or_size, int normalize,
-                       uint64_t seed, uint64_t subsequence, cudaStream_t st, float* out_pos = nullptr,
-                       const int32_t* off_pos = nullptr) {
+                       uint64_t seed, uint64_t subsequence, cudaStream_t st, int n_extra = 0,
+                       const int* extra_src = nullptr, float* const* extra_out = nullptr,
+                       const int32_t* const* extra_off = nullptr) {
   AUGCL_REQUIRE(r, "%s: ring is NULL", who);
   AUGCL_REQUIRE(B > 0, "%s: B must be positive (got %d)", who, B);
-  AUGCL_REQUIRE(out_obs || out_next || out_pos, "%s: every image output is NULL", who);
+  AUGCL_REQUIRE(n_extra >= 0 && n_extra <= kMaxViews - 2, "%s: at most %d extra views", who, kMaxViews - 2);
+  const int32_t* off[kMaxViews] = {off_obs, off_next};
+  float* outs[kMaxViews] = {out_obs, out_next};
+  int vsrc[kMaxViews] = {0, 1};
+  bool any_out = out_obs || out_next;
+  for (int v = 0; v < n_extra; ++v) {
+    AUGCL_REQUIRE(extra_src && extra_out && (extra_src[v] == 0 || extra_src[v] == 1), "%s: bad extra view %d", who, v);
+    outs[2 + v] = extra_out[v]; off[2 + v] = extra_off ? extra_off[v] : nullptr; vsrc[2 + v] = extra_src[v];
+    any_out = any_out || extra_out[v];
+  }
+  const bool has_extra = n_extra > 0;
+  AUGCL_REQUIRE(any_out, "%s: every image output is NULL", who);
   AUGCL_REQUIRE(aug_mode == AUGCL_AUG_NONE || aug_mode == AUGCL_AUG_SHIFT || aug_mode == AUGCL_AUG_CROP ||
                     aug_mode == AUGCL_AUG_SHIFT_OBS, "%s: unknown aug_mode %d", who, aug_mode);
   const bool obs_only = aug_mode == AUGCL_AUG_SHIFT_OBS;
-  if (obs_only) { aug_mode = AUGCL_AUG_SHIFT; off_next = nullptr; }
+  if (obs_only) { aug_mode = AUGCL_AUG_SHIFT; off_next = nullptr; off[1] = nullptr; }
   AUGCL_REQUIRE(idx_src == AUGCL_SRC_DEVICE || idx_src == AUGCL_SRC_HOST || idx_src == AUGCL_SRC_PHILOX,
                 "%s: unknown idx_src %d", who, idx_src);
   AUGCL_REQUIRE(off_src == AUGCL_SRC_DEVICE || off_src == AUGCL_SRC_HOST || off_src == AUGCL_SRC_PHILOX,
@@ -471,7 +483,7 @@ static int sample_impl(const char* who, augcl_ring* r, int idx_src, const int64_
   // kernel below keeps the short launches (batch 128: 15.8 vs 18.2 us).
   {
     const int min_b = g_sample_fused_min_batch.load();
-    if (min_b > 0 && B >= min_b && aug_mode != AUGCL_AUG_CROP && !out_pos && g_staging.load() == 0 && r->cpf == 3 &&
+    if (min_b > 0 && B >= min_b && aug_mode != AUGCL_AUG_CROP && !has_extra && g_staging.load() == 0 && r->cpf == 3 &&
         (r->W & 3) == 0 && ((r->H * r->W) & 15) == 0 && r->W <= 128 && r->W >= 8 && pad_or_size <= 63 &&
         aligned(out_obs, 16) && aligned(out_next, 16)) {
       augcl_fused_desc d{};
@@ -488,16 +500,13 @@ static int sample_impl(const char* who, augcl_ring* r, int idx_src, const int64_
   }
   SampleParams p{};
   p.store[0] = r->obs; p.store[1] = r->next; p.refs = r->dedup ? r->refs : nullptr; p.k = r->k; p.cpf = r->cpf;
-  p.out[0] = out_obs; p.out[1] = out_next; p.out[2] = out_pos;
-  p.vsrc[0] = 0; p.vsrc[1] = 1; p.vsrc[2] = 0;
+  for (int v = 0; v < kMaxViews; ++v) { p.out[v] = outs[v]; p.vsrc[v] = vsrc[v]; }
   p.idx = idx; p.act = r->act; p.rew = r->rew; p.nd = r->nd;
   p.out_act = out_act; p.out_rew = out_rew; p.out_nd = out_nd;
   p.capacity = r->capacity;
   p.B = B; p.C = r->C; p.H = r->H; p.W = r->W; p.A = r->A;
   p.Ho = r->H; p.Wo = r->W; p.pad = 0; p.normalize = normalize ? 1 : 0;
   p.idx_mode = idx_src; p.idx_hi = (uint64_t)idx_hi; p.seed = seed; p.subseq = subsequence;
-  const int32_t* off[3] = {off_obs, off_next, off_pos};
-  float* outs[3] = {out_obs, out_next, out_pos};
   int hi_row = 0, hi_col = 0;   // valid offsets: row in [0, hi_row], col in [0, hi_col]
   if (aug_mode == AUGCL_AUG_SHIFT) {
     AUGCL_REQUIRE(pad_or_size >= 0 && pad_or_size < (1 << 15), "%s: bad pad %d", who, pad_or_size);
@@ -513,7 +522,7 @@ static int sample_impl(const char* who, augcl_ring* r, int idx_src, const int64_
     if (off_src == AUGCL_SRC_PHILOX)
       AUGCL_REQUIRE(r->H == r->W && p.off_range > 0, "%s: PHILOX crop offsets need a square image larger than the crop", who);
   }
-  for (int t = 0; t < 3; ++t) {
+  for (int t = 0; t < kMaxViews; ++t) {
     if (aug_mode == AUGCL_AUG_NONE || !outs[t] || (obs_only && t == 1)) { p.off_mode[t] = kSrcNone; continue; }
     if (off_src == AUGCL_SRC_PHILOX) { p.off_mode[t] = off[t] ? AUGCL_SRC_DEVICE : AUGCL_SRC_PHILOX; p.off[t] = off[t]; continue; }
     if (!off[t]) {
@@ -525,9 +534,8 @@ static int sample_impl(const char* who, augcl_ring* r, int idx_src, const int64_
     p.off[t] = off[t];
   }
   p.nt = 0;
-  if (out_obs) p.tmap[p.nt++] = 0;
-  if (out_next) p.tmap[p.nt++] = 1;
-  if (out_pos) p.tmap[p.nt++] = 2;
+  for (int v = 0; v < kMaxViews; ++v)
+    if (outs[v]) p.tmap[p.nt++] = v;
   AUGCL_REQUIRE((int64_t)B * p.nt * p.C < (1ll << 31), "%s: batch too large", who);
   DeviceGuard g(r->device);
   AUGCL_CUDA(g.err);
@@ -535,14 +543,15 @@ static int sample_impl(const char* who, augcl_ring* r, int idx_src, const int64_
   // ---- HOST draws: validate (the reference raises IndexError on a bad index), then carry them by value
   //      in the launch (small batches, band geometries) or stage them through stream-ordered scratch.
   const bool host_idx = idx_src == AUGCL_SRC_HOST;
-  const bool host_off = off_src == AUGCL_SRC_HOST &&
-                        (p.off_mode[0] == AUGCL_SRC_HOST || p.off_mode[1] == AUGCL_SRC_HOST || p.off_mode[2] == AUGCL_SRC_HOST);
+  bool host_off = false, host_off_extra = false;
+  for (int t = 0; t < kMaxViews; ++t)
+    if (off_src == AUGCL_SRC_HOST && p.off_mode[t] == AUGCL_SRC_HOST) { host_off = true; host_off_extra = host_off_extra || t >= 3; }
   if (host_idx)
     for (int b = 0; b < B; ++b)
       AUGCL_REQUIRE(idx[b] >= 0 && idx[b] < r->capacity, "%s: index %lld (position %d) out of range [0, %lld)", who,
                     (long long)idx[b], b, (long long)r->capacity);
   if (host_off)
-    for (int t = 0; t < 3; ++t)
+    for (int t = 0; t < kMaxViews; ++t)
       if (p.off_mode[t] == AUGCL_SRC_HOST)
         for (int e = 0; e < 2 * B; ++e)
           AUGCL_REQUIRE(off[t][e] >= 0 && off[t][e] <= ((e & 1) ? hi_col : hi_row),
@@ -552,7 +561,9 @@ static int sample_impl(const char* who, augcl_ring* r, int idx_src, const int64_
   const int P = p.H * p.W;
   p.stage_bytes = ((P + 15) & ~15) + 32;
   const int kHeader = 64 + 8 * (int)sizeof(BandMeta);   // mbarriers + per-stage metas (both kernels fit in it)
-  const bool vec_ok = (p.Wo % 4 == 0) && aligned(out_obs, 16) && aligned(out_next, 16) && aligned(out_pos, 16) &&
+  bool outs_aligned = true;
+  for (int v = 0; v < kMaxViews; ++v) outs_aligned = outs_aligned && aligned(outs[v], 16);
+  const bool vec_ok = (p.Wo % 4 == 0) && outs_aligned &&
                       kHeader + p.stage_bytes <= kMaxSmem;
   const bool staged = g_staging.load() == 0 && vec_ok;
   int geom = 0;   // compile-time geometries of the reference's two image sizes (src/arguments.py:155-163)
@@ -566,7 +577,7 @@ static int sample_impl(const char* who, augcl_ring* r, int idx_src, const int64_
   bool use_inline = false;
   void* scratch = nullptr;
   if (host_idx || host_off) {
-    if (geom && B <= kInlineMax && r->capacity < (1ll << 31) && hi_row <= 127 && hi_col <= 127) {
+    if (geom && B <= kInlineMax && r->capacity < (1ll << 31) && hi_row <= 127 && hi_col <= 127 && !host_off_extra) {
       use_inline = true;
       if (host_idx) {
         for (int b = 0; b < B; ++b) inl.idx[b] = (int32_t)idx[b];
@@ -578,9 +589,9 @@ static int sample_impl(const char* who, augcl_ring* r, int idx_src, const int64_
           p.off_mode[t] = kSrcInline;
         }
     } else {
-      // stream-ordered scratch: [idx int64 B][off_obs int32 2B][off_next int32 2B][off_pos int32 2B]
+      // stream-ordered scratch: [idx int64 B][offsets of view 0 int32 2B][view 1] ...
       const size_t ib = (size_t)B * 8, ob = (size_t)B * 8;
-      AUGCL_CUDA(cudaMallocAsync(&scratch, ib + 3 * ob, st));
+      AUGCL_CUDA(cudaMallocAsync(&scratch, ib + kMaxViews * ob, st));
       uint8_t* sp = static_cast<uint8_t*>(scratch);
       cudaError_t e = cudaSuccess;
       if (host_idx) {
@@ -588,7 +599,7 @@ static int sample_impl(const char* who, augcl_ring* r, int idx_src, const int64_
         p.idx = reinterpret_cast<const int64_t*>(sp);
         p.idx_mode = AUGCL_SRC_DEVICE;
       }
-      for (int t = 0; t < 3 && e == cudaSuccess; ++t)
+      for (int t = 0; t < kMaxViews && e == cudaSuccess; ++t)
         if (p.off_mode[t] == AUGCL_SRC_HOST) {
           e = cudaMemcpyAsync(sp + ib + t * ob, off[t], ob, cudaMemcpyHostToDevice, st);
           p.off[t] = reinterpret_cast<const int32_t*>(sp + ib + t * ob);
@@ -684,9 +695,26 @@ int augcl_ring_sample_curl(augcl_ring* r, int idx_src, const int64_t* idx, int64
                            float* out_next, float* out_pos, float* out_act, float* out_rew, float* out_nd, int off_src,
                            const int32_t* off_obs, const int32_t* off_next, const int32_t* off_pos, int size, int normalize,
                            uint64_t seed, uint64_t subsequence, augcl_stream stream) {
+  const int src[1] = {0};
+  float* const outs[1] = {out_pos};
+  const int32_t* const offs[1] = {off_pos};
   return sample_impl("augcl_ring_sample_curl", r, idx_src, idx, idx_hi, B, out_obs, out_next, out_act, out_rew, out_nd,
                      AUGCL_AUG_CROP, off_src, off_obs, off_next, size, normalize, seed, subsequence, (cudaStream_t)stream,
-                     out_pos, off_pos);
+                     out_pos ? 1 : 0, src, outs, offs);
+}
+
+int augcl_ring_sample_views(augcl_ring* r, int idx_src, const int64_t* idx, int64_t idx_hi, int B, int n_views,
+                            const int* view_src, float* const* outs, const int32_t* const* offs, float* out_act,
+                            float* out_rew, float* out_nd, int aug_mode, int off_src, int pad_or_size, int normalize,
+                            uint64_t seed, uint64_t subsequence, augcl_stream stream) {
+  const char* who = "augcl_ring_sample_views";
+  AUGCL_REQUIRE(n_views >= 1 && n_views <= kMaxViews - 2, "%s: n_views must be in [1, %d]", who, kMaxViews - 2);
+  AUGCL_REQUIRE(view_src && outs, "%s: view_src/outs is NULL", who);
+  AUGCL_REQUIRE(aug_mode == AUGCL_AUG_NONE || aug_mode == AUGCL_AUG_SHIFT || aug_mode == AUGCL_AUG_CROP,
+                "%s: aug_mode must be NONE, SHIFT or CROP", who);
+  // every requested view is an "extra" view (2 ..): its Philox offsets come from subsequence + 3 + v
+  return sample_impl(who, r, idx_src, idx, idx_hi, B, nullptr, nullptr, out_act, out_rew, out_nd, aug_mode, off_src, nullptr,
+                     nullptr, pad_or_size, normalize, seed, subsequence, (cudaStream_t)stream, n_views, view_src, outs, offs);
 }
 
 }  // extern "C"

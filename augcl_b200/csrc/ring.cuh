@@ -32,14 +32,17 @@ struct augcl_ring {
 
 namespace augcl {
 
+constexpr int kMaxViews = 8;
+
 struct SampleParams {
   const uint8_t* store[2];   // v1: obs / next_obs stacks; v2: store[0] = frame pool
   const int32_t* refs;       // v2: [capacity][2][k] pool slots (NULL = v1)
   int k, cpf;
-  // output "views": 0 = obs, 1 = next_obs, 2 = a second, independently cropped copy of obs (sample_curl's `pos`)
-  float* out[3];
-  const int32_t* off[3];
-  int vsrc[3];               // ring tensor a view reads: {0, 1, 0}
+  // output "views": 0 = obs, 1 = next_obs, 2.. = further independently shifted / cropped copies of either tensor
+  // (sample_curl's `pos`; the K + M augmented copies of a DrQ update)
+  float* out[kMaxViews];
+  const int32_t* off[kMaxViews];
+  int vsrc[kMaxViews];       // ring tensor a view reads (0 obs, 1 next_obs)
   const int64_t* idx;
   const float* act;
   const float* rew;
@@ -52,12 +55,12 @@ struct SampleParams {
   int pad;        // SHIFT: pad; NONE/CROP: 0.  source coord = clamp(out coord + off - pad)
   int normalize;
   int nt;         // number of tensors written (1 or 2); slot s -> tensor tmap[s]
-  int tmap[3];
+  int tmap[kMaxViews];
   int stage_bytes;
   int stages;
   // where the draws come from (AUGCL_SRC_*; kSrcInline = by value in the launch's parameter block, kSrcNone = identity)
   int idx_mode;
-  int off_mode[3];
+  int off_mode[kMaxViews];
   uint32_t off_range;      // PHILOX offsets are uniform in [0, off_range)
   uint64_t idx_hi;         // PHILOX indices are uniform in [0, idx_hi)
   uint64_t seed, subseq;   // PHILOX streams: indices = subseq, obs offsets = subseq + 1, next_obs offsets = subseq + 2

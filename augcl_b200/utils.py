@@ -407,6 +407,56 @@ class ReplayBuffer(object):
         return self._sample(idxs, n=n, aug=L.AUG_SHIFT, off_obs=offsets.get("obs"), off_next=offsets.get("next_obs"),
                             pad_or_size=pad, device_indices=device_indices)
 
+    def sample_drq_km(self, n=None, pad=4, *, k=2, m=2, idxs=None, offsets=None, device_indices=False):
+        """A DrQ update's data (src/algorithms/drq.py:67-70) from ONE kernel: k independently shifted copies of obs and m
+        of next_obs.  Returns (obs_list, action, reward, next_obs_list, not_done).
+        offsets: optional {"obs": [k arrays (B,2)], "next_obs": [m arrays (B,2)]}; missing ones are drawn in the kernel."""
+        k, m = int(k), int(m)
+        if k < 0 or m < 0 or not 1 <= k + m <= 6:
+            raise ValueError("sample_drq_km: need 1 <= k + m <= 6")
+        self._flush()
+        nv = k + m
+        sub = augmentations._reserve_subsequences(3 + nv)
+        if device_indices and idxs is None:
+            B = self.batch_size if n is None else int(n)
+            i_src, i_ptr, keep_i = L.SRC_PHILOX, None, None
+            idx_hi = self.capacity if self.full else self.idx
+        else:
+            if idxs is None:
+                idxs = self._get_idxs(n)
+            i_src, i_ptr, B, keep_i = self._idx_arg(idxs)
+            idx_hi = 0
+        offsets = offsets or {}
+        given = list(offsets.get("obs") or [None] * k) + list(offsets.get("next_obs") or [None] * m)
+        if len(given) != nv:
+            raise ValueError(f"sample_drq_km: offsets must hold {k} obs and {m} next_obs arrays")
+        dev = self.device
+        keep = [keep_i]
+        with torch.cuda.device(dev):
+            offs = []
+            for g in given:                       # supplied draws become DEVICE arrays; the rest are PHILOX draws
+                if g is None:
+                    offs.append(None)
+                    continue
+                t = torch.as_tensor(np.asarray(g.cpu() if isinstance(g, torch.Tensor) else g)).to(device=dev, dtype=torch.int32).contiguous()
+                if tuple(t.shape) != (B, 2):
+                    raise ValueError(f"sample_drq_km: offsets must have shape ({B}, 2), got {tuple(t.shape)}")
+                offs.append(t)
+            keep.append(offs)
+            c, h, w = self.obs_shape
+            block = torch.empty((nv, B, c, h, w), dtype=torch.float32, device=dev)
+            views = list(block.unbind(0))
+            act = torch.empty((B,) + self.actions.shape[1:], dtype=torch.float32, device=dev)
+            rew, nd = torch.empty((2, B, 1), dtype=torch.float32, device=dev).unbind(0)
+            src = (C.c_int * nv)(*([0] * k + [1] * m))
+            outs = (C.c_void_p * nv)(*[v.data_ptr() for v in views])
+            offp = (C.c_void_p * nv)(*[None if o is None else o.data_ptr() for o in offs])
+            L.call("augcl_ring_sample_views", self._ring, i_src, i_ptr, idx_hi, B, nv, src, outs, offp, act.data_ptr(),
+                   rew.data_ptr(), nd.data_ptr(), L.AUG_SHIFT, L.SRC_PHILOX, int(pad), 0, augmentations._seed, sub,
+                   _raw_stream(self._dev_index))
+        self._keep = keep
+        return views[:k], act, rew, views[k:], nd
+
     def sample_svea(self, n=None, pad=4, *, idxs=None, offsets=None, device_indices=False):
         """The SVEA / AugCL access pattern (src/algorithms/svea.py:66-70, augcl.py:69-72) as one kernel:
         obs is shifted, next_obs is returned un-augmented.  offsets: optional (B,2) draws for obs."""

@@ -168,6 +168,18 @@ int augcl_ring_sample_curl(augcl_ring* ring, int idx_src, const int64_t* idx, in
                            const int32_t* off_obs, const int32_t* off_next, const int32_t* off_pos, int size,
                            int normalize, uint64_t seed, uint64_t subsequence, augcl_stream stream);
 
+/* One gather, up to 6 independently shifted / cropped views: the K augmented copies of obs and M of next_obs that a
+ * DrQ update builds with K + M calls of random_shift after sample() (src/algorithms/drq.py:67-70; K = drq_k, M = drq_m).
+ *   view_src[v]  0 = obs, 1 = next_obs        outs[v]  device f32 [B, C, Ho, Wo]
+ *   offs         NULL, or offs[v] = int32[B,2] offsets of view v (NULL entry: identity, or a PHILOX draw from
+ *                subsequence + 3 + v when off_src == PHILOX)
+ * aug_mode NONE / SHIFT / CROP; the other arguments as in augcl_ring_sample_ex.  Every u8 plane leaves HBM once; the
+ * later views read it from L2. */
+int augcl_ring_sample_views(augcl_ring* ring, int idx_src, const int64_t* idx, int64_t idx_hi, int B, int n_views,
+                            const int* view_src, float* const* outs, const int32_t* const* offs, float* out_act,
+                            float* out_rew, float* out_nd, int aug_mode, int off_src, int pad_or_size, int normalize,
+                            uint64_t seed, uint64_t subsequence, augcl_stream stream);
+
 /* ------------------------------------------------------------------------------------------
  * Fused per-algorithm sampler: ONE kernel gathers the minibatch and writes every tensor an update needs.
  * Replaces, for one update() of

@@ -320,3 +320,40 @@ def test_sample_curl_is_one_launch_with_three_independent_crops(U, O):
     assert torch.equal(pos2.cpu(), O.random_crop(o_obs, size, mine[:, 0], mine[:, 1]))
     d1 = O.rng_randint(2 * B, 0, S - size, 78, 1).reshape(B, 2)
     assert torch.equal(obs2.cpu(), O.random_crop(o_obs, size, d1[:, 0], d1[:, 1]))
+
+
+@pytest.mark.parametrize("S,B", [(84, 24), (84, 300), (20, 7)])
+def test_sample_drq_km_one_launch(U, O, S, B):
+    """DrQ's K shifted copies of obs and M of next_obs (src/algorithms/drq.py:67-70) from one launch: each view equals
+    random_shift of the gathered tensor with that view's offsets; offsets not supplied come from the view's own Philox
+    subsequence (seed, sub + 3 + view)."""
+    from augcl_b200 import _lib as L, augmentations as A
+    rng = np.random.RandomState(S + B)
+    cap, pad, k = 60, 4 if S > 30 else 2, 3
+    buf = U.ReplayBuffer((3 * k, S, S), (3,), cap, B)
+    ora = O.HostRing((3 * k, S, S), (3,), cap, B)
+    frames = rng.randint(0, 256, (cap + k, 3, S, S)).astype(np.uint8)
+    for t in range(cap):
+        a = rng.randn(3).astype(np.float32)
+        buf.add(U.LazyFrames(list(frames[t:t + k])), a, float(t), U.LazyFrames(list(frames[t + 1:t + 1 + k])), t % 7 == 0)
+        ora.add(O.LazyFrames(frames[t:t + k]), a, float(t), O.LazyFrames(frames[t + 1:t + 1 + k]), t % 7 == 0)
+    idxs = rng.randint(0, cap, size=B)
+    o_obs, o_act, o_rew, o_next, o_nd = ora.sample(idxs)
+    offs = {"obs": [rng.randint(0, 2 * pad + 1, (B, 2)) for _ in range(2)],
+            "next_obs": [rng.randint(0, 2 * pad + 1, (B, 2)) for _ in range(3)]}
+    n0 = L.launch_count()
+    obs_l, act, rew, next_l, nd = buf.sample_drq_km(pad=pad, k=2, m=3, idxs=idxs, offsets=offs)
+    assert L.launch_count() - n0 == 1 and len(obs_l) == 2 and len(next_l) == 3
+    for v, o in zip(obs_l, offs["obs"]):
+        assert torch.equal(v.cpu(), O.random_shift_int(o_obs, o, pad))
+    for v, o in zip(next_l, offs["next_obs"]):
+        assert torch.equal(v.cpu(), O.random_shift_int(o_next, o, pad))
+    assert torch.equal(act.cpu(), o_act) and torch.equal(rew.cpu(), o_rew) and torch.equal(nd.cpu(), o_nd)
+    A.seed(31)
+    obs_l, _, _, next_l, _ = buf.sample_drq_km(pad=pad, k=2, m=2, idxs=idxs)
+    draws = [O.rng_randint(2 * B, 0, 2 * pad + 1, 31, 3 + v).reshape(B, 2) for v in range(4)]
+    assert torch.equal(obs_l[0].cpu(), O.random_shift_int(o_obs, draws[0], pad))
+    assert torch.equal(obs_l[1].cpu(), O.random_shift_int(o_obs, draws[1], pad))
+    assert torch.equal(next_l[0].cpu(), O.random_shift_int(o_next, draws[2], pad))
+    assert torch.equal(next_l[1].cpu(), O.random_shift_int(o_next, draws[3], pad))
+    assert not torch.equal(obs_l[0], obs_l[1])
