@@ -726,3 +726,71 @@ class ReplayBuffer(object):
 
     def ring_bytes(self):
         return int(L.lib().augcl_ring_bytes(self._ring))
+
+
+class GraphSampler(object):
+    """A captured ``sample_drq`` / ``sample_svea`` / ``sample`` step for training loops that want the smallest host cost
+    per update: the host draws (the reference's ``np.random.randint`` indices, src/utils.py:229-232, and the shift offsets)
+    are written into ONE pinned staging block, copied to the device with one async H2D and consumed by a CUDA graph that
+    holds the sample kernel.  Outputs are the graph's own tensors: valid until the next ``sample`` call.
+
+        gs = GraphSampler(buf, kind="drq", pad=4)            # once
+        obs, action, reward, next_obs, not_done = gs.sample(idxs, offsets)   # every update
+    """
+
+    def __init__(self, buf, kind="drq", pad=4, batch=None):
+        if kind not in ("drq", "svea", "plain"):
+            raise ValueError("GraphSampler: kind must be 'drq', 'svea' or 'plain'")
+        self.buf, self.kind, self.pad = buf, kind, int(pad)
+        B = self.B = int(batch or buf.batch_size)
+        dev = buf.device
+        # staging layout (bytes): [idx int64 B][off_obs int32 2B][off_next int32 2B]
+        self._pin = torch.empty(24 * B, dtype=torch.uint8).pin_memory()
+        self._dev = torch.empty(24 * B, dtype=torch.uint8, device=dev)
+        hp = self._pin.numpy()
+        self._h_idx = hp[:8 * B].view(np.int64)
+        self._h_off = hp[8 * B:].view(np.int32).reshape(2, B, 2)
+        self._h_off[:] = self.pad
+        self._h_idx[:] = 0
+        d_idx = self._dev[:8 * B].view(torch.int64)
+        d_off = self._dev[8 * B:].view(torch.int32).view(2, B, 2)
+        self._dev.copy_(self._pin)
+
+        def step():
+            if kind == "drq":
+                return buf.sample_drq(pad=self.pad, idxs=d_idx, offsets={"obs": d_off[0], "next_obs": d_off[1]})
+            if kind == "svea":
+                return buf.sample_svea(pad=self.pad, idxs=d_idx, offsets=d_off[0])
+            return buf.sample(idxs=d_idx)
+
+        buf._flush()
+        cur = torch.cuda.current_stream(dev)
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(cur)
+        with torch.cuda.stream(side):
+            step()                                  # warm-up outside the capture
+        cur.wait_stream(side)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.out = step()
+
+    def sample(self, idxs, offsets=None, validate=True):
+        """idxs: (B,) host integers; offsets: {"obs": (B,2), "next_obs": (B,2)} host integers in [0, 2*pad] (drq), a (B,2)
+        array (svea) or None.  Returns (obs, action, reward, next_obs, not_done)."""
+        buf = self.buf
+        if buf._st_count:
+            buf._flush()
+        self._h_idx[:] = idxs
+        if validate and (self._h_idx.min() < 0 or self._h_idx.max() >= buf.capacity):
+            raise IndexError(f"GraphSampler: index outside [0, {buf.capacity})")
+        if offsets is not None:
+            if self.kind == "drq":
+                self._h_off[0] = offsets["obs"]
+                self._h_off[1] = offsets["next_obs"]
+            elif self.kind == "svea":
+                self._h_off[0] = offsets
+            if validate and (self._h_off.min() < 0 or self._h_off.max() > 2 * self.pad):
+                raise ValueError(f"GraphSampler: offset outside [0, {2 * self.pad}]")
+        self._dev.copy_(self._pin, non_blocking=True)
+        self.graph.replay()
+        return self.out

@@ -7,8 +7,10 @@ A "step" is one pass of the hot path over one minibatch: gather B transitions (o
 9x84x84 u8 each) from the 100k-transition device ring by random index, cast u8->f32 and apply
 random_shift(pad=4) to both (the DrQ K=M=1 pattern; ReplayBuffer.sample_drq) — ONE kernel launch.
 Prints ONE JSON line (rank 0).  `value` = samples/s with everything resident in HBM, timed with
-CUDA events on the launching stream; `e2e` = the same through ReplayBuffer.sample_drq() with HOST
-indices/offsets (pinned H2D inside the timed region) and a D2H read of the step's rewards.
+CUDA events on the launching stream; `e2e` = the same step from HOST indices/offsets through the public
+API (utils.GraphSampler: pinned H2D of the draws + the kernel replayed from a CUDA graph; the plain
+ReplayBuffer.sample_drq() call is reported beside it as `dropin_value`), with a D2H read of the step's
+rewards and a stream synchronize every step.
 Multi-GPU (torchrun): one ring shard + one seed per rank, no data-path collective; elapsed = max
 over ranks.  `--impl reference` times the reference's CPU path for the same step on the host cores.
 """
@@ -291,13 +293,34 @@ def run_ours(args):
         evs[j].record(stream)
     torch.cuda.synchronize(dev)
     el_p = shard.max_over_ranks(time.perf_counter() - t0, device=dev)
-    e2e = {"value": world * Ke * B / el, "unit": UNIT, "h2d_bytes_per_step": B * 4 + 2 * B * 2,
-           "d2h_bytes_per_step": B * 4, "steps": Ke, "ms_per_step": 1e3 * el / Ke,
-           "api": "ReplayBuffer.sample_drq(idxs=host numpy, offsets=host numpy) + D2H of the step's rewards + stream "
-                  "synchronize EVERY step; the host draws travel by value in the kernel launch's parameter block "
-                  "(augcl_ring_sample_ex HOST: int32 index + 2x2 int8 offsets per sample), so H2D is the launch itself",
+    # same step through the captured sampler (utils.GraphSampler): the host draws go through one pinned staging block and
+    # one H2D copy, the kernel is replayed from a CUDA graph; rewards D2H + stream synchronize every step as above
+    gs = U.GraphSampler(buf, kind="drq", pad=PAD, batch=B)
+
+    def graph_step(t):
+        out = gs.sample(n_idx[t], {"obs": n_off[t, 0], "next_obs": n_off[t, 1]})
+        h_rew.copy_(out[2], non_blocking=True)
+        stream.synchronize()
+    for t in range(3):
+        graph_step(t)
+    barrier()
+    t0 = time.perf_counter()
+    for t in range(3, Ke + 3):
+        graph_step(t)
+    torch.cuda.synchronize(dev)
+    el_g = shard.max_over_ranks(time.perf_counter() - t0, device=dev)
+    e2e = {"value": world * Ke * B / el_g, "unit": UNIT, "h2d_bytes_per_step": 24 * B, "d2h_bytes_per_step": B * 4,
+           "steps": Ke, "ms_per_step": 1e3 * el_g / Ke,
+           "api": "utils.GraphSampler(buf, kind='drq').sample(host idxs, host offsets) + D2H of the step's rewards + stream "
+                  "synchronize EVERY step: the host draws (int64 index + 2x2 int32 offsets per sample) are written into one "
+                  "pinned staging block, copied H2D (cudaMemcpyAsync, 24 B/sample) and consumed by the sample kernel replayed "
+                  "from a CUDA graph",
+           "dropin_value": world * Ke * B / el, "dropin_ms_per_step": 1e3 * el / Ke,
+           "dropin_note": "the reference-named call, ReplayBuffer.sample_drq(idxs=host numpy, offsets=host numpy), same copies "
+                          "and per-step synchronize; the host draws travel by value in the kernel's parameter block "
+                          "(augcl_ring_sample_ex HOST), outputs are fresh tensors every call",
            "pipelined_value": world * Ke * B / el_p, "pipelined_ms_per_step": 1e3 * el_p / Ke,
-           "pipelined_note": "same call and copies, each step's rewards read one step late (2 pinned slots + events)"}
+           "pipelined_note": "the drop-in call with each step's rewards read one step late (2 pinned slots + events)"}
     return dict(buf=buf, dev=dev, world=world, rank=rank, ms=ms, value=value, launches=launches, clocks=clocks, e2e=e2e,
                 step_raw=fn, K=K, W=W, B=B)
 

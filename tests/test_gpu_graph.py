@@ -54,3 +54,38 @@ def test_captured_samplers_replay_with_new_draws():
             assert (aug_g[1] - aug_e[1]).abs().max().item() / 255.0 <= TOL_NORM
     finally:
         A.set_background_bank(None)
+
+
+def test_graph_sampler_equals_eager_calls():
+    from augcl_b200 import utils as U
+    cap, B, S, pad = 3000, 128, 84, 4
+    buf = U.ReplayBuffer((9, S, S), (6,), cap, B)
+    buf.fill_synthetic(seed=4)
+    rng = np.random.RandomState(0)
+    for kind in ("drq", "svea", "plain"):
+        gs = U.GraphSampler(buf, kind=kind, pad=pad)
+        for _ in range(3):
+            idxs = rng.randint(0, cap, size=B)
+            o1, o2 = rng.randint(0, 2 * pad + 1, (B, 2)), rng.randint(0, 2 * pad + 1, (B, 2))
+            if kind == "drq":
+                got = gs.sample(idxs, {"obs": o1, "next_obs": o2})
+                want = buf.sample_drq(pad=pad, idxs=idxs, offsets={"obs": o1, "next_obs": o2})
+            elif kind == "svea":
+                got = gs.sample(idxs, o1)
+                want = buf.sample_svea(pad=pad, idxs=idxs, offsets=o1)
+            else:
+                got = gs.sample(idxs)
+                want = buf.sample(idxs=idxs)
+            torch.cuda.synchronize()
+            for a, b in zip(got, want):
+                assert torch.equal(a, b), kind
+        with pytest.raises(IndexError):
+            gs.sample(np.full(B, cap))
+    # transitions added after the capture are visible to the next replay (the ring is read at replay time)
+    gs = U.GraphSampler(buf, kind="plain")
+    frame = np.full((9, S, S), 7, dtype=np.uint8)
+    slot = buf.idx
+    buf.add(frame, np.zeros(6, np.float32), 1.5, frame, False)
+    got = gs.sample(np.full(B, slot))
+    torch.cuda.synchronize()
+    assert float(got[0].min()) == 7.0 and float(got[0].max()) == 7.0 and float(got[2][0]) == 1.5
