@@ -8,6 +8,8 @@
 // dense contraction, so no tensor cores.  This translation unit is compiled with --fmad=false: every
 // multiply/add below is rounded separately, exactly like the reference's chain of torch elementwise
 // ops, and FMAs appear only where written explicitly (the conv accumulation).
+#include <climits>
+#include <mutex>
 #include "common.cuh"
 #include "pixel.cuh"
 
@@ -115,14 +117,34 @@ __global__ void __launch_bounds__(256) shift_bilinear_vec_kernel(const float* __
                                                                  const float* __restrict__ base) {
   const int Hp = h + 2 * pad, Wp = w + 2 * pad;
   const float sc = (float)(2.0 / (double)Hp);
-  const int nq = w >> 2, nvec = h * nq;
+  const int nq = w >> 2;
+  // fixed mapping: thread = (row slot, 4-pixel column group); the column-side terms (ix, floor, weights, the two clamped
+  // source columns and their validity, x 4 columns) depend only on the sample -> computed once per plane, not per pixel
+  const int rpr = 256 / nq;                      // rows per round (12 at w = 84); requires nq <= 256
+  const int r0 = threadIdx.x / nq, q4 = threadIdx.x - r0 * nq;
+  const bool active = r0 < rpr;
+  float bx[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) bx[j] = active ? __ldg(base + 4 * q4 + j) : 0.0f;
   for (int plane = blockIdx.x; plane < planes; plane += gridDim.x) {
     const int i = plane / c;
     const float sy = (float)offsets[2 * i] * sc, sx = (float)offsets[2 * i + 1] * sc;
     const float* src = in + (int64_t)plane * h * w;
     float4* dst = reinterpret_cast<float4*>(out + (int64_t)plane * h * w);
-    for (int v = threadIdx.x; v < nvec; v += 256) {
-      const int r = v / nq, q4 = v - r * nq;
+    float tx[4], ex[4];
+    int c0[4], c1[4];
+    bool vx0[4], vx1[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float gx = bx[j] + sx;
+      const float ix = ((gx + 1.0f) * (float)Wp - 1.0f) / 2.0f;
+      const float fx = floorf(ix);
+      const int x0 = (int)fx, x1 = x0 + 1;
+      tx[j] = ix - fx; ex[j] = 1.0f - tx[j];
+      vx0[j] = x0 >= 0 && x0 < Wp; vx1[j] = x1 >= 0 && x1 < Wp;
+      c0[j] = clampi(x0 - pad, 0, w - 1); c1[j] = clampi(x1 - pad, 0, w - 1);
+    }
+    for (int r = active ? r0 : h; r < h; r += rpr) {
       const float gy = __ldg(base + r) + sy;
       const float iy = ((gy + 1.0f) * (float)Hp - 1.0f) / 2.0f;
       const float fy = floorf(iy);
@@ -134,19 +156,105 @@ __global__ void __launch_bounds__(256) shift_bilinear_vec_kernel(const float* __
       float o[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        const float gx = __ldg(base + 4 * q4 + j) + sx;
-        const float ix = ((gx + 1.0f) * (float)Wp - 1.0f) / 2.0f;
-        const float fx = floorf(ix);
-        const int x0 = (int)fx, x1 = x0 + 1;
-        const float tx = ix - fx, ex = 1.0f - tx;
-        const bool vx0 = x0 >= 0 && x0 < Wp, vx1 = x1 >= 0 && x1 < Wp;
-        const int c0 = clampi(x0 - pad, 0, w - 1), c1 = clampi(x1 - pad, 0, w - 1);
-        const float t00 = (vy0 && vx0) ? __ldg(row0 + c0) : 0.0f, t01 = (vy0 && vx1) ? __ldg(row0 + c1) : 0.0f;
-        const float t10 = (vy1 && vx0) ? __ldg(row1 + c0) : 0.0f, t11 = (vy1 && vx1) ? __ldg(row1 + c1) : 0.0f;
-        const float nw = t00 * (ex * ey), ne = t01 * (tx * ey), sw = t10 * (ex * ty), se = t11 * (tx * ty);
+        const float t00 = (vy0 && vx0[j]) ? __ldg(row0 + c0[j]) : 0.0f, t01 = (vy0 && vx1[j]) ? __ldg(row0 + c1[j]) : 0.0f;
+        const float t10 = (vy1 && vx0[j]) ? __ldg(row1 + c0[j]) : 0.0f, t11 = (vy1 && vx1[j]) ? __ldg(row1 + c1[j]) : 0.0f;
+        const float nw = t00 * (ex[j] * ey), ne = t01 * (tx[j] * ey), sw = t10 * (ex[j] * ty), se = t11 * (tx[j] * ty);
         o[j] = ((nw + ne) + sw) + se;
       }
-      dst[v] = make_float4(o[0], o[1], o[2], o[3]);
+      dst[r * nq + q4] = make_float4(o[0], o[1], o[2], o[3]);
+    }
+  }
+}
+
+// Staged variant for planes that fit shared memory (h, w <= 256 and h*w*4 + h*16 <= 96 KB: 84x84 takes 29 KB, so 7 CTAs
+// per SM overlap each other's fill and compute phases).  The 4-pixel-per-thread kernel above is issue bound (ncu: 69
+// instructions per pixel, a third of them 64-bit address arithmetic for the 4 taps); here the plane is copied to shared
+// memory with coalesced float4 loads, thread = (row chunk, column) so the 4 taps are conflict-free LDS at 32-bit
+// addresses, the column terms are computed once per plane per thread and the row terms once per plane per row.
+constexpr int kBilMaxH = 256;
+__device__ __forceinline__ float lds_f32(uint32_t addr) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+  return v;
+}
+constexpr int kBilSmemMax = 96 * 1024;
+__global__ void __launch_bounds__(256) shift_bilinear_smem_kernel(const float* __restrict__ in, float* __restrict__ out,
+                                                                  int planes, int c, int h, int w, int pad,
+                                                                  const int32_t* __restrict__ offsets,
+                                                                  const float* __restrict__ base, int vec) {
+  extern __shared__ __align__(16) unsigned char bsm[];
+  // per output row: {byte offset of the upper source row in the tile, of the lower one, ty, flags}; flags bit 0 / 1 = the
+  // upper / lower row lies outside the padded image (those taps read zero, as grid_sample's zeros padding does).  The
+  // table is padded to a multiple of 4 rows (copies of the last row) so a 4-row trip never indexes past it.
+  const int h4 = (h + 3) & ~3;
+  int4* s_row = reinterpret_cast<int4*>(bsm);
+  float* tile = reinterpret_cast<float*>(bsm + (size_t)h4 * 16);
+  const uint32_t tile_s = smem_u32(tile);
+  const int Hp = h + 2 * pad, Wp = w + 2 * pad;
+  const float sc = (float)(2.0 / (double)Hp);
+  const int nchunk = 256 / w, rows_per = (((h + nchunk - 1) / nchunk) + 3) & ~3;
+  const int rc = threadIdx.x / w, x = threadIdx.x - rc * w;
+  const bool active = rc < nchunk && rc * rows_per < h;
+  const float bx = active ? __ldg(base + x) : 0.0f;
+  const int n_el = h * w;
+  for (int plane = blockIdx.x; plane < planes; plane += gridDim.x) {
+    const int i = plane / c;
+    const float sy = (float)offsets[2 * i] * sc, sx = (float)offsets[2 * i + 1] * sc;
+    const float* src = in + (int64_t)plane * n_el;
+    __syncthreads();                               // the previous plane's taps are done
+    if (vec) {
+      const float4* s4 = reinterpret_cast<const float4*>(src);
+      float4* t4 = reinterpret_cast<float4*>(tile);
+      for (int e = threadIdx.x; e < (n_el >> 2); e += 256) t4[e] = __ldg(s4 + e);
+    } else {
+      for (int e = threadIdx.x; e < n_el; e += 256) tile[e] = __ldg(src + e);
+    }
+    for (int r = threadIdx.x; r < h4; r += 256) {
+      const float gy = __ldg(base + min(r, h - 1)) + sy;
+      const float iy = ((gy + 1.0f) * (float)Hp - 1.0f) / 2.0f;
+      const float fy = floorf(iy);
+      const int y0 = (int)fy, y1 = y0 + 1;
+      const int fl = ((y0 >= 0 && y0 < Hp) ? 0 : 1) | ((y1 >= 0 && y1 < Hp) ? 0 : 2);
+      s_row[r] = make_int4(clampi(y0 - pad, 0, h - 1) * w * 4, clampi(y1 - pad, 0, h - 1) * w * 4,
+                           __float_as_int(iy - fy), fl);
+    }
+    __syncthreads();
+    if (!active) continue;
+    const float gx = bx + sx;
+    const float ix = ((gx + 1.0f) * (float)Wp - 1.0f) / 2.0f;
+    const float fx = floorf(ix);
+    const int x0 = (int)fx, x1 = x0 + 1;
+    const float tx = ix - fx, ex = 1.0f - tx;
+    const bool vx0 = x0 >= 0 && x0 < Wp, vx1 = x1 >= 0 && x1 < Wp;
+    const int xfl = (vx0 && vx1) ? 0 : 4;
+    const uint32_t a0 = tile_s + clampi(x0 - pad, 0, w - 1) * 4, a1 = tile_s + clampi(x1 - pad, 0, w - 1) * 4;
+    const int r_beg = rc * rows_per, r_end = min(h, r_beg + rows_per);
+    float* o = out + (int64_t)plane * n_el + (int64_t)r_beg * w + x;
+    for (int rb = r_beg; rb < r_end; rb += 4, o += 4 * w) {
+      float t[4][4];
+      int4 q[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        q[u] = s_row[rb + u];
+        t[u][0] = lds_f32(a0 + q[u].x); t[u][1] = lds_f32(a1 + q[u].x);
+        t[u][2] = lds_f32(a0 + q[u].y); t[u][3] = lds_f32(a1 + q[u].y);
+      }
+      // a tap outside the padded image (only the first / last row or column, when a rounding puts floor() one off)
+      if ((q[0].w | q[1].w | q[2].w | q[3].w | xfl) != 0) {
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          if ((q[u].w & 1) || !vx0) t[u][0] = 0.0f;
+          if ((q[u].w & 1) || !vx1) t[u][1] = 0.0f;
+          if ((q[u].w & 2) || !vx0) t[u][2] = 0.0f;
+          if ((q[u].w & 2) || !vx1) t[u][3] = 0.0f;
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const float ty = __int_as_float(q[u].z), ey = 1.0f - ty;
+        const float nw = t[u][0] * (ex * ey), ne = t[u][1] * (tx * ey), sw = t[u][2] * (ex * ty), se = t[u][3] * (tx * ty);
+        if (rb + u < r_end) o[u * w] = ((nw + ne) + sw) + se;
+      }
     }
   }
 }
@@ -569,7 +677,20 @@ int augcl_random_shift(const float* in, float* out, int n, int c, int h, int w, 
   AUGCL_REQUIRE(mode == AUGCL_SHIFT_BILINEAR, "augcl_random_shift: unknown mode %d", mode);
   AUGCL_REQUIRE(base, "augcl_random_shift: BILINEAR needs the base grid");
   if (h != w) AUGCL_FAIL(AUGCL_ERR_UNSUPPORTED, "augcl_random_shift: BILINEAR (DrQ-v2 grid) requires h == w");
-  if (g_staging.load() == 0 && (w & 3) == 0 && aligned(out, 16)) {
+  const size_t bsmem = (size_t)((h + 3) & ~3) * 16 + (size_t)h * w * 4;
+  if (g_staging.load() == 0 && w <= 256 && h <= kBilMaxH && bsmem <= (size_t)kBilSmemMax) {
+    static std::once_flag once;
+    std::call_once(once, [] {
+      cudaFuncSetAttribute(shift_bilinear_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBilSmemMax);
+    });
+    const int planes = n * c;
+    const int vec = ((h * w) & 3) == 0 && aligned(in, 16);
+    shift_bilinear_smem_kernel<<<planes < kNumSMs * 8 ? planes : kNumSMs * 8, 256, bsmem, st>>>(
+        in, out, planes, c, h, w, pad, offsets, base, vec);
+    AUGCL_LAUNCHED();
+    return AUGCL_OK;
+  }
+  if (g_staging.load() == 0 && (w & 3) == 0 && w <= 1024 && aligned(out, 16)) {
     const int planes = n * c;
     shift_bilinear_vec_kernel<<<planes < kNumSMs * 8 ? planes : kNumSMs * 8, 256, 0, st>>>(in, out, planes, c, h, w, pad,
                                                                                         offsets, base);

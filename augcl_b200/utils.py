@@ -750,6 +750,7 @@ class GraphSampler(object):
         hp = self._pin.numpy()
         self._h_idx = hp[:8 * B].view(np.int64)
         self._h_off = hp[8 * B:].view(np.int32).reshape(2, B, 2)
+        self._h_idx_u, self._h_off_u = self._h_idx.view(np.uint64), self._h_off.view(np.uint32)
         self._h_off[:] = self.pad
         self._h_idx[:] = 0
         d_idx = self._dev[:8 * B].view(torch.int64)
@@ -781,7 +782,7 @@ class GraphSampler(object):
         if buf._st_count:
             buf._flush()
         self._h_idx[:] = idxs
-        if validate and (self._h_idx.min() < 0 or self._h_idx.max() >= buf.capacity):
+        if validate and int(self._h_idx_u.max()) >= buf.capacity:      # unsigned view: one reduction catches negatives too
             raise IndexError(f"GraphSampler: index outside [0, {buf.capacity})")
         if offsets is not None:
             if self.kind == "drq":
@@ -789,7 +790,7 @@ class GraphSampler(object):
                 self._h_off[1] = offsets["next_obs"]
             elif self.kind == "svea":
                 self._h_off[0] = offsets
-            if validate and (self._h_off.min() < 0 or self._h_off.max() > 2 * self.pad):
+            if validate and int(self._h_off_u.max()) > 2 * self.pad:
                 raise ValueError(f"GraphSampler: offset outside [0, {2 * self.pad}]")
         self._dev.copy_(self._pin, non_blocking=True)
         self.graph.replay()

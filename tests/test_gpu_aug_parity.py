@@ -111,6 +111,19 @@ def test_against_oracle(A, O, shape, pad, integer_pixels):
         A.set_background_bank(None)
 
 
+@pytest.mark.parametrize("S", [64, 85, 150, 252, 300, 258])
+def test_bilinear_shift_kernel_variants(A, O, S):
+    """Planes up to 96 KB take the shared-memory staged kernel (85: scalar fill, ragged row chunks), wider multiples of 4
+    the 4-pixel one, anything else the generic one.  The pixel coordinate's ulp grows with S, and with it the weight a
+    floor() flip moves between neighbouring taps: the tolerance scales accordingly above the 84-pixel case."""
+    g = torch.Generator().manual_seed(S)
+    x = torch.rand((3, 4, S, S), generator=g) * 255.0
+    for pad in (4, 11):
+        off = torch.randint(0, 2 * pad + 1, (3, 2), generator=g)
+        assert norm_err(A.random_shift(x.cuda(), pad, offsets=off, mode="bilinear"),
+                        O.random_shift_bilinear(x, off.flip(1).numpy(), pad)) <= TOL_NORM * max(1.0, S / 84)
+
+
 def test_known_answers(A):
     # zero weights -> sigmoid(0)*255 == 127.5 everywhere
     x = torch.rand(2, 6, 10, 12, device="cuda") * 255
