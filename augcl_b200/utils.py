@@ -732,13 +732,15 @@ class GraphSampler(object):
     """A captured ``sample_drq`` / ``sample_svea`` / ``sample`` step for training loops that want the smallest host cost
     per update: the host draws (the reference's ``np.random.randint`` indices, src/utils.py:229-232, and the shift offsets)
     are written into ONE pinned staging block, copied to the device with one async H2D and consumed by a CUDA graph that
-    holds the sample kernel.  Outputs are the graph's own tensors: valid until the next ``sample`` call.
+    holds the H2D copy and the sample kernel (and, with ``host_reward=True``, a D2H copy of the step's rewards into the
+    pinned ``reward_host`` tensor, readable after a stream synchronize): one graph launch per step.  Outputs are the
+    graph's own tensors: valid until the next ``sample`` call.
 
         gs = GraphSampler(buf, kind="drq", pad=4)            # once
         obs, action, reward, next_obs, not_done = gs.sample(idxs, offsets)   # every update
     """
 
-    def __init__(self, buf, kind="drq", pad=4, batch=None):
+    def __init__(self, buf, kind="drq", pad=4, batch=None, host_reward=False):
         if kind not in ("drq", "svea", "plain"):
             raise ValueError("GraphSampler: kind must be 'drq', 'svea' or 'plain'")
         self.buf, self.kind, self.pad = buf, kind, int(pad)
@@ -771,9 +773,14 @@ class GraphSampler(object):
         with torch.cuda.stream(side):
             step()                                  # warm-up outside the capture
         cur.wait_stream(side)
+        self.reward_host = torch.empty((B, 1), dtype=torch.float32).pin_memory() if host_reward else None
         self.graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.graph):
+            self._dev.copy_(self._pin, non_blocking=True)
             self.out = step()
+            if host_reward:
+                self.reward_host.copy_(self.out[2], non_blocking=True)
+        self._done = torch.cuda.Event()              # the previous replay has read the staging block
 
     def sample(self, idxs, offsets=None, validate=True):
         """idxs: (B,) host integers; offsets: {"obs": (B,2), "next_obs": (B,2)} host integers in [0, 2*pad] (drq), a (B,2)
@@ -781,6 +788,7 @@ class GraphSampler(object):
         buf = self.buf
         if buf._st_count:
             buf._flush()
+        self._done.synchronize()
         self._h_idx[:] = idxs
         if validate and int(self._h_idx_u.max()) >= buf.capacity:      # unsigned view: one reduction catches negatives too
             raise IndexError(f"GraphSampler: index outside [0, {buf.capacity})")
@@ -792,6 +800,6 @@ class GraphSampler(object):
                 self._h_off[0] = offsets
             if validate and int(self._h_off_u.max()) > 2 * self.pad:
                 raise ValueError(f"GraphSampler: offset outside [0, {2 * self.pad}]")
-        self._dev.copy_(self._pin, non_blocking=True)
         self.graph.replay()
+        self._done.record()
         return self.out

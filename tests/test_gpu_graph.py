@@ -63,7 +63,7 @@ def test_graph_sampler_equals_eager_calls():
     buf.fill_synthetic(seed=4)
     rng = np.random.RandomState(0)
     for kind in ("drq", "svea", "plain"):
-        gs = U.GraphSampler(buf, kind=kind, pad=pad)
+        gs = U.GraphSampler(buf, kind=kind, pad=pad, host_reward=(kind == "drq"))
         for _ in range(3):
             idxs = rng.randint(0, cap, size=B)
             o1, o2 = rng.randint(0, 2 * pad + 1, (B, 2)), rng.randint(0, 2 * pad + 1, (B, 2))
@@ -79,6 +79,8 @@ def test_graph_sampler_equals_eager_calls():
             torch.cuda.synchronize()
             for a, b in zip(got, want):
                 assert torch.equal(a, b), kind
+            if kind == "drq":       # the captured D2H: the step's rewards are in pinned host memory after the sync
+                assert torch.equal(gs.reward_host, want[2].cpu())
         with pytest.raises(IndexError):
             gs.sample(np.full(B, cap))
     # transitions added after the capture are visible to the next replay (the ring is read at replay time)
