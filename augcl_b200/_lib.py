@@ -65,6 +65,8 @@ SIGNATURES = {
     "augcl_random_overlay": (_i, [_p, _p, _i, _i, _i, _i, _p, _i, _i64, _p, _f, _p]),
     "augcl_splice": (_i, [_p, _p, _i, _i, _i, _i, _p, _i, _i64, _p, _f, _f, _f, _i, _p]),
     "augcl_hsv_mask": (_i, [_p, _p, _i, _i, _i, _f, _f, _f, _p]),
+    "augcl_color_jitter": (_i, [_p, _i, _i, _i, _p, _i, C.POINTER(C.c_int32), C.c_double, C.c_double, C.c_double,
+                                C.c_double, _i, _p]),
     "augcl_random_grayscale": (_i, [_p, _p, _i, _i, _i, _i, _p, _p]),
     "augcl_random_flip": (_i, [_p, _p, _i, _i, _i, _i, _p, _p]),
     "augcl_random_rotation": (_i, [_p, _p, _i, _i, _i, _i, _p, _p]),

@@ -369,21 +369,34 @@ def random_cutout_color(imgs, min_cut=10, max_cut=30, *, w1=None, h1=None, color
     return out
 
 
-def color_jitter(imgs, p=1):
+def color_jitter(imgs, p=1, *, sampled_idxs=None, params=None):
     """src/augmentations.py:225-237: torchvision ``ColorJitter(0, (0,2), (0,3), (-0.5,0.5))`` on a random subset of
-    the frames, IN PLACE like the reference.  Not a hand-written kernel: no reference algorithm or launch script
-    uses this entry (grep of scripts/, COMMANDS.md) and on 0..255 inputs torchvision clamps the result to [0,1];
-    it runs the reference's own torchvision op sequence on the device so ``--data_aug`` chains keep working."""
-    import torchvision.transforms as TF
+    the frames, IN PLACE like the reference (one kernel: augcl_color_jitter, the torchvision op sequence restated).
+    The draws are the reference's: ``np.random.randint(0, b, p*b*(c/3))`` frame indices (its quirk: only the first b of
+    the b*c/3 frames are candidates) and ``ColorJitter.get_params`` (torch CPU RNG: randperm(4), then the contrast,
+    saturation and hue factors).  ``sampled_idxs`` / ``params=(fn_idx, brightness, contrast, saturation, hue)``
+    supply them explicitly; a ``None`` factor turns its op off, as in torchvision."""
     if not (isinstance(imgs, torch.Tensor) and imgs.is_cuda):
         raise AssertionError("color_jitter: input must be a CUDA tensor (augcl_b200 has no CPU path)")
+    if imgs.dtype != torch.float32 or not imgs.is_contiguous():
+        raise ValueError("color_jitter: expected a contiguous float32 tensor (the op is in place)")
     b, c, h, w = imgs.shape
     num_samples = int(p * b * int(c / 3))
-    sampled_idxs = torch.from_numpy(np.random.randint(0, b, num_samples))
-    flat = imgs.view(-1, 3, h, w)
-    model = TF.ColorJitter(0, (0, 2), (0, 3), (-0.5, 0.5))
-    flat[sampled_idxs] = model(flat[sampled_idxs])
-    return flat.view(b, c, h, w)
+    if sampled_idxs is None:
+        sampled_idxs = np.random.randint(0, b, num_samples)
+    if params is None:
+        import torchvision.transforms as TF
+        params = TF.ColorJitter.get_params(None, [0.0, 2.0], [0.0, 3.0], [-0.5, 0.5])
+    fn_idx, bf, cf, sf, hf = params
+    sel_np = np.unique(np.asarray(sampled_idxs, dtype=np.int64))
+    if sel_np.size and (sel_np[0] < 0 or sel_np[-1] >= b * (c // 3)):
+        raise IndexError("color_jitter: frame index out of range")
+    sel = torch.from_numpy(sel_np.astype(np.int32)).to(imgs.device)
+    order = (C.c_int32 * 4)(*[int(v) for v in fn_idx])
+    enabled = sum(1 << i for i, f in enumerate((bf, cf, sf, hf)) if f is not None)
+    L.call("augcl_color_jitter", imgs.data_ptr(), b * (c // 3), h, w, sel.data_ptr(), int(sel_np.size), order,
+           float(bf or 0.0), float(cf or 0.0), float(sf or 0.0), float(hf or 0.0), enabled, _stream(imgs))
+    return imgs.view(-1, 3, h, w).view(b, c, h, w)
 
 
 # same 12 keys as src/augmentations.py:436-449

@@ -1,6 +1,6 @@
 // The remaining aug_to_func entries of /root/reference/src/augmentations.py as sm_100a kernels:
 //   random_grayscale :111-136 (+grayscale :88-108)   random_flip :139-168   random_rotation :171-213
-//   random_cutout_color :327-350
+//   random_cutout_color :327-350   color_jitter :225-237 (torchvision ColorJitter restated)
 // Same class as the hot five: read S32, write S32 per sample, pure permutation / elementwise work, HBM-bound.
 // The per-sample decisions (apply mask, quarter turns, box, colours) are inputs, like every other draw.
 // These functions came from RAD, where images are in [0,1]; the reference applies them to its 0..255 tensors
@@ -97,6 +97,92 @@ __global__ void __launch_bounds__(256) hsv_mask_kernel(const float* __restrict__
   }
 }
 
+
+// color_jitter (src/augmentations.py:225-237): torchvision ColorJitter(0, (0,2), (0,3), (-0.5,0.5)) on the selected RGB
+// frames, in place.  One CTA per selected frame: the frame (3*h*w floats, 85 KB at 84x84) sits in shared memory while the
+// up-to-four adjustments run in the drawn order (torchvision/transforms/_functional_tensor.py: _blend, adjust_contrast,
+// adjust_saturation, adjust_hue with _rgb2hsv/_hsv2rgb, rgb_to_grayscale), each restated op for op; contrast needs the
+// frame's mean luminance, a block reduction (the only place the summation order differs from torch's).
+struct JitterParams {
+  int order[4];        // torchvision's fn_idx: 0 brightness, 1 contrast, 2 saturation, 3 hue
+  float ratio[3];      // (float)factor for ops 0..2
+  float omr[3];        // (float)(1.0 - factor), formed in double like Python does
+  float hue;
+  int enabled;         // bit i = op i has a factor
+};
+
+__device__ __forceinline__ float lum(float r, float g, float b) { return (0.2989f * r + 0.587f * g) + 0.114f * b; }
+__device__ __forceinline__ float clamp01(float v) { return fminf(fmaxf(v, 0.0f), 1.0f); }
+
+__device__ __forceinline__ void hue_px(float& r, float& g, float& b, float hf) {
+  const float maxc = fmaxf(fmaxf(r, g), b), minc = fminf(fminf(r, g), b);
+  const bool eqc = maxc == minc;
+  const float cr = maxc - minc;
+  const float s = __fdiv_rn(cr, eqc ? 1.0f : maxc);
+  const float d = eqc ? 1.0f : cr;
+  const float rc = __fdiv_rn(maxc - r, d), gc = __fdiv_rn(maxc - g, d), bc = __fdiv_rn(maxc - b, d);
+  const float hr = (maxc == r) ? (bc - gc) : 0.0f;
+  const float hg = (maxc == g && maxc != r) ? ((2.0f + rc) - bc) : 0.0f;
+  const float hb = (maxc != g && maxc != r) ? ((4.0f + gc) - rc) : 0.0f;
+  float h = (hr + hg) + hb;
+  h = fmodf(__fdiv_rn(h, 6.0f) + 1.0f, 1.0f);
+  // (h + hue_factor) % 1.0: torch.remainder = fmod, moved into [0, 1) when negative
+  float m = fmodf(h + hf, 1.0f);
+  if (m != 0.0f && m < 0.0f) m += 1.0f;
+  const float h6 = m * 6.0f;
+  const float fl = floorf(h6);
+  const float f = h6 - fl;
+  const int i = ((int)fl) % 6;
+  const float v = maxc;
+  const float pp = clamp01(v * (1.0f - s));
+  const float q = clamp01(v * (1.0f - s * f));
+  const float t = clamp01(v * (1.0f - s * (1.0f - f)));
+  r = i == 0 ? v : i == 1 ? q : i == 2 ? pp : i == 3 ? pp : i == 4 ? t : v;
+  g = i == 0 ? t : i == 1 ? v : i == 2 ? v : i == 3 ? q : i == 4 ? pp : pp;
+  b = i == 0 ? pp : i == 1 ? pp : i == 2 ? t : i == 3 ? v : i == 4 ? v : q;
+}
+
+__global__ void __launch_bounds__(256) color_jitter_kernel(float* __restrict__ imgs, const int32_t* __restrict__ sel, int hw,
+                                                           JitterParams P) {
+  extern __shared__ __align__(16) float jsm[];     // [3][hw]
+  __shared__ float s_red[8];
+  float* fr = imgs + (int64_t)sel[blockIdx.x] * 3 * hw;
+  const int tid = threadIdx.x;
+  for (int e = tid; e < 3 * hw; e += 256) jsm[e] = fr[e];
+  __syncthreads();
+  for (int step = 0; step < 4; ++step) {
+    const int op = P.order[step];
+    if (!((P.enabled >> op) & 1)) continue;
+    if (op == 1) {
+      float part = 0.0f;
+      for (int px = tid; px < hw; px += 256) part += lum(jsm[px], jsm[hw + px], jsm[2 * hw + px]);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+      if ((tid & 31) == 0) s_red[tid >> 5] = part;
+      __syncthreads();
+      float tot = 0.0f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) tot += s_red[j];
+      const float other = P.omr[1] * __fdiv_rn(tot, (float)hw);
+      for (int e = tid; e < 3 * hw; e += 256) jsm[e] = clamp01(P.ratio[1] * jsm[e] + other);
+    } else if (op == 0) {
+      for (int e = tid; e < 3 * hw; e += 256) jsm[e] = clamp01(P.ratio[0] * jsm[e] + P.omr[0] * 0.0f);
+    } else {
+      for (int px = tid; px < hw; px += 256) {
+        float r = jsm[px], g = jsm[hw + px], b = jsm[2 * hw + px];
+        if (op == 2) {
+          const float y = P.omr[2] * lum(r, g, b);
+          r = clamp01(P.ratio[2] * r + y); g = clamp01(P.ratio[2] * g + y); b = clamp01(P.ratio[2] * b + y);
+        } else {
+          hue_px(r, g, b, P.hue);
+        }
+        jsm[px] = r; jsm[hw + px] = g; jsm[2 * hw + px] = b;
+      }
+    }
+    __syncthreads();
+  }
+  for (int e = tid; e < 3 * hw; e += 256) fr[e] = jsm[e];
+}
 }  // namespace augcl
 
 using namespace augcl;
@@ -155,6 +241,41 @@ int augcl_random_cutout_color(const float* in, float* out, int n, int c, int h, 
   const int planes = n * c;
   const int grid = planes < kNumSMs * 8 ? planes : kNumSMs * 8;
   cutout_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(in, out, planes, c, h, w, box, colors);
+  AUGCL_LAUNCHED();
+  return AUGCL_OK;
+}
+
+int augcl_color_jitter(float* imgs, int frames, int h, int w, const int32_t* sel, int n_sel, const int32_t* order,
+                       double brightness, double contrast, double saturation, double hue, int enabled,
+                       augcl_stream stream) {
+  AUGCL_REQUIRE(imgs && order, "augcl_color_jitter: imgs/order is NULL");
+  AUGCL_REQUIRE(frames > 0 && h > 0 && w > 0 && n_sel >= 0 && n_sel <= frames, "augcl_color_jitter: bad sizes");
+  AUGCL_REQUIRE((enabled & ~15) == 0, "augcl_color_jitter: enabled has unknown bits");
+  JitterParams P;
+  int seen = 0;
+  for (int i = 0; i < 4; ++i) {
+    AUGCL_REQUIRE(order[i] >= 0 && order[i] < 4, "augcl_color_jitter: order[%d]=%d", i, order[i]);
+    seen |= 1 << order[i];
+    P.order[i] = order[i];
+  }
+  AUGCL_REQUIRE(seen == 15, "augcl_color_jitter: order is not a permutation of 0..3");
+  const double fac[3] = {brightness, contrast, saturation};
+  for (int i = 0; i < 3; ++i) {
+    if ((enabled >> i) & 1) AUGCL_REQUIRE(fac[i] >= 0.0, "augcl_color_jitter: factor %d is negative", i);
+    P.ratio[i] = (float)fac[i];
+    P.omr[i] = (float)(1.0 - fac[i]);
+  }
+  if (enabled & 8) AUGCL_REQUIRE(hue >= -0.5 && hue <= 0.5, "augcl_color_jitter: hue factor %f outside [-0.5, 0.5]", hue);
+  P.hue = (float)hue;
+  P.enabled = enabled;
+  if (n_sel == 0 || enabled == 0) return AUGCL_OK;
+  AUGCL_REQUIRE(sel, "augcl_color_jitter: sel is NULL");
+  const size_t smem = (size_t)3 * h * w * sizeof(float);
+  if (smem > 200 * 1024) AUGCL_FAIL(AUGCL_ERR_UNSUPPORTED, "augcl_color_jitter: %dx%d frame does not fit shared memory", h, w);
+  static std::atomic<bool> configured{false};
+  if (!configured.exchange(true))
+    AUGCL_CUDA(cudaFuncSetAttribute(color_jitter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  color_jitter_kernel<<<n_sel, 256, smem, (cudaStream_t)stream>>>(imgs, sel, h * w, P);
   AUGCL_LAUNCHED();
   return AUGCL_OK;
 }

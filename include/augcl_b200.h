@@ -271,6 +271,15 @@ int augcl_splice(const float* in, float* out, int n, int c, int h, int w, const 
                  int bank_dtype, int64_t bank_len, const int64_t* bank_idx, float hue_thres,
                  float sat_thres, float val_thres, int variant, augcl_stream stream);
 
+/* color_jitter (src/augmentations.py:225-237): torchvision ColorJitter(0, (0,2), (0,3), (-0.5,0.5)).forward on the RGB
+ * frames listed in sel (device int32 [n_sel], distinct frame indices into imgs viewed as [frames][3][h][w]), IN PLACE like
+ * the reference's `flat[sampled_idxs] = model(flat[sampled_idxs])`.  order = fn_idx (host int32[4], a permutation of
+ * 0 brightness, 1 contrast, 2 saturation, 3 hue); enabled bit i = op i has a factor (the reference's model: 0b1110).
+ * The factors are ColorJitter.get_params' draws: the caller makes them, like every other draw. */
+int augcl_color_jitter(float* imgs, int frames, int h, int w, const int32_t* sel, int n_sel, const int32_t* order,
+                       double brightness, double contrast, double saturation, double hue, int enabled,
+                       augcl_stream stream);
+
 /* create_hsv_mask (src/augmentations.py:277-284): rgb f32 [n,3,h,w] ALREADY in [0,1] (the reference passes x/255);
  * mask u8 [n,h,w] = 1 where kornia-HSV hue, saturation and value all exceed their thresholds (strictly). */
 int augcl_hsv_mask(const float* rgb, uint8_t* mask, int n, int h, int w, float hue_thres, float sat_thres, float val_thres,
