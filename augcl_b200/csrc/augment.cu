@@ -383,7 +383,7 @@ __global__ void __launch_bounds__(kConvThreads, 6) random_conv_kernel(const floa
 // copy lands.  Tile row layout: [3]=left pad, [4 .. 4+w) = pixels (16-B aligned for the bulk copy and the
 // LDS.128 of the window), [4+w] = right pad.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kConvThreads, 6) random_conv_tma_kernel(const float* __restrict__ in, float* __restrict__ out,
+__global__ void __launch_bounds__(kConvThreads, 7) random_conv_tma_kernel(const float* __restrict__ in, float* __restrict__ out,
                                                                           int frames, int k, int h, int w,
                                                                           const float* __restrict__ weights, int bands, int RS) {
   extern __shared__ __align__(128) float csm[];
@@ -735,7 +735,7 @@ int augcl_random_conv(const float* in, float* out, int n, int c, int h, int w, c
       if (!configured2.exchange(true))
         AUGCL_CUDA(cudaFuncSetAttribute(random_conv_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
       int per_sm = (int)((228 * 1024) / (smem2 + 1024));
-      per_sm = per_sm < 1 ? 1 : (per_sm > 6 ? 6 : per_sm);
+      per_sm = per_sm < 1 ? 1 : (per_sm > 7 ? 7 : per_sm);
       const int grid = (int)(work < kNumSMs * per_sm ? work : kNumSMs * per_sm);
       random_conv_tma_kernel<<<grid, kConvThreads, smem2, (cudaStream_t)stream>>>(in, out, frames, k, h, w, weights, bands, RS2);
       AUGCL_LAUNCHED();
