@@ -803,3 +803,60 @@ class GraphSampler(object):
         self.graph.replay()
         self._done.record()
         return self.out
+
+
+class FastSampler(object):
+    """The leanest host path for ``sample`` / ``sample_drq`` / ``sample_svea`` at batch <= 256: one ctypes call per step
+    and nothing else.  The host draws (the reference's ``np.random.randint`` indices, src/utils.py:229-232, and the shift
+    offsets) travel BY VALUE in the kernel's parameter block (augcl_ring_sample_ex, HOST source): no H2D copy, no staging
+    block that a later call could overwrite, no event.  Outputs are fixed device tensors, valid until the next ``sample``
+    call; with ``host_reward=True`` the kernel writes the step's rewards straight into the pinned, device-mapped
+    ``reward_host`` tensor (readable after a stream synchronize) instead of a device tensor followed by a D2H copy.
+
+        fs = FastSampler(buf, kind="drq", pad=4)             # once
+        obs, action, reward, next_obs, not_done = fs.sample(idxs, offsets)   # every update
+    """
+
+    def __init__(self, buf, kind="drq", pad=4, batch=None, host_reward=False):
+        if kind not in ("drq", "svea", "plain"):
+            raise ValueError("FastSampler: kind must be 'drq', 'svea' or 'plain'")
+        B = self.B = int(batch or buf.batch_size)
+        if B > 256:
+            raise ValueError("FastSampler: batch > 256 does not fit the kernel's parameter block; use GraphSampler")
+        self.buf, self.kind, self.pad = buf, kind, int(pad)
+        dev = buf.device
+        c, h, w = buf.obs_shape
+        self._idx = np.zeros(B, dtype=np.int64)
+        self._off = np.full((2, B, 2), self.pad, dtype=np.int32)
+        obs, nxt = torch.empty((2, B, c, h, w), dtype=torch.float32, device=dev).unbind(0)
+        act = torch.empty((B,) + buf.actions.shape[1:], dtype=torch.float32, device=dev)
+        nd = torch.empty((B, 1), dtype=torch.float32, device=dev)
+        if host_reward:
+            rew = self.reward_host = torch.zeros((B, 1), dtype=torch.float32).pin_memory()
+        else:
+            rew, self.reward_host = torch.empty((B, 1), dtype=torch.float32, device=dev), None
+        self.out = (obs, act, rew, nxt, nd)
+        aug = {"drq": L.AUG_SHIFT, "svea": L.AUG_SHIFT_OBS, "plain": L.AUG_NONE}[kind]
+        self._args = (buf._ring, L.SRC_HOST, self._idx.ctypes.data, 0, B, obs.data_ptr(), nxt.data_ptr(), act.data_ptr(),
+                      rew.data_ptr(), nd.data_ptr(), aug, L.SRC_HOST, self._off[0].ctypes.data, self._off[1].ctypes.data,
+                      self.pad if kind != "plain" else 0, 0, 0, 0)
+        self._fn = buf._fn_sample
+        self._dev_index = buf._dev_index
+
+    def sample(self, idxs, offsets=None):
+        """idxs: (B,) host integers; offsets: {"obs": (B,2), "next_obs": (B,2)} host integers in [0, 2*pad] (drq), a (B,2)
+        array (svea) or None (keep the previous ones).  The library validates both (AugclError, like the drop-in call)."""
+        buf = self.buf
+        if buf._st_count:
+            buf._flush()
+        self._idx[:] = idxs
+        if offsets is not None:
+            if self.kind == "drq":
+                self._off[0] = offsets["obs"]
+                self._off[1] = offsets["next_obs"]
+            elif self.kind == "svea":
+                self._off[0] = offsets
+        rc = self._fn(*self._args, _raw_stream(self._dev_index))
+        if rc != 0:
+            raise L.AugclError("augcl_ring_sample_ex", rc, L.lib().augcl_last_error().decode(errors="replace"))
+        return self.out

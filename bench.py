@@ -8,9 +8,10 @@ A "step" is one pass of the hot path over one minibatch: gather B transitions (o
 random_shift(pad=4) to both (the DrQ K=M=1 pattern; ReplayBuffer.sample_drq) — ONE kernel launch.
 Prints ONE JSON line (rank 0).  `value` = samples/s with everything resident in HBM, timed with
 CUDA events on the launching stream; `e2e` = the same step from HOST indices/offsets through the public
-API (utils.GraphSampler: pinned H2D of the draws + the kernel replayed from a CUDA graph; the plain
-ReplayBuffer.sample_drq() call is reported beside it as `dropin_value`), with a D2H read of the step's
-rewards and a stream synchronize every step.
+API (utils.FastSampler: the draws travel by value in the kernel's parameter block, the rewards are written
+straight into pinned host memory; utils.GraphSampler and the plain ReplayBuffer.sample_drq() call are reported
+beside it as `graph_value` / `dropin_value`), with a stream synchronize and a host read of the step's rewards
+every step.
 Multi-GPU (torchrun): one ring shard + one seed per rank, no data-path collective; elapsed = max
 over ranks.  `--impl reference` times the reference's CPU path for the same step on the host cores.
 """
@@ -297,12 +298,13 @@ def run_ours(args):
     # one H2D copy, the kernel is replayed from a CUDA graph; rewards D2H + stream synchronize every step as above
     gs = U.GraphSampler(buf, kind="drq", pad=PAD, batch=B, host_reward=True)
     sink = 0.0
+    g_rew = gs.reward_host.numpy()
 
     def graph_step(t):
         nonlocal sink
         gs.sample(n_idx[t], {"obs": n_off[t, 0], "next_obs": n_off[t, 1]})
         stream.synchronize()
-        sink += float(gs.reward_host[0, 0])          # the step's rewards are on the host here
+        sink += float(g_rew[0, 0])                   # the step's rewards are on the host here
     for t in range(3):
         graph_step(t)
     barrier()
@@ -311,12 +313,34 @@ def run_ours(args):
         graph_step(t)
     torch.cuda.synchronize(dev)
     el_g = shard.max_over_ranks(time.perf_counter() - t0, device=dev)
-    e2e = {"value": world * Ke * B / el_g, "unit": UNIT, "h2d_bytes_per_step": 24 * B, "d2h_bytes_per_step": B * 4,
-           "steps": Ke, "ms_per_step": 1e3 * el_g / Ke,
-           "api": "utils.GraphSampler(buf, kind='drq').sample(host idxs, host offsets) + D2H of the step's rewards + stream "
-                  "synchronize EVERY step: the host draws (int64 index + 2x2 int32 offsets per sample) are written into one "
-                  "pinned staging block; ONE CUDA graph launch per step holds the H2D copy (24 B/sample), the sample kernel and "
-                  "the D2H copy of the rewards into pinned host memory",
+    # the leanest host path (utils.FastSampler): the draws travel by value in the kernel's parameter block, the kernel writes
+    # the rewards straight into pinned, device-mapped host memory: one ctypes call + one stream synchronize per step
+    fs = U.FastSampler(buf, kind="drq", pad=PAD, batch=B, host_reward=True)
+    f_rew = fs.reward_host.numpy()
+
+    def fast_step(t):
+        nonlocal sink
+        fs.sample(n_idx[t], {"obs": n_off[t, 0], "next_obs": n_off[t, 1]})
+        stream.synchronize()
+        sink += float(f_rew[0, 0])                   # the step's rewards are on the host here
+    for t in range(3):
+        fast_step(t)
+    barrier()
+    t0 = time.perf_counter()
+    for t in range(3, Ke + 3):
+        fast_step(t)
+    torch.cuda.synchronize(dev)
+    el_f = shard.max_over_ranks(time.perf_counter() - t0, device=dev)
+    e2e = {"value": world * Ke * B / el_f, "unit": UNIT, "h2d_bytes_per_step": 24 * B, "d2h_bytes_per_step": B * 4,
+           "steps": Ke, "ms_per_step": 1e3 * el_f / Ke,
+           "api": "utils.FastSampler(buf, kind='drq', host_reward=True).sample(host idxs, host offsets) + stream synchronize + "
+                  "a host read of the step's rewards EVERY step: the host draws (int64 index + 2x2 int32 offsets per sample, "
+                  "24 B/sample) travel host->device by value in the sample kernel's parameter block (augcl_ring_sample_ex, "
+                  "HOST source: no separate copy), and the kernel writes the step's rewards (4 B/sample) device->host "
+                  "straight into pinned, device-mapped memory",
+           "graph_value": world * Ke * B / el_g, "graph_ms_per_step": 1e3 * el_g / Ke,
+           "graph_note": "utils.GraphSampler: draws through one pinned staging block; ONE CUDA graph launch per step holds the "
+                         "H2D copy (24 B/sample), the sample kernel and the D2H copy of the rewards into pinned host memory",
            "dropin_value": world * Ke * B / el, "dropin_ms_per_step": 1e3 * el / Ke,
            "dropin_note": "the reference-named call, ReplayBuffer.sample_drq(idxs=host numpy, offsets=host numpy), same copies "
                           "and per-step synchronize; the host draws travel by value in the kernel's parameter block "

@@ -91,3 +91,47 @@ def test_graph_sampler_equals_eager_calls():
     got = gs.sample(np.full(B, slot))
     torch.cuda.synchronize()
     assert float(got[0].min()) == 7.0 and float(got[0].max()) == 7.0 and float(got[2][0]) == 1.5
+
+
+def test_fast_sampler_equals_eager_calls():
+    """utils.FastSampler: host draws by value in the launch, fixed outputs, rewards written straight to pinned host
+    memory: same results as the drop-in calls, draws validated by the library, later adds visible."""
+    from augcl_b200 import utils as U
+    from augcl_b200._lib import AugclError
+    S, cap, B, pad = 84, 300, 32, 4
+    buf = U.ReplayBuffer((9, S, S), (6,), cap, B)
+    buf.fill_synthetic(seed=3)
+    rng = np.random.RandomState(1)
+    for kind in ("drq", "svea", "plain"):
+        fs = U.FastSampler(buf, kind=kind, pad=pad, host_reward=(kind != "svea"))
+        for _ in range(3):
+            idxs = rng.randint(0, cap, size=B)
+            o1, o2 = rng.randint(0, 2 * pad + 1, (B, 2)), rng.randint(0, 2 * pad + 1, (B, 2))
+            if kind == "drq":
+                got = fs.sample(idxs, {"obs": o1, "next_obs": o2})
+                want = buf.sample_drq(pad=pad, idxs=idxs, offsets={"obs": o1, "next_obs": o2})
+            elif kind == "svea":
+                got = fs.sample(idxs, o1)
+                want = buf.sample_svea(pad=pad, idxs=idxs, offsets=o1)
+            else:
+                got = fs.sample(idxs)
+                want = buf.sample(idxs=idxs)
+            torch.cuda.synchronize()
+            for i, (a, b) in enumerate(zip(got, want)):
+                assert torch.equal(a.cpu(), b.cpu()), (kind, i)
+            if kind != "svea":
+                assert fs.reward_host is got[2] and not got[2].is_cuda
+        with pytest.raises(AugclError):
+            fs.sample(np.full(B, cap))
+        if kind == "drq":
+            with pytest.raises(AugclError):
+                fs.sample(np.zeros(B, np.int64), {"obs": np.full((B, 2), 2 * pad + 1), "next_obs": np.zeros((B, 2))})
+    fs = U.FastSampler(buf, kind="plain")
+    frame = np.full((9, S, S), 9, dtype=np.uint8)
+    slot = buf.idx
+    buf.add(frame, np.zeros(6, np.float32), 2.5, frame, False)
+    got = fs.sample(np.full(B, slot))
+    torch.cuda.synchronize()
+    assert float(got[0].min()) == 9.0 and float(got[0].max()) == 9.0 and float(got[2][0]) == 2.5
+    with pytest.raises(ValueError):
+        U.FastSampler(buf, batch=257)
