@@ -566,7 +566,7 @@ extern "C" int augcl_ring_sample_fused(augcl_ring* r, const augcl_fused_desc* d,
     }
   if (host_idx || host_off) {
     const size_t ib = (size_t)B * 8, ob = (size_t)B * 8;
-    AUGCL_CUDA(cudaMallocAsync(&scratch, ib + 2 * ob, st));
+    AUGCL_CUDA(cudaMallocFromPoolAsync(&scratch, ib + 2 * ob, r->scratch_pool, st));
     uint8_t* spn = static_cast<uint8_t*>(scratch);
     cudaError_t e = cudaSuccess;
     if (host_idx) {

@@ -306,7 +306,19 @@ static int ring_create_impl(const char* who, augcl_ring** out, int device, int64
   if (e == cudaSuccess) e = cudaMalloc(&r->nd, fbytes);
   if (e == cudaSuccess) e = cudaMalloc(&r->sched, 64);
   if (e == cudaSuccess) e = cudaMemset(r->sched, 0, 64);
+  if (e == cudaSuccess) {
+    cudaMemPoolProps props{};
+    props.allocType = cudaMemAllocationTypePinned;
+    props.location.type = cudaMemLocationTypeDevice;
+    props.location.id = device;
+    e = cudaMemPoolCreate(&r->scratch_pool, &props);
+    if (e == cudaSuccess) {
+      uint64_t keep = UINT64_MAX;
+      e = cudaMemPoolSetAttribute(r->scratch_pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    }
+  }
   if (e != cudaSuccess) {
+    if (r->scratch_pool) cudaMemPoolDestroy(r->scratch_pool);
     cudaFree(r->sched);
     cudaFree(r->obs); cudaFree(r->next); cudaFree(r->refs); cudaFree(r->act); cudaFree(r->rew); cudaFree(r->nd);
     delete r;
@@ -333,6 +345,7 @@ int augcl_ring_destroy(augcl_ring* r) {
   DeviceGuard g(r->device);
   cudaFree(r->obs); cudaFree(r->next); cudaFree(r->refs); cudaFree(r->act); cudaFree(r->rew); cudaFree(r->nd);
   cudaFree(r->sched);
+  if (r->scratch_pool) cudaMemPoolDestroy(r->scratch_pool);
   delete r;
   return AUGCL_OK;
 }
@@ -591,7 +604,7 @@ static int sample_impl(const char* who, augcl_ring* r, int idx_src, const int64_
     } else {
       // stream-ordered scratch: [idx int64 B][offsets of view 0 int32 2B][view 1] ...
       const size_t ib = (size_t)B * 8, ob = (size_t)B * 8;
-      AUGCL_CUDA(cudaMallocAsync(&scratch, ib + kMaxViews * ob, st));
+      AUGCL_CUDA(cudaMallocFromPoolAsync(&scratch, ib + kMaxViews * ob, r->scratch_pool, st));
       uint8_t* sp = static_cast<uint8_t*>(scratch);
       cudaError_t e = cudaSuccess;
       if (host_idx) {
