@@ -82,7 +82,8 @@ enum { kPreNone = 0, kPreSplice = 1, kPreSpliceFast = 2, kPreOverlay = 3 };
 // PRE, CONV: the aug chain (compile time: every variant is straight-line code, a few hundred SASS instructions
 // instead of one 5 000-instruction kernel that thrashes the instruction cache).  WC: image width (0 = p.sp.W).
 template <int PRE, bool CONV, bool NORM, int WC>
-__global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const __grid_constant__ FusedParams p) {
+__global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const __grid_constant__ FusedParams p,
+                                                                         const __grid_constant__ InlineDraws<kInlineMax> inl) {
   extern __shared__ __align__(128) uint8_t smem[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem);                 // <= 4 mbarriers
   FusedMeta* meta = reinterpret_cast<FusedMeta*>(smem + 32);          // <= 4 metas (4 x 56 B = 224 B)
@@ -101,7 +102,6 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
   constexpr bool kSplice = PRE == kPreSplice || PRE == kPreSpliceFast;
   constexpr bool kBank = PRE != kPreNone;
   constexpr int hal = CONV ? 1 : 0;
-  const InlineDraws<0> none{};
 
   // ---- static partition of the cost line [0, T) over the CTAs; a CTA owns the units whose start falls in its range
   const int64_t T = p.units_obs * p.cost_obs + p.units_next * p.cost_next;
@@ -141,9 +141,9 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
     const int b = (int)(fr / (uint32_t)p.k), f = (int)(fr - (uint32_t)b * (uint32_t)p.k);
     const int BAND = CONV ? kFBand : p.band;
     const int r0 = band * BAND, rows = min(BAND, H - r0);
-    const int64_t slot = sample_index(p.sp, none, b);
+    const int64_t slot = sample_index(p.sp, inl, b);
     int dy, dx;
-    sample_offset(p.sp, none, t, b, dy, dx);
+    sample_offset(p.sp, inl, t, b, dy, dx);
     const bool want_aug = t == 0 && p.o_aug != nullptr;
     const bool want_shift = p.o_shift[t] != nullptr;
     const bool want_plain = p.o_plain[t] != nullptr;
@@ -208,7 +208,7 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
   }
   if (dyn) __syncthreads();                     // valid[] of the prologue stages
   pdl_launch_dependents();
-  gather_scalars(p.sp, none);
+  gather_scalars(p.sp, inl);
 
   uint32_t phase = 0;
   int s = 0;
@@ -411,7 +411,7 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
 }  // namespace augcl
 
 namespace augcl {
-using FusedKernel = void (*)(const FusedParams);
+using FusedKernel = void (*)(const FusedParams, const InlineDraws<kInlineMax>);
 
 template <int PRE, bool CONV>
 static FusedKernel pick_wn(bool norm, int W) {
@@ -564,7 +564,19 @@ extern "C" int augcl_ring_sample_fused(augcl_ring* r, const augcl_fused_desc* d,
         AUGCL_REQUIRE(off[t][e] >= 0 && off[t][e] <= 2 * d->pad, "%s: offset %d (tensor %d, element %d) outside [0, %d]", who,
                       off[t][e], t, e, 2 * d->pad);
     }
-  if (host_idx || host_off) {
+  InlineDraws<kInlineMax> inl;
+  if ((host_idx || host_off) && B <= kInlineMax && r->capacity < (1ll << 31) && 2 * d->pad <= 127) {
+    // by value in the launch's parameter block: no scratch, no H2D copy (the offsets were range-checked above)
+    if (host_idx) {
+      for (int b = 0; b < B; ++b) inl.idx[b] = (int32_t)d->idx[b];
+      sp.idx_mode = kSrcInline;
+    }
+    for (int t = 0; t < 2; ++t)
+      if (sp.off_mode[t] == AUGCL_SRC_HOST) {
+        for (int b = 0; b < B; ++b) { inl.off[t][b][0] = (int8_t)off[t][2 * b]; inl.off[t][b][1] = (int8_t)off[t][2 * b + 1]; }
+        sp.off_mode[t] = kSrcInline;
+      }
+  } else if (host_idx || host_off) {
     const size_t ib = (size_t)B * 8, ob = (size_t)B * 8;
     AUGCL_CUDA(cudaMallocFromPoolAsync(&scratch, ib + 2 * ob, r->scratch_pool, st));
     uint8_t* spn = static_cast<uint8_t*>(scratch);
@@ -611,7 +623,7 @@ extern "C" int augcl_ring_sample_fused(augcl_ring* r, const augcl_fused_desc* d,
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = g_sample_pdl.load() ? 1 : 0;
-  cudaError_t le = cudaLaunchKernelEx(&cfg, kern, p);
+  cudaError_t le = cudaLaunchKernelEx(&cfg, kern, p, inl);
   if (le == cudaSuccess) le = cudaGetLastError();
   if (scratch) cudaFreeAsync(scratch, st);   // stream-ordered: released after the kernel that reads it
   if (le != cudaSuccess) AUGCL_FAIL(AUGCL_ERR_CUDA, "%s: launch failed: %s", who, cudaGetErrorString(le));

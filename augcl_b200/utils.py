@@ -860,3 +860,96 @@ class FastSampler(object):
         if rc != 0:
             raise L.AugclError("augcl_ring_sample_ex", rc, L.lib().augcl_last_error().decode(errors="replace"))
         return self.out
+
+
+class FastFusedSampler(object):
+    """``sample_augcl`` / ``sample_svea_aug`` with the per-call Python work taken out (batch <= 256): fixed output tensors,
+    a cached ``augcl_fused_desc``, the host indices by value in the launch.  Per step: the bank-row and conv-weight draws
+    (two small Philox launches, the same subsequences ``sample_fused`` would use) and ONE fused sample kernel.
+
+        fs = FastFusedSampler(buf, kind="augcl", data_aug="splice-conv")          # once
+        obs_shift, obs_aug, action, reward, next_obs, not_done = fs.sample()      # every update (src/algorithms/augcl.py:69-72)
+
+    kind="svea_aug" augments the SHIFTED obs (src/algorithms/svea.py:67 + :46).  Outputs are valid until the next call."""
+
+    def __init__(self, buf, kind="augcl", data_aug=None, aug_params=None, pad=4, batch=None):
+        if kind not in ("augcl", "svea_aug"):
+            raise ValueError("FastFusedSampler: kind must be 'augcl' or 'svea_aug'")
+        data_aug = data_aug if data_aug is not None else ("splice-conv" if kind == "augcl" else "overlay")
+        keys = tuple(k for k in str(data_aug).split("-") if k and k != "identity")
+        if not keys or keys not in ReplayBuffer._FUSED_CHAINS:
+            raise NotImplementedError(f"FastFusedSampler: chain {data_aug!r} is not fused")
+        B = self.B = int(batch or buf.batch_size)
+        if B > 256:
+            raise ValueError("FastFusedSampler: batch > 256 does not fit the kernel's parameter block")
+        self.buf, self.kind, self.pad = buf, kind, int(pad)
+        aug_params = aug_params or {}
+        dev = buf.device
+        c, h, w = buf.obs_shape
+        self._idx = np.zeros(B, dtype=np.int64)
+        self._off = np.full((2, B, 2), self.pad, dtype=np.int32)
+        obs_shift, obs_aug, nxt = torch.empty((3, B, c, h, w), dtype=torch.float32, device=dev).unbind(0)
+        act = torch.empty((B,) + buf.actions.shape[1:], dtype=torch.float32, device=dev)
+        rew, nd = torch.empty((2, B, 1), dtype=torch.float32, device=dev).unbind(0)
+        self.out = (obs_shift, obs_aug, act, rew, nxt, nd)
+        d = self._d = L.FusedDesc()
+        d.struct_size = C.sizeof(L.FusedDesc)
+        d.B, d.idx_src, d.idx, d.idx_hi = B, L.SRC_HOST, self._idx.ctypes.data, 0
+        d.pad, d.normalize, d.seed = self.pad, 0, augmentations._seed
+        d.out_obs_shift, d.out_obs_aug, d.out_next = obs_shift.data_ptr(), obs_aug.data_ptr(), nxt.data_ptr()
+        d.out_act, d.out_rew, d.out_nd = act.data_ptr(), rew.data_ptr(), nd.data_ptr()
+        ops = 0
+        for k in keys:
+            ops |= ReplayBuffer._FUSED_OPS[k]
+        d.aug_ops = ops
+        d.aug_input = L.AUG_INPUT_SHIFTED if kind == "svea_aug" else L.AUG_INPUT_PLAIN
+        self._rows = self._wt = None
+        pre = next((k for k in keys if k != "conv"), None)
+        if pre is not None:
+            prm = aug_params.get(pre, {})
+            augmentations.load_dataloader(batch_size=B, image_size=h, dataset=prm.get("dataset", "coco"), device=dev)
+            bank = self._bank = augmentations.get_background_bank()
+            if bank.dtype != torch.uint8 or bank.device != dev or tuple(bank.shape[2:]) != (h, w):
+                raise NotImplementedError("FastFusedSampler: needs a uint8 background bank of the observation size on the ring's device")
+            self._rows = torch.empty(B, dtype=torch.int64, device=dev)
+            d.bank, d.bank_len, d.bank_idx = bank.data_ptr(), bank.shape[0], self._rows.data_ptr()
+            if pre == "overlay":
+                d.alpha = float(prm.get("alpha", 0.5))
+            else:
+                dflt = (0, 0, 0.6) if pre == "splice" else (3.5, 0, 0)
+                d.hue_thres = float(prm.get("hue_thres", dflt[0]))
+                d.sat_thres = float(prm.get("sat_thres", dflt[1]))
+                d.val_thres = float(prm.get("val_thres", dflt[2]))
+        if "conv" in keys:
+            self._wt = torch.empty((B, 3, 3, 3, 3), dtype=torch.float32, device=dev)
+            d.conv_weights = self._wt.data_ptr()
+        lib = L.lib()
+        self._fill_idx, self._fill_normal, self._fused = lib.augcl_rng_fill_indices, lib.augcl_rng_fill_normal, lib.augcl_ring_sample_fused
+        self._dref = C.byref(d)
+        self._dev_index = buf._dev_index
+
+    def sample(self, idxs=None, offsets=None):
+        """idxs: (B,) host integers (default: the reference's np.random.randint draw, src/utils.py:229-232); offsets:
+        {"obs": (B,2), "next_obs": (B,2)} host shift draws, default drawn in the kernel (Philox)."""
+        buf, d = self.buf, self._d
+        if buf._st_count:
+            buf._flush()
+        self._idx[:] = buf._get_idxs(self.B) if idxs is None else idxs
+        st = _raw_stream(self._dev_index)
+        d.seed = augmentations._seed
+        d.subsequence = augmentations._reserve_subsequences(3)
+        if offsets is None:
+            d.off_src, d.off_obs, d.off_next = L.SRC_PHILOX, None, None
+        else:
+            self._off[0] = offsets["obs"]
+            d.off_src, d.off_obs, d.off_next = L.SRC_HOST, self._off[0].ctypes.data, None
+        rc = 0
+        if self._rows is not None:
+            rc = self._fill_idx(self._rows.data_ptr(), self.B, 0, d.bank_len, d.seed, augmentations._next_subsequence(), st)
+        if rc == 0 and self._wt is not None:
+            rc = self._fill_normal(self._wt.data_ptr(), self.B * 81, d.seed, augmentations._next_subsequence(), st)
+        if rc == 0:
+            rc = self._fused(buf._ring, self._dref, st)
+        if rc != 0:
+            raise L.AugclError("augcl_ring_sample_fused", rc, L.lib().augcl_last_error().decode(errors="replace"))
+        return self.out

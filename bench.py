@@ -394,7 +394,7 @@ def fused_configs(res):
     device-timed extras next to the bench line (configs[1] stays the headline workload)."""
     import ctypes
     import torch
-    from augcl_b200 import _lib as L, augmentations as A
+    from augcl_b200 import _lib as L, augmentations as A, utils as U
     buf, dev = res["buf"], res["dev"]
     peak = load_peaks()[0]
     A.load_dataloader(128, S, device=dev)
@@ -444,10 +444,26 @@ def fused_configs(res):
         torch.cuda.synchronize(dev)
         us = e0.elapsed_time(e1) * 1e3 / iters
         gbs = B * abytes / us / 1e3
+        # the same update() input end to end: utils.FastFusedSampler with HOST indices (numpy), the bank-row / weight /
+        # offset draws on the device, a stream synchronize and a host read of the rewards every step
+        fs = U.FastFusedSampler(buf, kind="svea_aug" if aug_in == L.AUG_INPUT_SHIFTED else "augcl",
+                                data_aug="overlay" if ops == L.OP_OVERLAY else "splice-conv", pad=PAD, batch=B)
+        h_idx = np.random.RandomState(3).randint(0, CAP, (64, B))
+        h_rew = torch.empty((B, 1), dtype=torch.float32).pin_memory()
+        for t in range(5):
+            fs.sample(h_idx[t])
+        stream.synchronize()
+        t0 = time.perf_counter()
+        for t in range(500):
+            h_rew.copy_(fs.sample(h_idx[t % 64])[3], non_blocking=True)
+            stream.synchronize()
+        e2e_us = (time.perf_counter() - t0) / 500 * 1e6
         out.append({"workload": name, "batch": B, "us_per_step": round(us, 2), "samples_per_s": round(B / us * 1e6),
                     "algorithmic_bytes_per_sample": abytes, "GB/s": round(gbs, 1), "frac": round(gbs / peak, 4),
-                    "kernel": "ring_sample_fused_kernel", "launches_per_step": 1})
-        del o
+                    "kernel": "ring_sample_fused_kernel", "launches_per_step": 1,
+                    "e2e_us_per_step": round(e2e_us, 2), "e2e_samples_per_s": round(B / e2e_us * 1e6),
+                    "e2e_api": "utils.FastFusedSampler.sample(host idxs) + D2H of the rewards + stream synchronize every step"})
+        del o, fs
     return out
 
 

@@ -135,3 +135,40 @@ def test_fast_sampler_equals_eager_calls():
     assert float(got[0].min()) == 9.0 and float(got[0].max()) == 9.0 and float(got[2][0]) == 2.5
     with pytest.raises(ValueError):
         U.FastSampler(buf, batch=257)
+
+
+@pytest.mark.parametrize("kind,data_aug", [("augcl", "splice-conv"), ("svea_aug", "overlay"), ("augcl", "conv"),
+                                           ("svea_aug", "CS_splice")])
+def test_fast_fused_sampler_equals_sample_fused(kind, data_aug):
+    """utils.FastFusedSampler (cached descriptor, fixed outputs, host indices by value in the launch) returns what
+    ReplayBuffer.sample_augcl / sample_svea_aug return for the same seed, indices and (optional) host offsets."""
+    from augcl_b200 import utils as U, augmentations as A
+    S, cap, B, pad = 84, 200, 24, 4
+    buf = U.ReplayBuffer((9, S, S), (6,), cap, B)
+    buf.fill_synthetic(seed=5)
+    bank = torch.randint(0, 256, (32, 3, S, S), dtype=torch.uint8, device="cuda")
+    A.set_background_bank(bank)
+    try:
+        fs = U.FastFusedSampler(buf, kind=kind, data_aug=data_aug, pad=pad)
+        ref = buf.sample_augcl if kind == "augcl" else buf.sample_svea_aug
+        rng = np.random.RandomState(2)
+        for step in range(3):
+            idxs = rng.randint(0, cap, size=B)
+            offs = None if step == 0 else {"obs": rng.randint(0, 2 * pad + 1, (B, 2))}
+            A.seed(11 + step)
+            want = ref(idxs=idxs, data_aug=data_aug, pad=pad, offsets=offs)
+            A.seed(11 + step)
+            got = fs.sample(idxs, offs)
+            torch.cuda.synchronize()
+            for i, (a, b) in enumerate(zip(got, want)):
+                assert torch.equal(a, b), (kind, data_aug, step, i)
+        np.random.seed(3)
+        A.seed(1)
+        want = ref(data_aug=data_aug, pad=pad)           # the reference's own index draw (numpy global RNG)
+        np.random.seed(3)
+        A.seed(1)
+        got = fs.sample()
+        for a, b in zip(got, want):
+            assert torch.equal(a, b)
+    finally:
+        A.set_background_bank(None)
