@@ -22,6 +22,11 @@
  *     functions generate such draws on the device (Philox4x32-10) when the caller has none.
  *   - device pointers must belong to the calling thread's current CUDA device, except ring
  *     calls, which switch to the ring's device for the duration of the call.
+ *   - threading: the stateless augmentation entry points may be called from any thread on any
+ *     stream.  A ring handle is single-writer like the reference's ReplayBuffer (one Python
+ *     thread, src/train.py): calls on ONE ring must be issued in order on ONE stream at a time
+ *     (its sample kernels share schedule counters and stream-ordered scratch); different rings
+ *     are independent.  CUDA-graph capture of ring calls is supported (tests/test_gpu_graph.py).
  */
 #ifndef AUGCL_B200_H_
 #define AUGCL_B200_H_
