@@ -14,6 +14,7 @@
 #include "pixel.cuh"
 
 namespace augcl {
+std::atomic<int> g_bil_tma{1};   // bilinear shift: double-buffered cp.async.bulk tiles (0 = single tile, LDG fill)
 
 // ---------------------------------------------------------------------------------------------
 // window copy: out[i,ch,r,q] = in[i,ch,clamp(r+dy_i,0,H-1),clamp(q+dx_i,0,W-1)]
@@ -186,10 +187,17 @@ __global__ void __launch_bounds__(256) shift_bilinear_smem_kernel(const float* _
   // per output row: {byte offset of the upper source row in the tile, of the lower one, ty, flags}; flags bit 0 / 1 = the
   // upper / lower row lies outside the padded image (those taps read zero, as grid_sample's zeros padding does).  The
   // table is padded to a multiple of 4 rows (copies of the last row) so a 4-row trip never indexes past it.
+  // vec == 2: two tiles, the next plane's 4*h*w bytes arrive by ONE cp.async.bulk while this plane is computed.
   const int h4 = (h + 3) & ~3;
+  __shared__ uint64_t bars[2];
   int4* s_row = reinterpret_cast<int4*>(bsm);
-  float* tile = reinterpret_cast<float*>(bsm + (size_t)h4 * 16);
-  const uint32_t tile_s = smem_u32(tile);
+  float* tile0 = reinterpret_cast<float*>(bsm + (size_t)h4 * 16);
+  const bool tma = vec == 2;
+  if (tma && threadIdx.x == 0) {
+    mbar_init(&bars[0], 1);
+    mbar_init(&bars[1], 1);
+    mbar_fence_init();
+  }
   const int Hp = h + 2 * pad, Wp = w + 2 * pad;
   const float sc = (float)(2.0 / (double)Hp);
   const int nchunk = 256 / w, rows_per = (((h + nchunk - 1) / nchunk) + 3) & ~3;
@@ -197,12 +205,28 @@ __global__ void __launch_bounds__(256) shift_bilinear_smem_kernel(const float* _
   const bool active = rc < nchunk && rc * rows_per < h;
   const float bx = active ? __ldg(base + x) : 0.0f;
   const int n_el = h * w;
-  for (int plane = blockIdx.x; plane < planes; plane += gridDim.x) {
+  if (tma) {
+    __syncthreads();
+    if (threadIdx.x == 0 && (int)blockIdx.x < planes) {
+      mbar_expect_tx(&bars[0], (uint32_t)n_el * 4);
+      bulk_g2s(tile0, in + (int64_t)blockIdx.x * n_el, (uint32_t)n_el * 4, &bars[0]);
+    }
+  }
+  int it = 0;
+  for (int plane = blockIdx.x; plane < planes; plane += gridDim.x, ++it) {
     const int i = plane / c;
     const float sy = (float)offsets[2 * i] * sc, sx = (float)offsets[2 * i + 1] * sc;
     const float* src = in + (int64_t)plane * n_el;
+    float* tile = tile0 + (tma ? (it & 1) * n_el : 0);
+    const uint32_t tile_s = smem_u32(tile);
     __syncthreads();                               // the previous plane's taps are done
-    if (vec) {
+    if (tma) {
+      const int nxt = plane + gridDim.x;
+      if (threadIdx.x == 0 && nxt < planes) {
+        mbar_expect_tx(&bars[(it + 1) & 1], (uint32_t)n_el * 4);
+        bulk_g2s(tile0 + ((it + 1) & 1) * n_el, in + (int64_t)nxt * n_el, (uint32_t)n_el * 4, &bars[(it + 1) & 1]);
+      }
+    } else if (vec) {
       const float4* s4 = reinterpret_cast<const float4*>(src);
       float4* t4 = reinterpret_cast<float4*>(tile);
       for (int e = threadIdx.x; e < (n_el >> 2); e += 256) t4[e] = __ldg(s4 + e);
@@ -220,6 +244,7 @@ __global__ void __launch_bounds__(256) shift_bilinear_smem_kernel(const float* _
     }
     __syncthreads();
     if (!active) continue;
+    if (tma) mbar_wait(&bars[it & 1], (uint32_t)(it >> 1) & 1u);
     const float gx = bx + sx;
     const float ix = ((gx + 1.0f) * (float)Wp - 1.0f) / 2.0f;
     const float fx = floorf(ix);
@@ -684,8 +709,15 @@ int augcl_random_shift(const float* in, float* out, int n, int c, int h, int w, 
       cudaFuncSetAttribute(shift_bilinear_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBilSmemMax);
     });
     const int planes = n * c;
-    const int vec = ((h * w) & 3) == 0 && aligned(in, 16);
-    shift_bilinear_smem_kernel<<<planes < kNumSMs * 8 ? planes : kNumSMs * 8, 256, bsmem, st>>>(
+    int vec = ((h * w) & 3) == 0 && aligned(in, 16);
+    size_t smem = bsmem;
+    if (vec && bsmem + (size_t)h * w * 4 <= (size_t)kBilSmemMax && g_bil_tma.load()) {
+      vec = 2;                                   // double-buffered tiles filled by cp.async.bulk
+      smem = bsmem + (size_t)h * w * 4;
+    }
+    const int per_sm = (int)((228 * 1024) / (smem + 1024));
+    const int cap = kNumSMs * (per_sm < 1 ? 1 : (per_sm > 8 ? 8 : per_sm));
+    shift_bilinear_smem_kernel<<<planes < cap ? planes : cap, 256, smem, st>>>(
         in, out, planes, c, h, w, pad, offsets, base, vec);
     AUGCL_LAUNCHED();
     return AUGCL_OK;

@@ -17,6 +17,7 @@ extern std::atomic<int> g_fused_cost_next;
 extern std::atomic<int> g_fused_fast_mask;
 extern std::atomic<int> g_fused_stages;
 extern std::atomic<int> g_fused_band;
+extern std::atomic<int> g_bil_tma;
 extern std::atomic<int> g_fused_dynamic;
 static thread_local std::string t_error;
 void set_error(const std::string& msg) { t_error = msg; }
@@ -66,6 +67,7 @@ int augcl_set_option(const char* key, const char* value) {
     AUGCL_REQUIRE(v >= 0 && v <= 14, "fused_band must be in [0,14] (0 = auto)");
     g_fused_band = v; return AUGCL_OK;
   }
+  if (!strcmp(key, "bilinear_tma")) { g_bil_tma = atoi(value) != 0; return AUGCL_OK; }
   if (!strcmp(key, "fused_fast_mask")) { g_fused_fast_mask = atoi(value) != 0; return AUGCL_OK; }
   if (!strcmp(key, "fused_cost_next")) { g_fused_cost_next = atoi(value); return AUGCL_OK; }
   AUGCL_FAIL(AUGCL_ERR_BAD_ARG, "augcl_set_option: unknown key '%s'", key);
