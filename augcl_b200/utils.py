@@ -407,6 +407,30 @@ class ReplayBuffer(object):
         return self._sample(idxs, n=n, aug=L.AUG_SHIFT, off_obs=offsets.get("obs"), off_next=offsets.get("next_obs"),
                             pad_or_size=pad, device_indices=device_indices)
 
+    def sample_encoder_input(self, n=None, *, idxs=None, center_crop=None, device_indices=False):
+        """sample() with the encoder's first two layers folded into the same kernel:
+        obs / next_obs = NormalizeImg(CenterCrop(center_crop)(.)) of src/algorithms/modules.py:69-90 — the centre
+        ``center_crop`` x ``center_crop`` window (None or the stored size: no crop) divided by 255.0 (IEEE-rounded, bit-equal
+        to torch's ``x / 255.0``).  Saves the f32 round trip of the un-normalised batch per encoder call."""
+        c, h, w = self.obs_shape
+        size = h if center_crop is None else int(center_crop)
+        if size == h and size == w:
+            return self._sample(idxs, n=n, normalize=True, device_indices=device_indices)
+        if not (0 < size <= min(h, w)) or (h - size) % 2 or (w - size) % 2:
+            raise ValueError(f"sample_encoder_input: cannot centre a {size}x{size} window in {h}x{w}")
+        B = self.batch_size if n is None else int(n)
+        if idxs is not None:
+            B = int(idxs.numel()) if isinstance(idxs, torch.Tensor) else int(np.asarray(idxs).size)
+        key = (B, size)
+        off = self._center_off.get(key) if hasattr(self, "_center_off") else None
+        if off is None:
+            if not hasattr(self, "_center_off"):
+                self._center_off = {}
+            off = self._center_off[key] = torch.tensor([[(h - size) // 2, (w - size) // 2]], dtype=torch.int32,
+                                                       device=self.device).repeat(B, 1).contiguous()
+        return self._sample(idxs, n=n, aug=L.AUG_CROP, off_obs=off, off_next=off, pad_or_size=size, normalize=True,
+                            device_indices=device_indices)
+
     def sample_drq_km(self, n=None, pad=4, *, k=2, m=2, idxs=None, offsets=None, device_indices=False):
         """A DrQ update's data (src/algorithms/drq.py:67-70) from ONE kernel: k independently shifted copies of obs and m
         of next_obs.  Returns (obs_list, action, reward, next_obs_list, not_done).

@@ -357,3 +357,25 @@ def test_sample_drq_km_one_launch(U, O, S, B):
     assert torch.equal(next_l[0].cpu(), O.random_shift_int(o_next, draws[2], pad))
     assert torch.equal(next_l[1].cpu(), O.random_shift_int(o_next, draws[3], pad))
     assert not torch.equal(obs_l[0], obs_l[1])
+
+
+@pytest.mark.parametrize("S,size", [(100, 84), (84, 84), (100, None), (20, 12)])
+def test_sample_encoder_input_is_centercrop_plus_normalize(U, S, size):
+    """NormalizeImg(CenterCrop(size)(obs)) of src/algorithms/modules.py:69-90 out of the sample kernel,
+    bit-equal to slicing and dividing the plain sample() with torch (x[:, :, p:-p, p:-p] / 255.0)."""
+    cap, B = 60, 10
+    buf = U.ReplayBuffer((9, S, S), (3,), cap, B)
+    buf.fill_synthetic(seed=S)
+    idxs = np.random.RandomState(S).randint(0, cap, size=B)
+    plain = buf.sample(idxs=idxs)
+    got = buf.sample_encoder_input(idxs=idxs, center_crop=size)
+    p = 0 if size is None else (S - size) // 2
+    for i in (0, 3):
+        x = plain[i].cpu()
+        want = (x[:, :, p:S - p, p:S - p] if p else x) / 255.0
+        assert torch.equal(got[i].cpu(), want)
+    for i in (1, 2, 4):
+        assert torch.equal(got[i], plain[i])
+    if S == 20:
+        with pytest.raises(ValueError):
+            buf.sample_encoder_input(idxs=idxs, center_crop=13)
