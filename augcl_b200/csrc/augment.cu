@@ -14,6 +14,7 @@
 #include "pixel.cuh"
 
 namespace augcl {
+std::atomic<int> g_conv_part{1};  // random_conv: part-of-frame items (0 = 12-row bands, double-buffered)
 std::atomic<int> g_bil_tma{1};   // bilinear shift: double-buffered cp.async.bulk tiles (0 = single tile, LDG fill)
 
 // ---------------------------------------------------------------------------------------------
@@ -519,6 +520,110 @@ __global__ void __launch_bounds__(kConvThreads, 7) random_conv_tma_kernel(const 
 }
 
 // ---------------------------------------------------------------------------------------------
+// random_conv, part-of-frame variant (w % 4 == 0, 16-B aligned tensors): a work item is R consecutive rows of one RGB
+// frame (R = 42 at 84x84: half a frame), brought in by THREE cp.async.bulk (each plane's rows are contiguous) into one
+// tile whose row stride is w itself; the replicate pad is index clamping (rows) and a select in registers (columns), so
+// nothing touches the tile after the copy lands.  224 threads = 441 tasks in two rounds; one item = 7x the work of the
+// 12-row band kernel between CTA barriers.  Single tile: the other CTAs of the SM compute while this one loads.
+// ---------------------------------------------------------------------------------------------
+constexpr int kPartThreads = 224;
+__global__ void __launch_bounds__(kPartThreads, 4) random_conv_part_kernel(const float* __restrict__ in, float* __restrict__ out,
+                                                                           int frames, int k, int h, int w,
+                                                                           const float* __restrict__ weights, int parts, int R) {
+  extern __shared__ __align__(128) float psm[];
+  uint64_t* bar = reinterpret_cast<uint64_t*>(psm);        // 1 mbarrier; header padded to 128 floats
+  float* wsm = psm + 16;                                   // [27][4]
+  float* tile = psm + 128;                                 // [3][R+2][w]
+  const int tid = threadIdx.x;
+  const int nq = w >> 2;
+  const int total = frames * parts;
+  if (tid == 0) {
+    mbar_init(bar, 1);
+    mbar_fence_init();
+  }
+  __syncthreads();
+  pdl_wait();
+  pdl_launch_dependents();
+  int n = 0;
+  for (int work = blockIdx.x; work < total; work += gridDim.x, ++n) {
+    const int frame = work / parts, part = work - frame * parts;
+    const int sample = frame / k;
+    const int r0 = part * R;
+    const int rows = min(R, h - r0);
+    const int lo = max(r0 - 1, 0), hi = min(r0 + rows, h - 1);      // source rows [lo, hi] are staged
+    const int nrows = hi - lo + 1;
+    __syncthreads();                                       // the previous item no longer reads the tile / wsm
+    if (tid == 0) {
+      const uint32_t bytes = (uint32_t)(nrows * w * 4);
+      mbar_expect_tx(bar, 3 * bytes);
+#pragma unroll
+      for (int ci = 0; ci < 3; ++ci)
+        bulk_g2s(tile + ci * (R + 2) * w, in + (((int64_t)frame * 3 + ci) * h + lo) * w, bytes, bar);
+    }
+    if (tid < 81) {
+      // weights[sample][co][ci][ky][kx] / 255 -> wsm[(ci*9 + ky*3 + kx)*4 + co]
+      const int co = tid / 27, tap = tid - co * 27;
+      wsm[tap * 4 + co] = __fdiv_rn(weights[(int64_t)sample * 81 + tid], 255.0f);
+    }
+    __syncthreads();
+    mbar_wait(bar, (uint32_t)n & 1u);
+    const int ntask = ((rows + 1) >> 1) * nq;
+    for (int task = tid; task < ntask; task += (int)blockDim.x) {
+      const int rp = task / nq, q4 = task - rp * nq;
+      const int r = rp * 2;
+      const bool left = q4 == 0, right = q4 == nq - 1;
+      int trow_off[4];
+#pragma unroll
+      for (int y = 0; y < 4; ++y) trow_off[y] = (clampi(r0 + r + y - 1, 0, h - 1) - lo) * w + q4 * 4;
+      float acc[2][3][4];
+#pragma unroll
+      for (int a = 0; a < 2; ++a)
+#pragma unroll
+        for (int co = 0; co < 3; ++co)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) acc[a][co][j] = 0.0f;
+#pragma unroll 1
+      for (int ci = 0; ci < 3; ++ci) {
+        const float* pl = tile + ci * (R + 2) * w;
+        float x[4][6];
+#pragma unroll
+        for (int y = 0; y < 4; ++y) {
+          const float* trow = pl + trow_off[y];
+          const float4 a = *reinterpret_cast<const float4*>(trow);
+          const float l = trow[-1], rt = trow[4];
+          x[y][0] = left ? a.x : l; x[y][1] = a.x; x[y][2] = a.y; x[y][3] = a.z; x[y][4] = a.w; x[y][5] = right ? a.w : rt;
+        }
+#pragma unroll
+        for (int ky = 0; ky < 3; ++ky) {
+#pragma unroll
+          for (int kx = 0; kx < 3; ++kx) {
+            const float4 wv = *reinterpret_cast<const float4*>(wsm + (ci * 9 + ky * 3 + kx) * 4);
+#pragma unroll
+            for (int a = 0; a < 2; ++a)
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                acc[a][0][j] = fmaf(x[a + ky][j + kx], wv.x, acc[a][0][j]);
+                acc[a][1][j] = fmaf(x[a + ky][j + kx], wv.y, acc[a][1][j]);
+                acc[a][2][j] = fmaf(x[a + ky][j + kx], wv.z, acc[a][2][j]);
+              }
+          }
+        }
+      }
+#pragma unroll
+      for (int a = 0; a < 2; ++a) {
+        if (r + a >= rows) break;
+#pragma unroll
+        for (int co = 0; co < 3; ++co) {
+          float4* dst = reinterpret_cast<float4*>(out + (((int64_t)frame * 3 + co) * h + (r0 + r + a)) * w) + q4;
+          st_global_f4(dst, make_float4(sigmoid255(acc[a][co][0]), sigmoid255(acc[a][co][1]), sigmoid255(acc[a][co][2]),
+                                        sigmoid255(acc[a][co][3])));
+        }
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
 // overlay / splice: streaming elementwise kernels.  Background rows come from a device-resident bank
 // ([M][3][h][w], u8 or f32 in [0,1]); a u8 pixel is divided by 255 like torchvision's ToTensor.
 // ---------------------------------------------------------------------------------------------
@@ -759,6 +864,35 @@ int augcl_random_conv(const float* in, float* out, int n, int c, int h, int w, c
   const int vec = ((w & 3) == 0 && aligned(in, 16) && aligned(out, 16)) ? 1 : 0;
   const int64_t work = (int64_t)frames * bands;
   AUGCL_REQUIRE(work < (1ll << 30), "augcl_random_conv: batch too large");
+  if (vec && g_staging.load() == 0 && g_conv_part.load()) {
+    // part-of-frame items: the fewest parts whose tile fits ~55 KB (4 CTAs per SM) -- measured best from batch 128 to
+    // 2048 (scripts/tune_conv.py; conv_part >= 2 forces the count)
+    int parts = 1;
+    while (parts < h && (size_t)3 * ((h + parts - 1) / parts + 2) * w * 4 > 54 * 1024) ++parts;
+    if (g_conv_part.load() >= 2) parts = g_conv_part.load();
+    const int R = (((h + parts - 1) / parts) + 1) & ~1;          // even: row pairs never straddle two items
+    parts = (h + R - 1) / R;
+    // threads: the item's tasks in the fewest equal rounds of <= 224 threads
+    const int ntask = (R / 2) * (w / 4);
+    const int rounds = (ntask + kPartThreads - 1) / kPartThreads;
+    int threads = (((ntask + rounds - 1) / rounds) + 31) & ~31;
+    if (threads < 96) threads = 96;                              // 81 threads stage the weights
+    const size_t smem3 = (128 + (size_t)3 * (R + 2) * w + 4) * sizeof(float);
+    if (smem3 <= 100 * 1024) {
+      static std::atomic<bool> configured3{false};
+      if (!configured3.exchange(true))
+        AUGCL_CUDA(cudaFuncSetAttribute(random_conv_part_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+      int per_sm = (int)((228 * 1024) / (smem3 + 1024));
+      const int by_regs = 65536 / (72 * threads);
+      per_sm = per_sm > by_regs ? by_regs : per_sm;
+      per_sm = per_sm < 1 ? 1 : per_sm;
+      const int64_t items = (int64_t)frames * parts;
+      const int grid = (int)(items < kNumSMs * per_sm ? items : kNumSMs * per_sm);
+      random_conv_part_kernel<<<grid, threads, smem3, (cudaStream_t)stream>>>(in, out, frames, k, h, w, weights, parts, R);
+      AUGCL_LAUNCHED();
+      return AUGCL_OK;
+    }
+  }
   if (vec && g_staging.load() == 0) {
     const int RS2 = (w + 8) & ~3;
     const size_t smem2 = (16 + 27 * 4 + 2 * 3 * (kBand + 2) * (size_t)RS2) * sizeof(float);

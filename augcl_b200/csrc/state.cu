@@ -18,6 +18,7 @@ extern std::atomic<int> g_fused_fast_mask;
 extern std::atomic<int> g_fused_stages;
 extern std::atomic<int> g_fused_band;
 extern std::atomic<int> g_bil_tma;
+extern std::atomic<int> g_conv_part;
 extern std::atomic<int> g_fused_dynamic;
 static thread_local std::string t_error;
 void set_error(const std::string& msg) { t_error = msg; }
@@ -67,6 +68,7 @@ int augcl_set_option(const char* key, const char* value) {
     AUGCL_REQUIRE(v >= 0 && v <= 14, "fused_band must be in [0,14] (0 = auto)");
     g_fused_band = v; return AUGCL_OK;
   }
+  if (!strcmp(key, "conv_part")) { g_conv_part = atoi(value); return AUGCL_OK; }   // 0 off, 1 auto, >= 2 parts
   if (!strcmp(key, "bilinear_tma")) { g_bil_tma = atoi(value) != 0; return AUGCL_OK; }
   if (!strcmp(key, "fused_fast_mask")) { g_fused_fast_mask = atoi(value) != 0; return AUGCL_OK; }
   if (!strcmp(key, "fused_cost_next")) { g_fused_cost_next = atoi(value); return AUGCL_OK; }

@@ -124,6 +124,24 @@ def test_bilinear_shift_kernel_variants(A, O, S):
                         O.random_shift_bilinear(x, off.flip(1).numpy(), pad)) <= TOL_NORM * max(1.0, S / 84)
 
 
+@pytest.mark.parametrize("shape", [(3, 3, 8, 8), (2, 6, 16, 16), (5, 9, 84, 84), (2, 3, 33, 40), (3, 6, 100, 100),
+                                   (1, 3, 50, 200)])
+def test_random_conv_kernel_variants(A, O, shape):
+    """The part-of-frame kernel (any part count, including the ragged last part and tiny images whose CTA is smaller
+    than the 81 weight loaders) and the 12-row band kernels give the oracle's result."""
+    from augcl_b200 import _lib as L
+    g = torch.Generator().manual_seed(sum(shape))
+    x = torch.rand(shape, generator=g) * 255.0
+    wt = torch.randn(shape[0], 3, 3, 3, 3, generator=g)
+    want = O.random_conv(x, wt)
+    try:
+        for parts in (1, 0, 2, 3, 4, 6):
+            L.set_option("conv_part", str(parts))
+            assert norm_err(A.random_conv(x.cuda(), weights=wt), want) <= TOL_NORM, parts
+    finally:
+        L.set_option("conv_part", "1")
+
+
 def test_known_answers(A):
     # zero weights -> sigmoid(0)*255 == 127.5 everywhere
     x = torch.rand(2, 6, 10, 12, device="cuda") * 255
