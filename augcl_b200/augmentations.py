@@ -385,8 +385,12 @@ def color_jitter(imgs, p=1, *, sampled_idxs=None, params=None):
     if sampled_idxs is None:
         sampled_idxs = np.random.randint(0, b, num_samples)
     if params is None:
-        import torchvision.transforms as TF
-        params = TF.ColorJitter.get_params(None, [0.0, 2.0], [0.0, 3.0], [-0.5, 0.5])
+        # torchvision ColorJitter.get_params(None, [0,2], [0,3], [-0.5,0.5]) restated: same calls on torch's CPU RNG, in order
+        fn_idx = torch.randperm(4)
+        cf = float(torch.empty(1).uniform_(0.0, 2.0))
+        sf = float(torch.empty(1).uniform_(0.0, 3.0))
+        hf = float(torch.empty(1).uniform_(-0.5, 0.5))
+        params = (fn_idx, None, cf, sf, hf)
     fn_idx, bf, cf, sf, hf = params
     sel_np = np.unique(np.asarray(sampled_idxs, dtype=np.int64))
     if sel_np.size and (sel_np[0] < 0 or sel_np[-1] >= b * (c // 3)):
