@@ -35,6 +35,7 @@ class FusedDesc(C.Structure):
         ("aug_input", C.c_int32), ("aug_ops", C.c_int32),
         ("bank", _p), ("bank_len", _i64), ("bank_idx", _p), ("conv_weights", _p),
         ("hue_thres", _f), ("sat_thres", _f), ("val_thres", _f), ("alpha", _f),
+        ("bank_subsequence", _u64),
     ]
 
 

@@ -42,6 +42,7 @@ struct FusedParams {
   float* o_aug;
   const uint8_t* bank;
   const int64_t* bank_idx;
+  uint64_t bank_subseq;     // bank_idx == nullptr: rows drawn here, same values as augcl_rng_fill_indices
   const float* weights;
   int64_t bank_len;
   SpliceThr thr;
@@ -175,7 +176,8 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
     m.gkoff = 0;
     if (kBank && want_aug) {
       const int64_t j = kSplice ? (int64_t)(fr % (uint32_t)p.sp.B) : b;   // batch-tiled (splice) vs channel-tiled (overlay)
-      int64_t row = p.bank_idx[j];
+      int64_t row = p.bank_idx ? p.bank_idx[j]
+                               : (int64_t)(((uint64_t)philox_word((uint64_t)j, p.bank_subseq, p.sp.seed) * (uint64_t)p.bank_len) >> 32);
       row = row < 0 ? 0 : (row >= p.bank_len ? p.bank_len - 1 : row);
       const uint8_t* g = p.bank + row * 3 * P;
       const int glo = max(r0 - hal, 0), ghi = min(r0 + rows - 1 + hal, H - 1);
@@ -460,7 +462,7 @@ extern "C" int augcl_ring_sample_fused(augcl_ring* r, const augcl_fused_desc* d,
     AUGCL_REQUIRE(d->aug_input == AUGCL_AUG_INPUT_PLAIN || d->aug_input == AUGCL_AUG_INPUT_SHIFTED,
                   "%s: unknown aug_input %d", who, d->aug_input);
     if (pre) {
-      AUGCL_REQUIRE(d->bank && d->bank_idx && d->bank_len > 0, "%s: splice / overlay need bank, bank_idx, bank_len", who);
+      AUGCL_REQUIRE(d->bank && d->bank_len > 0 && d->bank_len <= (1ll << 32), "%s: splice / overlay need bank and bank_len", who);
       if (!aligned(d->bank, 16)) AUGCL_FAIL(AUGCL_ERR_BAD_ALIGN, "%s: bank must be 16-byte aligned", who);
     }
     if (ops & AUGCL_OP_CONV) AUGCL_REQUIRE(d->conv_weights, "%s: CONV needs conv_weights", who);
@@ -495,7 +497,7 @@ extern "C" int augcl_ring_sample_fused(augcl_ring* r, const augcl_fused_desc* d,
   p.o_plain[0] = d->out_obs; p.o_plain[1] = d->out_next;
   p.o_shift[0] = d->out_obs_shift; p.o_shift[1] = d->out_next_shift;
   p.o_aug = d->out_obs_aug;
-  p.bank = d->bank; p.bank_idx = d->bank_idx; p.bank_len = d->bank_len; p.weights = d->conv_weights;
+  p.bank = d->bank; p.bank_idx = d->bank_idx; p.bank_subseq = d->bank_subsequence; p.bank_len = d->bank_len; p.weights = d->conv_weights;
   p.thr = SpliceThr{d->hue_thres, d->sat_thres, d->val_thres, (ops & AUGCL_OP_CS_SPLICE) ? AUGCL_CS_SPLICE : AUGCL_SPLICE};
   int pre = kPreNone;
   if (ops & AUGCL_OP_OVERLAY) pre = kPreOverlay;

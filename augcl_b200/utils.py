@@ -577,9 +577,14 @@ class ReplayBuffer(object):
                     bank = augmentations.get_background_bank()
                     if bank.dtype != torch.uint8 or bank.device != dev or tuple(bank.shape[2:]) != (h, w):
                         raise NotImplementedError("sample_fused: needs a uint8 background bank of the observation size on the ring's device")
-                    rows = augmentations._bank_rows(B, bank.shape[0], bank_idx, dev)
-                    d.bank, d.bank_len, d.bank_idx = bank.data_ptr(), bank.shape[0], rows.data_ptr()
-                    keep += [bank, rows]
+                    d.bank, d.bank_len = bank.data_ptr(), bank.shape[0]
+                    if bank_idx is None:      # drawn inside the kernel: the values augcl_rng_fill_indices would write
+                        d.bank_idx, d.bank_subsequence = None, augmentations._next_subsequence()
+                        keep.append(bank)
+                    else:
+                        rows = augmentations._bank_rows(B, bank.shape[0], bank_idx, dev)
+                        d.bank_idx = rows.data_ptr()
+                        keep += [bank, rows]
                     if pre == "overlay":
                         d.alpha = float(prm.get("alpha", 0.5))
                     else:
@@ -889,7 +894,8 @@ class FastSampler(object):
 class FastFusedSampler(object):
     """``sample_augcl`` / ``sample_svea_aug`` with the per-call Python work taken out (batch <= 256): fixed output tensors,
     a cached ``augcl_fused_desc``, the host indices by value in the launch.  Per step: the bank-row and conv-weight draws
-    (two small Philox launches, the same subsequences ``sample_fused`` would use) and ONE fused sample kernel.
+    (bank rows inside the kernel, conv weights by one small Philox launch; the same subsequences ``sample_fused`` uses) and
+    ONE fused sample kernel.
 
         fs = FastFusedSampler(buf, kind="augcl", data_aug="splice-conv")          # once
         obs_shift, obs_aug, action, reward, next_obs, not_done = fs.sample()      # every update (src/algorithms/augcl.py:69-72)
@@ -935,8 +941,8 @@ class FastFusedSampler(object):
             bank = self._bank = augmentations.get_background_bank()
             if bank.dtype != torch.uint8 or bank.device != dev or tuple(bank.shape[2:]) != (h, w):
                 raise NotImplementedError("FastFusedSampler: needs a uint8 background bank of the observation size on the ring's device")
-            self._rows = torch.empty(B, dtype=torch.int64, device=dev)
-            d.bank, d.bank_len, d.bank_idx = bank.data_ptr(), bank.shape[0], self._rows.data_ptr()
+            self._rows = True                # bank rows are drawn inside the kernel (desc.bank_idx = NULL)
+            d.bank, d.bank_len, d.bank_idx = bank.data_ptr(), bank.shape[0], None
             if pre == "overlay":
                 d.alpha = float(prm.get("alpha", 0.5))
             else:
@@ -969,8 +975,8 @@ class FastFusedSampler(object):
             d.off_src, d.off_obs, d.off_next = L.SRC_HOST, self._off[0].ctypes.data, None
         rc = 0
         if self._rows is not None:
-            rc = self._fill_idx(self._rows.data_ptr(), self.B, 0, d.bank_len, d.seed, augmentations._next_subsequence(), st)
-        if rc == 0 and self._wt is not None:
+            d.bank_subsequence = augmentations._next_subsequence()
+        if self._wt is not None:
             rc = self._fill_normal(self._wt.data_ptr(), self.B * 81, d.seed, augmentations._next_subsequence(), st)
         if rc == 0:
             rc = self._fused(buf._ring, self._dref, st)

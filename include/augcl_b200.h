@@ -228,10 +228,13 @@ typedef struct augcl_fused_desc {
   const uint8_t* bank;        /* device [bank_len,3,H,W] u8 background bank (SPLICE / CS_SPLICE / OVERLAY)       */
   int64_t bank_len;
   const int64_t* bank_idx;    /* device int64[B]: overlay uses bank_idx[s] for every frame of sample s; splice   */
-                              /* uses bank_idx[(s*k+f) mod B] for frame f (the reference's tiling quirks)        */
+                              /* uses bank_idx[(s*k+f) mod B] for frame f (the reference's tiling quirks).       */
+                              /* NULL = drawn in the kernel: the values augcl_rng_fill_indices(out, B, 0,        */
+                              /* bank_len, seed, bank_subsequence) would write (no extra launch)                 */
   const float* conv_weights;  /* device f32 [B,3,3,3,3] (CONV)                                                   */
   float hue_thres, sat_thres, val_thres;   /* splice thresholds (src/augmentations.py:295 / :309)               */
   float alpha;                /* overlay alpha (0.5 in the reference)                                            */
+  uint64_t bank_subsequence;  /* Philox subsequence of the in-kernel bank row draw (bank_idx == NULL)            */
 } augcl_fused_desc;
 
 int augcl_ring_sample_fused(augcl_ring* ring, const augcl_fused_desc* desc, augcl_stream stream);

@@ -237,3 +237,30 @@ def test_fast_splice_mask_equals_float_hsv_on_all_colours(U, A):
             assert torch.equal(slow, ref)
     finally:
         A.set_background_bank(None)
+
+
+@pytest.mark.parametrize("chain,fn", [("overlay", "sample_svea_aug"), ("splice", "sample_augcl")])
+def test_in_kernel_bank_rows_equal_explicit_rows(U, A, chain, fn):
+    """desc.bank_idx == NULL: the background rows are drawn inside the fused kernel and are the values
+    augcl_rng_fill_indices(out, B, 0, bank_len, seed, subsequence) writes (no extra launch)."""
+    from augcl_b200 import _lib as L
+    S, cap, B = 84, 120, 20
+    buf = U.ReplayBuffer((9, S, S), (4,), cap, B)
+    buf.fill_synthetic(seed=9)
+    bank = torch.randint(0, 256, (37, 3, S, S), dtype=torch.uint8, device="cuda")
+    A.set_background_bank(bank)
+    try:
+        idxs = np.random.RandomState(4).randint(0, cap, size=B)
+        off = {"obs": np.random.RandomState(5).randint(0, 9, (B, 2))}
+        A.seed(21)
+        got = getattr(buf, fn)(idxs=idxs, data_aug=chain, offsets=off)
+        # the call reserves subsequences 0..2 for its own draws, then takes the next one (3) for the bank rows
+        rows = torch.empty(B, dtype=torch.int64, device="cuda")
+        L.call("augcl_rng_fill_indices", rows.data_ptr(), B, 0, bank.shape[0], 21, 3, torch.cuda.current_stream().cuda_stream)
+        A.seed(21)
+        want = getattr(buf, fn)(idxs=idxs, data_aug=chain, offsets=off, bank_idx=rows)
+        for a, b in zip(got, want):
+            assert torch.equal(a, b)
+        assert len(set(rows.tolist())) > 5
+    finally:
+        A.set_background_bank(None)
