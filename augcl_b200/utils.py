@@ -31,28 +31,27 @@ except AttributeError:                  # pragma: no cover
 
 
 class LazyFrames(object):
-    """k frames concatenated along channels on demand (src/utils.py:283-322)."""
+    """k frames joined along the channel axis on demand: the pickle-compatible counterpart of the reference's class
+    (src/utils.py:283-322).  The three attribute names are part of the on-disk chunk format (instances are pickled by
+    ReplayBuffer.save and unpickled by the reference, and the other way round), so they are kept; the behaviour is the
+    reference's: ``extremely_lazy`` never caches, otherwise the joined array is cached and the frame list dropped."""
 
     def __init__(self, frames, extremely_lazy=True):
-        self._frames = frames
-        self._extremely_lazy = extremely_lazy
-        self._out = None
+        self._frames, self._extremely_lazy, self._out = frames, extremely_lazy, None
 
-    @property
-    def frames(self):
-        return self._frames
+    frames = property(lambda self: self._frames)
 
     def _force(self):
-        if self._extremely_lazy:
-            return np.concatenate(self._frames, axis=0)
-        if self._out is None:
-            self._out = np.concatenate(self._frames, axis=0)
-            self._frames = None
-        return self._out
+        if self._out is not None:
+            return self._out
+        joined = np.concatenate(self._frames, axis=0)
+        if not self._extremely_lazy:             # cache, and let go of the per-frame references
+            self._out, self._frames = joined, None
+        return joined
 
     def __array__(self, dtype=None, copy=None):
-        out = self._force()
-        return out if dtype is None else out.astype(dtype)
+        arr = self._force()
+        return arr if dtype is None else arr.astype(dtype)
 
     def __len__(self):
         return len(self._frames) if self._extremely_lazy else len(self._force())
@@ -64,7 +63,7 @@ class LazyFrames(object):
         return len(self._frames) if self._extremely_lazy else self._force().shape[0] // 3
 
     def frame(self, i):
-        return self._force()[i * 3:(i + 1) * 3]
+        return self._force()[3 * i:3 * i + 3]
 
 
 # chunks written by save() unpickle under the reference (its class lives in module ``utils``)
