@@ -539,7 +539,11 @@ def main():
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "kernel": "ring_sample_band_kernel<84,84,84,84,0>", "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": B * BYTES_PER_SAMPLE,
-                         "note": "per-launch time = timed region / steps (one launch per step, CUDA events on the launching stream)"},
+                         "note": "per-launch time = timed region / steps (one launch per step, CUDA events on the launching stream)",
+                         "traffic_note": "ncu --set full, one isolated launch (profiles/r01_ncu_ring_sample.csv): 16.2 MB read = the "
+                                         "launch's u8 inputs exactly, 8.3 MB written -- the other 57 MB of its 65 MB f32 output are "
+                                         "still dirty lines in the 126 MB L2 when the kernel ends and reach DRAM during later "
+                                         "launches; no re-reads (traffic below the algorithmic bytes, not above)"},
             "clocks": res["clocks"], "e2e": res["e2e"], "gpu_launches": res["launches"],
         }
         if world == 1 and not args.no_sweep:
