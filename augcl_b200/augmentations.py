@@ -29,7 +29,7 @@ from . import _lib as L
 __all__ = ["random_shift", "random_crop", "random_conv", "random_overlay", "splice", "CS_splice",
            "random_grayscale", "random_flip", "random_rotation", "random_cutout_color",
            "identity", "aug_to_func", "seed", "set_background_bank", "load_dataloader", "create_hsv_mask",
-           "view_as_windows_cuda", "color_jitter"]
+           "view_as_windows_cuda", "color_jitter", "batch_from_obs", "prepare_pad_batch"]
 
 # --------------------------------------------------------------------------------------------
 # process-global state (the reference keeps `dataloader` / `data_iter` globals, :11-12)
@@ -147,10 +147,20 @@ def random_crop(x, size=84, w1=None, h1=None, return_w1_h1=False):
         if w1 is None:
             off = _draw_offsets(n, 0, crop_max, x.device)       # random_(0, crop_max): upper bound exclusive
         else:
-            off = torch.stack([torch.as_tensor(w1).reshape(n), torch.as_tensor(h1).reshape(n)], dim=1)
+            w1t, h1t = torch.as_tensor(w1).reshape(n), torch.as_tensor(h1).reshape(n)
+            for name, t in (("w1", w1t), ("h1", h1t)):
+                # the reference's windows[arange, w1, h1] raises IndexError outside [0, crop_max); host draws are checked
+                # here, device draws are trusted (checking them would cost a device->host sync; the kernel clamps)
+                if not t.is_cuda and t.numel() and (int(t.min()) < -crop_max or int(t.max()) >= crop_max):
+                    raise IndexError(f"random_crop: {name} outside [0, {crop_max}) (window positions of view_as_windows_cuda)")
+            if not w1t.is_cuda:     # negative host indices wrap like torch advanced indexing does
+                w1t, h1t = w1t % crop_max, h1t % crop_max
+            off = torch.stack([w1t, h1t], dim=1)
             off = off.to(device=x.device, dtype=torch.int32).contiguous()
         out = torch.empty((n, c, size, size), dtype=torch.float32, device=x.device)
         L.call("augcl_random_crop", x.data_ptr(), out.data_ptr(), n, c, H, W, int(size), off.data_ptr(), _stream(x))
+        if xin.dtype != torch.float32:       # the reference's window view keeps the input dtype (uint8 from prepare_pad_batch)
+            out = out.to(xin.dtype)
     if return_w1_h1:
         return out, off[:, 0].long(), off[:, 1].long()
     return out
@@ -401,6 +411,25 @@ def color_jitter(imgs, p=1, *, sampled_idxs=None, params=None):
     L.call("augcl_color_jitter", imgs.data_ptr(), b * (c // 3), h, w, sel.data_ptr(), int(sel_np.size), order,
            float(bf or 0.0), float(cf or 0.0), float(sf or 0.0), float(hf or 0.0), enabled, _stream(imgs))
     return imgs.view(-1, 3, h, w).view(b, c, h, w)
+
+
+def batch_from_obs(obs, batch_size=32):
+    """src/augmentations.py:353-362: one observation repeated along a new batch axis (tensor in, tensor out; array in,
+    array out)."""
+    if isinstance(obs, torch.Tensor):
+        return (obs.unsqueeze(0) if obs.dim() == 3 else obs).repeat(batch_size, 1, 1, 1)
+    obs = np.asarray(obs)
+    return np.repeat(obs[None] if obs.ndim == 3 else obs, repeats=batch_size, axis=0)
+
+
+def prepare_pad_batch(obs, next_obs, action, batch_size=32):
+    """src/augmentations.py:365-371 (PAD's test-time batch, called from src/eval.py:36): the observation pair repeated
+    batch_size times on the device, each copy randomly cropped by the random_crop kernel."""
+    dev = torch.device("cuda", torch.cuda.current_device())
+    batch_obs = batch_from_obs(torch.from_numpy(np.asarray(obs)).to(dev), batch_size)
+    batch_next_obs = batch_from_obs(torch.from_numpy(np.asarray(next_obs)).to(dev), batch_size)
+    batch_action = torch.from_numpy(np.asarray(action)).to(dev).unsqueeze(0).repeat(batch_size, 1)
+    return random_crop(batch_obs), random_crop(batch_next_obs), batch_action
 
 
 # same 12 keys as src/augmentations.py:436-449

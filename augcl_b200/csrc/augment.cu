@@ -9,7 +9,6 @@
 // multiply/add below is rounded separately, exactly like the reference's chain of torch elementwise
 // ops, and FMAs appear only where written explicitly (the conv accumulation).
 #include <climits>
-#include <mutex>
 #include "common.cuh"
 #include "pixel.cuh"
 
@@ -809,10 +808,7 @@ int augcl_random_shift(const float* in, float* out, int n, int c, int h, int w, 
   if (h != w) AUGCL_FAIL(AUGCL_ERR_UNSUPPORTED, "augcl_random_shift: BILINEAR (DrQ-v2 grid) requires h == w");
   const size_t bsmem = (size_t)((h + 3) & ~3) * 16 + (size_t)h * w * 4;
   if (g_staging.load() == 0 && w <= 256 && h <= kBilMaxH && bsmem <= (size_t)kBilSmemMax) {
-    static std::once_flag once;
-    std::call_once(once, [] {
-      cudaFuncSetAttribute(shift_bilinear_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBilSmemMax);
-    });
+    if (int rc = ensure_dyn_smem(reinterpret_cast<const void*>(shift_bilinear_smem_kernel), kBilSmemMax)) return rc;
     const int planes = n * c;
     int vec = ((h * w) & 3) == 0 && aligned(in, 16);
     size_t smem = bsmem;
@@ -858,9 +854,7 @@ int augcl_random_conv(const float* in, float* out, int n, int c, int h, int w, c
   const int RS = ((w + 2 + 3) & ~3) + 4;  // padded row stride: multiple of 4 floats, room for the float2 tail
   const size_t smem = (27 * 4 + 3 * (kBand + 2) * (size_t)RS) * sizeof(float);
   if (smem > 200 * 1024) AUGCL_FAIL(AUGCL_ERR_UNSUPPORTED, "augcl_random_conv: width %d too large", w);
-  static std::atomic<bool> configured{false};
-  if (!configured.exchange(true))
-    AUGCL_CUDA(cudaFuncSetAttribute(random_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  if (int rc = ensure_dyn_smem(reinterpret_cast<const void*>(random_conv_kernel), 200 * 1024)) return rc;
   const int vec = ((w & 3) == 0 && aligned(in, 16) && aligned(out, 16)) ? 1 : 0;
   const int64_t work = (int64_t)frames * bands;
   AUGCL_REQUIRE(work < (1ll << 30), "augcl_random_conv: batch too large");
@@ -879,9 +873,7 @@ int augcl_random_conv(const float* in, float* out, int n, int c, int h, int w, c
     if (threads < 96) threads = 96;                              // 81 threads stage the weights
     const size_t smem3 = (128 + (size_t)3 * (R + 2) * w + 4) * sizeof(float);
     if (smem3 <= 100 * 1024) {
-      static std::atomic<bool> configured3{false};
-      if (!configured3.exchange(true))
-        AUGCL_CUDA(cudaFuncSetAttribute(random_conv_part_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+      if (int rc = ensure_dyn_smem(reinterpret_cast<const void*>(random_conv_part_kernel), 100 * 1024)) return rc;
       int per_sm = (int)((228 * 1024) / (smem3 + 1024));
       const int by_regs = 65536 / (72 * threads);
       per_sm = per_sm > by_regs ? by_regs : per_sm;
@@ -897,9 +889,7 @@ int augcl_random_conv(const float* in, float* out, int n, int c, int h, int w, c
     const int RS2 = (w + 8) & ~3;
     const size_t smem2 = (16 + 27 * 4 + 2 * 3 * (kBand + 2) * (size_t)RS2) * sizeof(float);
     if (smem2 <= 200 * 1024) {
-      static std::atomic<bool> configured2{false};
-      if (!configured2.exchange(true))
-        AUGCL_CUDA(cudaFuncSetAttribute(random_conv_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+      if (int rc = ensure_dyn_smem(reinterpret_cast<const void*>(random_conv_tma_kernel), 200 * 1024)) return rc;
       int per_sm = (int)((228 * 1024) / (smem2 + 1024));
       per_sm = per_sm < 1 ? 1 : (per_sm > 7 ? 7 : per_sm);
       const int grid = (int)(work < kNumSMs * per_sm ? work : kNumSMs * per_sm);

@@ -272,9 +272,7 @@ int augcl_color_jitter(float* imgs, int frames, int h, int w, const int32_t* sel
   AUGCL_REQUIRE(sel, "augcl_color_jitter: sel is NULL");
   const size_t smem = (size_t)3 * h * w * sizeof(float);
   if (smem > 200 * 1024) AUGCL_FAIL(AUGCL_ERR_UNSUPPORTED, "augcl_color_jitter: %dx%d frame does not fit shared memory", h, w);
-  static std::atomic<bool> configured{false};
-  if (!configured.exchange(true))
-    AUGCL_CUDA(cudaFuncSetAttribute(color_jitter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  if (int rc = ensure_dyn_smem(reinterpret_cast<const void*>(color_jitter_kernel), 200 * 1024)) return rc;
   color_jitter_kernel<<<n_sel, 256, smem, (cudaStream_t)stream>>>(imgs, sel, h * w, P);
   AUGCL_LAUNCHED();
   return AUGCL_OK;

@@ -16,6 +16,10 @@ namespace augcl {
 extern std::atomic<int64_t> g_launches;
 extern std::atomic<int> g_staging;  // 0 = tma (default), 1 = generic
 void set_error(const std::string& msg);
+// Opt a kernel into `bytes` of dynamic shared memory on the CURRENT device.  The attribute is per (function, device);
+// the (function, device) pairs already configured are remembered, so a repeated call costs one cudaGetDevice.
+// Returns AUGCL_OK or AUGCL_ERR_CUDA (message set).
+int ensure_dyn_smem(const void* func, int bytes);
 
 constexpr int kNumSMs = 148;  // B200: 2 dies x 74 SMs; grids are sized in multiples of this
 

@@ -601,12 +601,9 @@ extern "C" int augcl_ring_sample_fused(augcl_ring* r, const augcl_fused_desc* d,
   }
 
   const FusedKernel kern = pick_kernel(pre, (ops & AUGCL_OP_CONV) != 0, p.normalize != 0, (r->H == 84 && r->W == 84) ? 84 : 0);
-  {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);   // idempotent, ~1 us
-    if (e != cudaSuccess) {
-      if (scratch) cudaFreeAsync(scratch, st);
-      AUGCL_FAIL(AUGCL_ERR_CUDA, "%s: cudaFuncSetAttribute failed: %s", who, cudaGetErrorString(e));
-    }
+  if (int rc = ensure_dyn_smem(reinterpret_cast<const void*>(kern), 200 * 1024)) {   // per (kernel, device), remembered
+    if (scratch) cudaFreeAsync(scratch, st);
+    return rc;
   }
   int per_sm = g_fused_ctas_per_sm.load();
   if (per_sm <= 0) per_sm = ops == 0 ? 7 : 6;

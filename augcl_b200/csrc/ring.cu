@@ -530,7 +530,11 @@ static int sample_impl(const char* who, augcl_ring* r, int idx_src, const int64_
     AUGCL_REQUIRE(pad_or_size > 0 && pad_or_size <= r->H && pad_or_size <= r->W,
                   "%s: crop size %d does not fit %dx%d", who, pad_or_size, r->H, r->W);
     p.Ho = p.Wo = pad_or_size;
-    hi_row = r->H - pad_or_size; hi_col = r->W - pad_or_size;
+    // the reference indexes windows[arange, w1, h1] of view_as_windows_cuda, which has H - size (not H - size + 1)
+    // window positions (src/augmentations.py:416-433): offset H - size itself raises IndexError there
+    hi_row = r->H - pad_or_size - 1; hi_col = r->W - pad_or_size - 1;
+    if (hi_row < 0) hi_row = 0;   // size == H: the single window at 0
+    if (hi_col < 0) hi_col = 0;
     p.off_range = (uint32_t)(r->W - pad_or_size);           // random_(0, crop_max): upper bound exclusive (:404-405)
     if (off_src == AUGCL_SRC_PHILOX)
       AUGCL_REQUIRE(r->H == r->W && p.off_range > 0, "%s: PHILOX crop offsets need a square image larger than the crop", who);
@@ -641,11 +645,8 @@ static int sample_impl(const char* who, augcl_ring* r, int idx_src, const int64_
     if (ctas_per_sm > 8) ctas_per_sm = 8;   // 2048 threads / 256
     const bool pdl = g_sample_pdl.load() != 0;
     auto launch = [&](auto kern, int64_t work_items, auto... args) -> int {
-      static std::atomic<uint64_t> configured{0};   // one bit per device, per kernel instantiation
-      if (!(configured.load() >> (r->device & 63) & 1)) {
-        AUGCL_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem));
-        configured.fetch_or(1ull << (r->device & 63));
-      }
+      // per (kernel address, device): a static flag here would be shared by every instantiation with the same signature
+      if (int rc = ensure_dyn_smem(reinterpret_cast<const void*>(kern), kMaxSmem)) return rc;
       int64_t grid = (int64_t)kNumSMs * ctas_per_sm;
       if (grid > work_items) grid = work_items;
       cudaLaunchConfig_t cfg{};

@@ -22,6 +22,46 @@ extern std::atomic<int> g_conv_part;
 extern std::atomic<int> g_fused_dynamic;
 static thread_local std::string t_error;
 void set_error(const std::string& msg) { t_error = msg; }
+
+// (function, device) pairs whose MaxDynamicSharedMemorySize has been raised.  Lock-free: a slot is claimed by CAS on its
+// function pointer; the per-device bits are set only after cudaFuncSetAttribute succeeded (a racing thread at worst
+// repeats the idempotent call).  More kernels than slots: the attribute is simply set on every call.
+namespace {
+struct SmemSlot {
+  std::atomic<const void*> func{nullptr};
+  std::atomic<uint64_t> bytes_ok[2];   // device bit masks (devices 0..127) configured for >= `bytes`
+  std::atomic<int> bytes{0};
+};
+constexpr int kSmemSlots = 256;
+SmemSlot g_smem_slots[kSmemSlots];
+}  // namespace
+
+int ensure_dyn_smem(const void* func, int bytes) {
+  int dev = 0;
+  AUGCL_CUDA(cudaGetDevice(&dev));
+  SmemSlot* slot = nullptr;
+  for (int i = 0; i < kSmemSlots; ++i) {
+    const void* f = g_smem_slots[i].func.load(std::memory_order_acquire);
+    if (f == nullptr) {
+      const void* expected = nullptr;
+      if (g_smem_slots[i].func.compare_exchange_strong(expected, func)) f = func; else f = expected;
+    }
+    if (f == func) { slot = &g_smem_slots[i]; break; }
+  }
+  const bool tracked = slot != nullptr && dev >= 0 && dev < 128;
+  if (tracked && slot->bytes.load(std::memory_order_acquire) >= bytes &&
+      ((slot->bytes_ok[dev >> 6].load(std::memory_order_acquire) >> (dev & 63)) & 1))
+    return AUGCL_OK;
+  AUGCL_CUDA(cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+  if (tracked) {
+    if (slot->bytes.load() < bytes) {   // a larger request invalidates what other devices were configured for
+      slot->bytes_ok[0].store(0); slot->bytes_ok[1].store(0);
+      slot->bytes.store(bytes, std::memory_order_release);
+    }
+    slot->bytes_ok[dev >> 6].fetch_or(1ull << (dev & 63), std::memory_order_release);
+  }
+  return AUGCL_OK;
+}
 }  // namespace augcl
 
 extern "C" {

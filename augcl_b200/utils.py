@@ -30,6 +30,14 @@ except AttributeError:                  # pragma: no cover
         return torch.cuda.current_stream(index).cuda_stream
 
 
+def k_dev_keep(*srcs):
+    """True when a call made device-side copies of its offset sources (they must outlive the launch)."""
+    for x in srcs:
+        if x is not None and x[2] is not None:
+            return True
+    return False
+
+
 class LazyFrames(object):
     """k frames joined along the channel axis on demand: the pickle-compatible counterpart of the reference's class
     (src/utils.py:283-322).  The three attribute names are part of the on-disk chunk format (instances are pickled by
@@ -138,6 +146,8 @@ class ReplayBuffer(object):
         self._st_start = 0      # ring slot of staged transition 0
         self._st_count = 0
         self._st_event = None   # completion of the last flush (staging must not be overwritten before)
+        self._host_blocks = {}  # batch size -> host block of the draws of one call (_host_block)
+        self._held = collections.deque()   # (event, device-side sources of a call) not yet known to be consumed
 
     def __del__(self):
         ring, self._ring = getattr(self, "_ring", None), None
@@ -260,44 +270,73 @@ class ReplayBuffer(object):
         return np.random.randint(0, self.capacity if self.full else self.idx, size=n)
 
     # ------------------------------------------------------------------ the fused sample kernel
+    def _host_block(self, B):
+        """Per-batch-size host block the HOST draws of a call are copied into (one numpy slice assignment each: dtype
+        conversion, contiguity and list -> array in one step, ~0.4 us) so the C ABI always gets the same three
+        pre-computed pointers.  HOST sources are consumed before the call returns (by value in the launch for B <= 256,
+        a synchronous pageable staging copy otherwise), so the block can be reused by the next call."""
+        blk = self._host_blocks.get(B)
+        if blk is None:
+            idx = np.zeros(B, dtype=np.int64)
+            off = np.zeros((3, B, 2), dtype=np.int32)
+            blk = self._host_blocks[B] = (idx, off, idx.ctypes.data, off[0].ctypes.data, off[1].ctypes.data,
+                                          off[2].ctypes.data)
+        return blk
+
     def _idx_arg(self, idxs):
         """-> (AUGCL_SRC_*, pointer, B, keepalive).  numpy / list / CPU tensor = HOST (the reference's case:
         np.random.randint on the host, src/utils.py:229-232); CUDA tensor = DEVICE."""
         if isinstance(idxs, torch.Tensor):
             t = idxs.reshape(-1)
-            if t.dtype != torch.int64 or not t.is_contiguous():
-                t = t.to(torch.int64).contiguous()
             if t.is_cuda:
-                if t.device != self.device:
-                    t = t.to(self.device)
-                return L.SRC_DEVICE, t.data_ptr(), t.numel(), t
-            return L.SRC_HOST, t.data_ptr(), t.numel(), t
-        a = np.ascontiguousarray(idxs, dtype=np.int64).reshape(-1)
-        return L.SRC_HOST, a.ctypes.data, a.size, a
+                made = t.dtype != torch.int64 or not t.is_contiguous() or t.device != self.device
+                if made:        # a converted copy must outlive the launch (_hold); the caller's own tensor is the caller's
+                    t = t.to(device=self.device, dtype=torch.int64).contiguous()
+                return L.SRC_DEVICE, t.data_ptr(), t.numel(), (t if made else None)
+            idxs = t.numpy()
+        elif type(idxs) is not np.ndarray:
+            idxs = np.asarray(idxs)
+        if idxs.ndim != 1:
+            idxs = idxs.reshape(-1)
+        B = idxs.shape[0]
+        if B == 0:
+            raise L.AugclError("augcl_ring_sample_ex", -1, "B must be positive (got 0)")
+        if idxs.dtype.kind not in "iu":
+            raise TypeError(f"ReplayBuffer: indices must be integers, got {idxs.dtype}")
+        blk = self._host_block(B)
+        blk[0][:] = idxs
+        return L.SRC_HOST, blk[2], B, None
 
-    def _off_arg(self, v, B):
-        """-> None | (AUGCL_SRC_*, pointer, keepalive) for one (B,2) offsets array."""
+    def _off_arg(self, v, B, slot=0):
+        """-> None | (AUGCL_SRC_*, pointer, keepalive) for one (B,2) offsets array (slot 0 obs, 1 next_obs, 2 pos)."""
         if v is None:
             return None
-        if isinstance(v, torch.Tensor) and v.is_cuda:
-            t = v.to(device=self.device, dtype=torch.int32).contiguous()
-            if tuple(t.shape) != (B, 2):
-                raise ValueError(f"ReplayBuffer: offsets must have shape ({B}, 2), got {tuple(t.shape)}")
-            return L.SRC_DEVICE, t.data_ptr(), t
-        a = v.numpy() if isinstance(v, torch.Tensor) else np.asarray(v)
-        a = np.ascontiguousarray(a, dtype=np.int32)
-        if a.shape != (B, 2):
-            raise ValueError(f"ReplayBuffer: offsets must have shape ({B}, 2), got {a.shape}")
-        return L.SRC_HOST, a.ctypes.data, a
+        if isinstance(v, torch.Tensor):
+            if v.is_cuda:
+                if tuple(v.shape) != (B, 2):
+                    raise ValueError(f"ReplayBuffer: offsets must have shape ({B}, 2), got {tuple(v.shape)}")
+                made = v.dtype != torch.int32 or not v.is_contiguous() or v.device != self.device
+                t = v.to(device=self.device, dtype=torch.int32).contiguous() if made else v
+                return L.SRC_DEVICE, t.data_ptr(), (t if made else None)
+            v = v.numpy()
+        elif type(v) is not np.ndarray:
+            v = np.asarray(v)
+        if v.shape != (B, 2):
+            raise ValueError(f"ReplayBuffer: offsets must have shape ({B}, 2), got {v.shape}")
+        blk = self._host_block(B)
+        blk[1][slot] = v
+        return L.SRC_HOST, blk[3 + slot], None
 
     def _sample(self, idxs=None, *, n=None, obs=True, next_obs=True, scalars=True, aug=L.AUG_NONE, off_obs=None,
-                off_next=None, pad_or_size=0, normalize=False, device_indices=False, pos=False, off_pos=None):
+                off_next=None, pad_or_size=0, normalize=False, device_indices=False, pos=False, off_pos=None, rng=True):
         """One augcl_ring_sample_ex launch.  Returns (obs, actions, rewards, next_obs, not_dones); entries
         that were not requested are None.  Host indices / offsets travel inside the launch (no extra H2D);
-        offsets that are not supplied are drawn inside the kernel (Philox stream of augmentations.seed())."""
-        self._flush()
-        sub = augmentations._reserve_subsequences(4 if pos else 3)
-        if device_indices and idxs is None:
+        offsets that are not supplied are drawn inside the kernel (Philox stream of augmentations.seed()).
+        rng=False: the call draws nothing and leaves the Philox call counter alone (internal reads: save())."""
+        if self._st_count:
+            self._flush()
+        sub = augmentations._reserve_subsequences(4 if pos else 3) if rng else 0
+        if idxs is None and device_indices:
             B = self.batch_size if n is None else int(n)
             i_src, i_ptr, keep_i = L.SRC_PHILOX, None, None
             idx_hi = self.capacity if self.full else self.idx
@@ -306,66 +345,89 @@ class ReplayBuffer(object):
                 idxs = self._get_idxs(n)
             i_src, i_ptr, B, keep_i = self._idx_arg(idxs)
             idx_hi = 0
-        oo, on = self._off_arg(off_obs, B), self._off_arg(off_next, B)
-        op = self._off_arg(off_pos, B) if pos else None
-        need_draw = aug in (L.AUG_SHIFT, L.AUG_CROP) and ((obs and oo is None) or (next_obs and on is None) or (pos and op is None))
-        need_draw = need_draw or (aug == L.AUG_SHIFT_OBS and obs and oo is None)
-        kinds = {x[0] for x in (oo, on, op) if x is not None}
-        if need_draw or len(kinds) > 1:
-            # PHILOX draws for the missing tensors; supplied arrays must then be DEVICE arrays
-            def to_dev(x):
-                if x is None or x[0] == L.SRC_DEVICE:
-                    return x
-                t = torch.from_numpy(x[2]).to(self.device, non_blocking=False)
-                return L.SRC_DEVICE, t.data_ptr(), t
-            oo, on, op = to_dev(oo), to_dev(on), to_dev(op)
-            o_src = L.SRC_PHILOX if need_draw else L.SRC_DEVICE
+        oo, on = self._off_arg(off_obs, B, 0), self._off_arg(off_next, B, 1)
+        op = self._off_arg(off_pos, B, 2) if pos else None
+        if aug == L.AUG_NONE:
+            o_src = L.SRC_DEVICE
         else:
-            o_src = kinds.pop() if kinds else L.SRC_DEVICE
+            if aug == L.AUG_SHIFT_OBS:
+                need_draw = obs and oo is None
+            else:
+                need_draw = (obs and oo is None) or (next_obs and on is None) or (pos and op is None)
+            k_host = k_dev = False
+            for x in (oo, on, op):
+                if x is not None:
+                    if x[0] == L.SRC_HOST:
+                        k_host = True
+                    else:
+                        k_dev = True
+            if k_host and (need_draw or k_dev):
+                # PHILOX draws for the missing tensors (or a mix of sources): host arrays become DEVICE arrays
+                def to_dev(x, slot):
+                    if x is None or x[0] == L.SRC_DEVICE:
+                        return x
+                    t = torch.from_numpy(self._host_block(B)[1][slot]).to(self.device, non_blocking=False)
+                    return L.SRC_DEVICE, t.data_ptr(), t
+                oo, on, op = to_dev(oo, 0), to_dev(on, 1), to_dev(op, 2)
+                k_host = False
+            o_src = L.SRC_PHILOX if need_draw else (L.SRC_HOST if k_host else L.SRC_DEVICE)
         c, h, w = self.obs_shape
         ho, wo = (pad_or_size, pad_or_size) if aug == L.AUG_CROP else (h, w)
+        # torch.empty(device=) and the raw-stream query name the ring's device explicitly and the library switches to the
+        # ring's device for the call (DeviceGuard), so no device context manager is needed here
         dev = self.device
-        guard = None
-        if torch.cuda.current_device() != self._dev_index:    # rare: only then pay for a device context switch
-            guard = torch.cuda.device(dev)
-            guard.__enter__()
-        try:
-            o = no = act = rew = nd = None
-            po = pn = pa = pr = pd = None
-            if obs and next_obs:
-                o, no = torch.empty((2, B, c, ho, wo), dtype=torch.float32, device=dev).unbind(0)
-                po = o.data_ptr()
-                pn = po + 4 * B * c * ho * wo
-            elif obs:
-                o = torch.empty((B, c, ho, wo), dtype=torch.float32, device=dev)
-                po = o.data_ptr()
-            elif next_obs:
-                no = torch.empty((B, c, ho, wo), dtype=torch.float32, device=dev)
-                pn = no.data_ptr()
-            if scalars:
-                act = torch.empty((B,) + self.actions.shape[1:], dtype=torch.float32, device=dev)
-                rew, nd = torch.empty((2, B, 1), dtype=torch.float32, device=dev).unbind(0)
-                pa, pr = act.data_ptr(), rew.data_ptr()
-                pd = pr + 4 * B
-            if pos:     # sample_curl: a third, independently cropped view of obs from the same launch
-                ps = torch.empty((B, c, ho, wo), dtype=torch.float32, device=dev)
-                rc = L.lib().augcl_ring_sample_curl(
-                    self._ring, i_src, i_ptr, idx_hi, B, po, pn, ps.data_ptr(), pa, pr, pd, o_src,
-                    None if oo is None else oo[1], None if on is None else on[1], None if op is None else op[1],
-                    int(pad_or_size), 1 if normalize else 0, augmentations._seed, sub, _raw_stream(self._dev_index))
-                self._pos = ps
-            else:
-                rc = self._fn_sample(self._ring, i_src, i_ptr, idx_hi, B, po, pn, pa, pr, pd, aug, o_src,
-                                     None if oo is None else oo[1], None if on is None else on[1], int(pad_or_size),
-                                     1 if normalize else 0, augmentations._seed, sub, _raw_stream(self._dev_index))
-            if rc != 0:
-                raise L.AugclError("augcl_ring_sample_curl" if pos else "augcl_ring_sample_ex", rc,
-                                   L.lib().augcl_last_error().decode(errors="replace"))
-        finally:
-            if guard is not None:
-                guard.__exit__(None, None, None)
-        self._keep = (keep_i, oo, on, op)   # page-locked host sources of a staged (B > 256) call must outlive the copy
+        o = no = act = rew = nd = None
+        po = pn = pa = pr = pd = None
+        if obs and next_obs:
+            o, no = torch.empty((2, B, c, ho, wo), dtype=torch.float32, device=dev).unbind(0)
+            po = o.data_ptr()
+            pn = po + 4 * B * c * ho * wo
+        elif obs:
+            o = torch.empty((B, c, ho, wo), dtype=torch.float32, device=dev)
+            po = o.data_ptr()
+        elif next_obs:
+            no = torch.empty((B, c, ho, wo), dtype=torch.float32, device=dev)
+            pn = no.data_ptr()
+        if scalars:
+            act = torch.empty(self._act_shape(B), dtype=torch.float32, device=dev)
+            rew, nd = torch.empty((2, B, 1), dtype=torch.float32, device=dev).unbind(0)
+            pa, pr = act.data_ptr(), rew.data_ptr()
+            pd = pr + 4 * B
+        if pos:     # sample_curl: a third, independently cropped view of obs from the same launch
+            ps = torch.empty((B, c, ho, wo), dtype=torch.float32, device=dev)
+            rc = L.lib().augcl_ring_sample_curl(
+                self._ring, i_src, i_ptr, idx_hi, B, po, pn, ps.data_ptr(), pa, pr, pd, o_src,
+                None if oo is None else oo[1], None if on is None else on[1], None if op is None else op[1],
+                int(pad_or_size), 1 if normalize else 0, augmentations._seed, sub, _raw_stream(self._dev_index))
+            self._pos = ps
+        else:
+            rc = self._fn_sample(self._ring, i_src, i_ptr, idx_hi, B, po, pn, pa, pr, pd, aug, o_src,
+                                 None if oo is None else oo[1], None if on is None else on[1], int(pad_or_size),
+                                 1 if normalize else 0, augmentations._seed, sub, _raw_stream(self._dev_index))
+        if rc != 0:
+            raise L.AugclError("augcl_ring_sample_curl" if pos else "augcl_ring_sample_ex", rc,
+                               L.lib().augcl_last_error().decode(errors="replace"))
+        if keep_i is not None or k_dev_keep(oo, on, op):
+            self._hold((keep_i, oo, on, op))
         return o, act, rew, no, nd
+
+    def _act_shape(self, B):
+        return (B,) + self.actions.shape[1:]
+
+    def _hold(self, keep):
+        """Device-side sources made for one call (converted offsets, a moved index tensor) stay referenced until the
+        kernel that reads them has run: a short FIFO of (event, objects), released as the events complete.  (torch's
+        caching allocator is stream-ordered, so dropping them early would be safe on the launching stream; the FIFO
+        also covers callers that hand over tensors produced on another stream.)"""
+        if torch.cuda.is_current_stream_capturing():
+            self._held.append((None, keep))          # kept for the buffer's lifetime: a graph replays the launch
+            return
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.device))
+        q = self._held
+        q.append((ev, keep))
+        while len(q) > 1 and q[0][0] is not None and q[0][0].query():
+            q.popleft()
 
     # ------------------------------------------------------------------ reference API
     def tensor_buffer_samples(self, idxs):
@@ -477,7 +539,9 @@ class ReplayBuffer(object):
             L.call("augcl_ring_sample_views", self._ring, i_src, i_ptr, idx_hi, B, nv, src, outs, offp, act.data_ptr(),
                    rew.data_ptr(), nd.data_ptr(), L.AUG_SHIFT, L.SRC_PHILOX, int(pad), 0, augmentations._seed, sub,
                    _raw_stream(self._dev_index))
-        self._keep = keep
+        # `keep` holds tensors made on the launching stream: torch's allocator is stream-ordered, so letting them go here
+        # is safe (their memory is not reused before the kernel that reads them has run)
+        del keep
         return views[:k], act, rew, views[k:], nd
 
     def sample_svea(self, n=None, pad=4, *, idxs=None, offsets=None, device_indices=False):
@@ -530,17 +594,17 @@ class ReplayBuffer(object):
                 idxs = self._get_idxs(n)
             i_src, i_ptr, B, keep_i = self._idx_arg(idxs)
             idx_hi = 0
-        oo, on = self._off_arg(offsets.get("obs"), B), self._off_arg(offsets.get("next_obs"), B)
+        oo, on = self._off_arg(offsets.get("obs"), B, 0), self._off_arg(offsets.get("next_obs"), B, 1)
         shift_obs = "obs_shift" in want or ("obs_aug" in want and aug_input == "shift")
         need_draw = (shift_obs and oo is None) or ("next_obs_shift" in want and on is None)
         kinds = {x[0] for x in (oo, on) if x is not None}
         if need_draw or len(kinds) > 1:
-            def to_dev(x):
+            def to_dev(x, slot):
                 if x is None or x[0] == L.SRC_DEVICE:
                     return x
-                t = torch.from_numpy(x[2]).to(self.device)
+                t = torch.from_numpy(self._host_block(B)[1][slot]).to(self.device)
                 return L.SRC_DEVICE, t.data_ptr(), t
-            oo, on = to_dev(oo), to_dev(on)
+            oo, on = to_dev(oo, 0), to_dev(on, 1)
             o_src = L.SRC_PHILOX if need_draw else L.SRC_DEVICE
         else:
             o_src = kinds.pop() if kinds else L.SRC_DEVICE
@@ -608,7 +672,7 @@ class ReplayBuffer(object):
                 if rc == -5:
                     raise NotImplementedError(e)
                 raise L.AugclError("augcl_ring_sample_fused", rc, e)
-        self._keep = keep
+        del keep        # made on the launching stream: the stream-ordered allocator keeps them valid for the kernel
         out.update(action=act, reward=rew, not_done=nd)
         return out
 
@@ -638,7 +702,7 @@ class ReplayBuffer(object):
         if self.dedup:      # no stacks in HBM to copy out: gather them with the sample kernel (exact u8 -> f32 -> u8)
             for s0 in range(0, n, 256):
                 m = min(256, n - s0)
-                o, _, _, no, _ = self._sample(np.arange(start + s0, start + s0 + m), scalars=False)
+                o, _, _, no, _ = self._sample(np.arange(start + s0, start + s0 + m), scalars=False, rng=False)
                 obs[s0:s0 + m] = o.to(torch.uint8).cpu().numpy()
                 nxt[s0:s0 + m] = no.to(torch.uint8).cpu().numpy()
             return obs, nxt

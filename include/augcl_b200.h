@@ -130,8 +130,10 @@ int augcl_ring_fill_synthetic(augcl_ring* ring, int64_t count, uint64_t seed, au
  *   out_act [B,action_dim], out_rew [B], out_nd [B]  device f32, each may be NULL
  *   off_obs / off_next   device int32[B,2] = (row, col) offsets.  SHIFT: in [0, 2*pad], the crop
  *              origin inside the replicate-padded image (pad,pad == identity); NULL = identity for
- *              that tensor.  CROP: (w1, h1) of the reference (w1 indexes rows), in [0, H-size] x
- *              [0, W-size]; must not be NULL for a tensor that is written.
+ *              that tensor.  CROP: (w1, h1) of the reference (w1 indexes rows), in [0, H-size) x
+ *              [0, W-size) -- the reference's window view has H-size positions, the last geometric one is excluded
+ *              (src/augmentations.py:416-433); HOST offsets outside are AUGCL_ERR_BAD_ARG, DEVICE offsets are trusted
+ *              (clamped per pixel for memory safety); must not be NULL for a tensor that is written.
  *   pad_or_size  pad (SHIFT) or size (CROP); ignored for NONE. */
 int augcl_ring_sample(augcl_ring* ring, const int64_t* idx, int B, float* out_obs, float* out_next,
                       float* out_act, float* out_rew, float* out_nd, int aug_mode,

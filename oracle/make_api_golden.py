@@ -18,7 +18,7 @@ from oracle import ref_harness as R  # noqa: E402
 
 AUG_FUNCS = ["random_shift", "random_crop", "random_conv", "random_overlay", "splice", "CS_splice", "random_grayscale",
              "random_flip", "random_rotation", "random_cutout_color", "color_jitter", "identity", "load_dataloader",
-             "view_as_windows_cuda", "create_hsv_mask"]
+             "view_as_windows_cuda", "create_hsv_mask", "batch_from_obs", "prepare_pad_batch"]
 RB_METHODS = ["__init__", "add", "sample", "sample_obs", "sample_curl", "sample_drq", "save", "requeue_save", "load",
               "tensor_buffer_samples", "_get_idxs"]
 
