@@ -3,8 +3,10 @@
 Runs the reference's own Python code (GT-RIPL/AugCL, mounted read-only at
 /root/reference) on CPU so that (1) the restatement in ``augcl_oracle.py`` can
 be pinned against it and (2) golden vectors can be generated for
-``tests/golden/`` (``make_golden.py``).  The reference cannot travel to the GPU
-box, so nothing here is used by ``-m gpu`` tests, ``smoke()`` or ``bench.py``.
+``tests/golden/`` (``make_golden.py``).  /root/reference does not exist on the GPU
+box; there the harness falls back to ``oracle/_ref/`` — the same modules compiled to
+bytecode by the committed recipe ``oracle/build_ref.py`` (a built artefact that ships
+with the snapshot like the ``.so``; nothing reads /root/reference at run time).
 
 The reference does not import in this container as-is:
   * ``src/augmentations.py:6`` imports kornia (absent, unpinned) -> stub module;
@@ -27,11 +29,24 @@ import types
 import numpy as np
 import torch
 
-REF_SRC = "/root/reference/src"
+REF_LIVE = "/root/reference/src"                                             # build container only
+REF_BUILT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")  # oracle/build_ref.py output (ships to the GPU box)
+
+
+def ref_dir():
+    """Directory the reference's modules are imported from: the live tree when it is mounted, else the compiled copy."""
+    if os.path.isfile(os.path.join(REF_LIVE, "augmentations.py")):
+        return REF_LIVE
+    if os.path.isfile(os.path.join(REF_BUILT, "augmentations.pyc")):
+        return REF_BUILT
+    return None
+
+
+REF_SRC = ref_dir() or REF_LIVE
 
 
 def available() -> bool:
-    return os.path.isfile(os.path.join(REF_SRC, "augmentations.py"))
+    return ref_dir() is not None
 
 
 # --------------------------------------------------------------------------
@@ -123,16 +138,17 @@ def load_reference():
     global _ref_mods
     if _ref_mods is not None:
         return _ref_mods
-    if not available():
-        raise RuntimeError("/root/reference is not present on this machine")
+    src = ref_dir()
+    if src is None:
+        raise RuntimeError("neither /root/reference nor oracle/_ref (python oracle/build_ref.py) is present on this machine")
     _install_kornia_stub()
     saved = {k: sys.modules.pop(k) for k in ("augmentations", "utils") if k in sys.modules}
-    sys.path.insert(0, REF_SRC)
+    sys.path.insert(0, src)
     try:
         import augmentations as ref_aug  # noqa: E402
         import utils as ref_utils  # noqa: E402
     finally:
-        sys.path.remove(REF_SRC)
+        sys.path.remove(src)
         # keep the reference modules out of the global namespace
         sys.modules.pop("augmentations", None)
         sys.modules.pop("utils", None)
