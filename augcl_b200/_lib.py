@@ -45,6 +45,7 @@ SIGNATURES = {
     "augcl_last_error": (C.c_char_p, []),
     "augcl_launch_count": (_i64, []),
     "augcl_set_option": (_i, [C.c_char_p, C.c_char_p]),
+    "augcl_stream_delay": (_i, [_u64, _p]),
     "augcl_ring_create": (_i, [C.POINTER(_p), _i, _i64, _i, _i, _i, _i, _i]),
     "augcl_ring_create_dedup": (_i, [C.POINTER(_p), _i, _i64, _i, _i, _i, _i, _i, _i64]),
     "augcl_ring_put_frames": (_i, [_p, _i64, _i64, _p, _p]),

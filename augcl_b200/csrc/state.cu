@@ -64,7 +64,28 @@ int ensure_dyn_smem(const void* func, int bytes) {
 }
 }  // namespace augcl
 
+namespace augcl {
+// One thread spins on %globaltimer for `ns` nanoseconds (bounded by the host wrapper): occupies the stream so that the
+// launches enqueued behind it are all in the queue when it ends (bench.py: the timed region then measures the GPU, not
+// the host's launch cadence).  Waits on nothing but the clock.
+__global__ void stream_delay_kernel(unsigned long long ns) {
+  unsigned long long t0, t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  do {
+    __nanosleep(1000);
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  } while (t - t0 < ns);
+}
+}  // namespace augcl
+
 extern "C" {
+
+int augcl_stream_delay(uint64_t nanoseconds, augcl_stream stream) {
+  AUGCL_REQUIRE(nanoseconds <= 50ull * 1000 * 1000, "augcl_stream_delay: at most 50 ms");
+  augcl::stream_delay_kernel<<<1, 1, 0, (cudaStream_t)stream>>>((unsigned long long)nanoseconds);
+  AUGCL_CUDA(cudaGetLastError());
+  return AUGCL_OK;
+}
 
 const char* augcl_version(void) { return "augcl_b200 0.1.0 (sm_100a)"; }
 const char* augcl_last_error(void) { return augcl::t_error.c_str(); }

@@ -44,6 +44,45 @@ def plan(capacity_per_gpu: int, batch_per_gpu: int, base_seed: int = 0, rank=Non
                      draw_seed=base_seed + rank, global_batch=int(batch_per_gpu) * world)
 
 
+def core_slice(local_rank: int, local_world: int, cores) -> list:
+    """The cores rank `local_rank` of `local_world` co-located ranks should run on: an equal, contiguous slice of the
+    allowed set (at least one core each; with more ranks than cores they wrap).  Each rank drives its own launch loop;
+    without pinning the scheduler migrates them onto each other and the slowest rank's launch cadence shows up as lost
+    scaling although no byte crosses between GPUs."""
+    cores = sorted(cores)
+    n = len(cores)
+    if n == 0 or local_world <= 0:
+        return []
+    per = max(1, n // local_world)
+    lo = (local_rank * per) % n
+    return cores[lo:lo + per] or [cores[lo]]
+
+
+def pin_to_cores(local_rank=None, local_world=None):
+    """Pin this process to its core slice (Linux).  Returns the cores, or None when affinity is not available."""
+    if not hasattr(os, "sched_setaffinity"):
+        return None
+    lr = int(os.environ.get("LOCAL_RANK", "0")) if local_rank is None else local_rank
+    lw = int(os.environ.get("LOCAL_WORLD_SIZE", os.environ.get("WORLD_SIZE", "1"))) if local_world is None else local_world
+    try:
+        cores = core_slice(lr, lw, os.sched_getaffinity(0))
+        if cores:
+            os.sched_setaffinity(0, cores)
+        return cores
+    except OSError:
+        return None
+
+
+def gather_over_ranks(value: float, device=None) -> list:
+    """Every rank's host scalar, in rank order (identity without a process group).  Off the data path."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+        return [float(value)]
+    t = torch.tensor([float(value)], dtype=torch.float64, device=device if device is not None else "cpu")
+    out = [torch.empty_like(t) for _ in range(dist.get_world_size())]
+    dist.all_gather(out, t)
+    return [float(x.item()) for x in out]
+
+
 def barrier():
     if dist.is_available() and dist.is_initialized():
         dist.barrier()

@@ -46,6 +46,7 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-sweep", action="store_true")
+    ap.add_argument("--no-gpu-reference", action="store_true", help="skip the reference-on-the-same-GPU leg")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU budget of the cpu_baseline leg")
     return ap.parse_args()
 
@@ -63,14 +64,14 @@ def config_dict(args, n_gpus):
 # CPU legs: the reference's algorithm for one step, on the host cores.  The only place bench.py
 # touches oracle/ (as the measured *baseline*, never as the product path).
 # ------------------------------------------------------------------------------------------------
-def cpu_step_factory(batch, cap_host=20_000, seed=0):
-    """Returns (step_fn, kind, sample_description).  Uses the reference's own code when
-    /root/reference is mounted (build container), else the oracle port (GPU box)."""
+def cpu_step_factory(batch, cap_host=CAP, seed=0):
+    """Returns (step_fn, kind, sample_description).  Uses the reference's own code (the live tree in the build
+    container, oracle/_ref -- compiled by oracle/build_ref.py -- on the GPU box), else the oracle port."""
     import torch
     from oracle import augcl_oracle as O
     from oracle import ref_harness as R
     rng = np.random.RandomState(seed)
-    frames = rng.randint(0, 256, (cap_host + K_FRAMES, 3, S, S), dtype=np.uint8)
+    frames = np.random.default_rng(seed).integers(0, 256, (cap_host + K_FRAMES, 3, S, S), dtype=np.uint8)   # 2.1 GB at 100k
     if R.available():
         kind = "reference"
         buf = R.ref_replay_buffer((C, S, S), (A_DIM,), cap_host, batch)
@@ -97,6 +98,23 @@ def cpu_step_factory(batch, cap_host=20_000, seed=0):
     return step, kind, desc
 
 
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def cpu_model():
+    try:
+        for ln in open("/proc/cpuinfo"):
+            if ln.startswith("model name"):
+                return ln.split(":", 1)[1].strip()
+    except OSError:
+        pass
+    return "unknown"
+
+
 def time_cpu(step, budget_s, min_steps=3):
     import torch
     step()                                   # warm-up
@@ -114,10 +132,10 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    cores = os.cpu_count() or 1
+    cores = host_cores()
     torch.set_num_threads(cores)
     step, kind, desc = cpu_step_factory(args.batch)
-    for _ in range(max(1, min(args.warmup, 3))):
+    for _ in range(max(1, min(args.warmup, 5))):
         step()
     steps = max(1, min(args.steps, 300))     # bounded: ~20 ms per step on a server core
     t0 = time.perf_counter()
@@ -127,10 +145,10 @@ def run_reference(args):
     value = steps * args.batch / el
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
-        "warmup": min(args.warmup, 3), "ms_per_step": 1e3 * el / steps, "higher_is_better": True, "scaling": "weak",
+        "warmup": max(1, min(args.warmup, 5)), "ms_per_step": 1e3 * el / steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8->f32", "data": "synthetic", "config": config_dict(args, args.gpus),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind,
-                         "sample": f"{steps} steps: " + desc},
+                         "sample": f"{steps} steps: " + desc, "cpu_model": cpu_model()},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }))
@@ -140,12 +158,16 @@ def run_reference(args):
 # clocks during the timed region (NVML; same fields as the recipe's nvidia-smi line)
 # ------------------------------------------------------------------------------------------------
 class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons for the whole run.  It is started BEFORE the warm-up steps (thread start,
+    `import pynvml`, nvmlInit and the first samples all happen outside any timed region) and keeps sampling through the
+    e2e legs; window(t0, t1) summarises the samples taken between two perf_counter stamps."""
     REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
 
-    def __init__(self, index, period_s=0.005):
+    def __init__(self, index, period_s=0.002):
         super().__init__(daemon=True)
         self.index, self.period, self.stop_flag = index, period_s, threading.Event()
-        self.sm, self.reasons, self.max_mhz, self.err = [], set(), None, None
+        self.samples, self.max_mhz, self.err = [], None, None      # (t, sm_mhz, reason bits)
+        self.ready = threading.Event()
 
     def run(self):
         try:
@@ -154,24 +176,32 @@ class ClockSampler(threading.Thread):
             h = nv.nvmlDeviceGetHandleByIndex(self.index)
             self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
             while not self.stop_flag.is_set():
-                self.sm.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
-                bits = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
-                for bit, name in self.REASONS.items():
-                    if bits & bit:
-                        self.reasons.add(name)
+                self.samples.append((time.perf_counter(), nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM),
+                                     nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)))
+                self.ready.set()
                 time.sleep(self.period)
         except Exception as e:  # reported, never fatal
             self.err = repr(e)
+            self.ready.set()
 
-    def summary(self):
-        self.stop_flag.set()
-        self.join(timeout=2)
-        sm = sorted(self.sm)
-        out = {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+    def window(self, t0, t1, pad_s=0.004):
+        """Samples in [t0 - pad, t1 + pad] (a 0.3 ms timed region falls between two samples: its neighbours count)."""
+        rows = [r for r in list(self.samples) if t0 - pad_s <= r[0] <= t1 + pad_s]
+        sm = sorted(r[1] for r in rows)
+        reasons = set()
+        for r in rows:
+            for bit, name in self.REASONS.items():
+                if r[2] & bit:
+                    reasons.add(name)
+        out = {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(reasons),
                "samples": len(sm)}
         if self.err:
             out["error"] = self.err
         return out
+
+    def stop(self):
+        self.stop_flag.set()
+        self.join(timeout=2)
 
 
 def physical_gpu_index(local_rank):
@@ -188,7 +218,6 @@ def physical_gpu_index(local_rank):
 # our arm
 # ------------------------------------------------------------------------------------------------
 def run_ours(args):
-    import ctypes
     import torch
     import torch.distributed as dist
     import __graft_entry__ as entry
@@ -201,27 +230,33 @@ def run_ours(args):
     world, rank, local = plan.world, plan.rank, plan.local_rank
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; augcl_b200 has no CPU path (use --impl reference for the CPU arm)")
+    cores = shard.pin_to_cores()          # each rank's launch loop on its own cores (torchrun does not pin)
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
+    # clock sampler first: thread start, NVML init and the first samples are over long before anything is timed
+    sampler = ClockSampler(physical_gpu_index(local))
+    sampler.start()
     B, K, W = args.batch, args.steps, max(args.warmup, 3)
+    R = 5 if K <= 2000 else 1             # timed blocks of K steps: block 0 is the number of record, the others show its spread
 
     # ---- one ring shard per rank, synthetic frames, per-rank seed
     buf = U.ReplayBuffer((C, S, S), (A_DIM,), CAP, B, device=dev)
     buf.fill_synthetic(seed=plan.ring_seed)
     g = torch.Generator(device="cpu").manual_seed(plan.draw_seed)
     n_sets = 8
-    outs = [(torch.empty((B, C, S, S), dtype=torch.float32, device=dev), torch.empty((B, C, S, S), dtype=torch.float32, device=dev),
-             torch.empty((B, A_DIM), device=dev), torch.empty((B, 1), device=dev), torch.empty((B, 1), device=dev))
-            for _ in range(n_sets)]
-    T = K + W
+    outs = [(torch.zeros((B, C, S, S), dtype=torch.float32, device=dev), torch.zeros((B, C, S, S), dtype=torch.float32, device=dev),
+             torch.zeros((B, A_DIM), device=dev), torch.zeros((B, 1), device=dev), torch.zeros((B, 1), device=dev))
+            for _ in range(n_sets)]       # zeros, not empty: every page of the 8 output sets is touched before warm-up
+    T = W + R * K
     idx = torch.randint(0, CAP, (T, B), generator=g).to(dev)                       # resident before the timed region
     off = torch.randint(0, 2 * PAD + 1, (T, 2, B, 2), generator=g, dtype=torch.int32).to(dev)
     stream = torch.cuda.current_stream(dev)
     sp = stream.cuda_stream
     ring = buf._ring
-    fn = L.lib().augcl_ring_sample
+    lib = L.lib()
+    fn, delay = lib.augcl_ring_sample, lib.augcl_stream_delay
     idx_p, off_p = idx.data_ptr(), off.data_ptr()
     ptrs = [tuple(t.data_ptr() for t in o) for o in outs]
 
@@ -230,7 +265,7 @@ def run_ours(args):
         rc = fn(ring, idx_p + t * B * 8, B, o[0], o[1], o[2], o[3], o[4], L.AUG_SHIFT, off_p + t * 16 * B,
                 off_p + t * 16 * B + 8 * B, PAD, 0, sp)
         if rc:
-            raise RuntimeError(L.lib().augcl_last_error().decode())
+            raise RuntimeError(lib.augcl_last_error().decode())
 
     def barrier():
         if world > 1:
@@ -240,81 +275,103 @@ def run_ours(args):
     for t in range(W):
         step(t)
     barrier()
-    sampler = ClockSampler(physical_gpu_index(local))
-    sampler.start()
+    sampler.ready.wait(5.0)
+    # A one-thread delay kernel (augcl_stream_delay) occupies the stream while the K launches are enqueued behind it, so
+    # the events bracket K back-to-back launches on the GPU and not the host's launch cadence (at --steps 20 the region is
+    # 0.3 ms: one descheduled launch loop would otherwise be the whole measurement).
+    delay_ns = min(45_000_000, 200_000 + 8_000 * min(K, 4096))
+    blocks, enq = [], []
     l0 = L.launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record(stream)
-    for t in range(W, T):
-        step(t)
-    e1.record(stream)
-    barrier()
-    launches = L.launch_count() - l0
-    clocks = sampler.summary()
-    ms = e0.elapsed_time(e1)
-    ms = shard.max_over_ranks(ms, device=dev)             # off the data path: one scalar after timing stops
+    clk_t0 = time.perf_counter()
+    for r in range(R):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t_h = time.perf_counter()
+        if delay(delay_ns, sp):
+            raise RuntimeError(lib.augcl_last_error().decode())
+        e0.record(stream)
+        for t in range(W + r * K, W + (r + 1) * K):
+            step(t)
+        e1.record(stream)
+        enq.append(1e3 * (time.perf_counter() - t_h))
+        barrier()
+        blocks.append(e0.elapsed_time(e1))
+        if r == 0:
+            launches = L.launch_count() - l0
+            clk_t1 = time.perf_counter()
+    ms_rank = blocks[0]
+    per_rank = shard.gather_over_ranks(ms_rank, device=dev)                    # off the data path, after timing stops
+    ms = max(per_rank)
     value = shard.aggregate_rate(K * B, world, ms * 1e-3)
+    blocks_max = [shard.max_over_ranks(b, device=dev) for b in blocks]
+    timing = {"per_rank_ms": [round(x, 5) for x in per_rank], "blocks_ms_per_step": [round(b / K, 6) for b in blocks_max],
+              "enqueue_ms_rank0": [round(x, 4) for x in enq], "delay_kernel_ns": delay_ns,
+              "cores_rank0": [cores[0], cores[-1]] if cores else None,
+              "note": "block 0 (the first K steps after warm-up) is ms_per_step / value; blocks 1.. repeat the same K-step "
+                      "measurement on fresh indices to show its spread; each block's K launches are enqueued behind a "
+                      "one-thread delay kernel that ends before the start event"}
+    clocks = sampler.window(clk_t0, clk_t1)
 
-    # ---- e2e: public API with HOST indices/offsets, pinned H2D + D2H of the rewards every step
-    Ke = min(K, 2000)
-    h_idx = torch.randint(0, CAP, (Ke + 3, B), generator=g).pin_memory()
-    h_off = torch.randint(0, 2 * PAD + 1, (Ke + 3, 2, B, 2), generator=g, dtype=torch.int32).pin_memory()
+    # ---- e2e: the reference-named call, ReplayBuffer.sample_drq, with HOST indices/offsets in and the rewards read back
+    Ke = min(max(K, 300), 2000)
+    We = 20
+    h_idx = torch.randint(0, CAP, (Ke + We, B), generator=g)
+    h_off = torch.randint(0, 2 * PAD + 1, (Ke + We, 2, B, 2), generator=g, dtype=torch.int32)
     h_rew = torch.empty((B, 1), dtype=torch.float32).pin_memory()
-
-    n_idx, n_off = h_idx.numpy(), h_off.numpy()          # views of the pinned buffers
+    n_idx, n_off = h_idx.numpy(), h_off.numpy()
+    sink = 0.0
+    h_rew_np = h_rew.numpy()
 
     def e2e_step(t):
+        nonlocal sink
         obs, act, rew, nxt, nd = buf.sample_drq(pad=PAD, idxs=n_idx[t], offsets={"obs": n_off[t, 0], "next_obs": n_off[t, 1]})
         h_rew.copy_(rew, non_blocking=True)
         stream.synchronize()
+        sink += float(h_rew_np[0, 0])                # the step's rewards are on the host here
         return obs
 
-    for t in range(3):
-        e2e_step(t)
-    barrier()
-    t0 = time.perf_counter()
-    for t in range(3, Ke + 3):
-        e2e_step(t)
-    torch.cuda.synchronize(dev)
-    el = shard.max_over_ranks(time.perf_counter() - t0, device=dev)
+    def timed(fn_step, n_warm=We):
+        for t in range(n_warm):
+            fn_step(t)
+        barrier()
+        t0 = time.perf_counter()
+        for t in range(n_warm, Ke + n_warm):
+            fn_step(t)
+        torch.cuda.synchronize(dev)
+        return shard.max_over_ranks(time.perf_counter() - t0, device=dev)
 
-    # same steps, result read one step late (double-buffered D2H + events): what an asynchronous training loop sees
+    e2e_t0 = time.perf_counter()
+    el = timed(e2e_step)
+    e2e_clocks = sampler.window(e2e_t0, time.perf_counter())
+
+    # same steps, result read one step late (two pinned slots + events): what an asynchronous training loop sees
     h_rew2 = [torch.empty((B, 1), dtype=torch.float32).pin_memory() for _ in range(2)]
+    h_rew2_np = [h.numpy() for h in h_rew2]
     evs = [torch.cuda.Event() for _ in range(2)]
-    acc = 0.0
-    barrier()
-    t0 = time.perf_counter()
-    for t in range(3, Ke + 3):
+    pending = [False, False]
+
+    def pipe_step(t):
+        nonlocal sink
         j = t & 1
-        if t >= 5:
+        if pending[j]:
             evs[j].synchronize()
-            acc += float(h_rew2[j][0, 0])
+            sink += float(h_rew2_np[j][0, 0])
         obs, act, rew, nxt, nd = buf.sample_drq(pad=PAD, idxs=n_idx[t], offsets={"obs": n_off[t, 0], "next_obs": n_off[t, 1]})
         h_rew2[j].copy_(rew, non_blocking=True)
         evs[j].record(stream)
-    torch.cuda.synchronize(dev)
-    el_p = shard.max_over_ranks(time.perf_counter() - t0, device=dev)
-    # same step through the captured sampler (utils.GraphSampler): the host draws go through one pinned staging block and
-    # one H2D copy, the kernel is replayed from a CUDA graph; rewards D2H + stream synchronize every step as above
+        pending[j] = True
+    el_p = timed(pipe_step)
+
+    # extras: the captured sampler (utils.GraphSampler: one pinned staging block + ONE CUDA graph launch holding the H2D
+    # copy, the kernel and the D2H copy) and the leanest one (utils.FastSampler: fixed output tensors, one ctypes call)
     gs = U.GraphSampler(buf, kind="drq", pad=PAD, batch=B, host_reward=True)
-    sink = 0.0
     g_rew = gs.reward_host.numpy()
 
     def graph_step(t):
         nonlocal sink
         gs.sample(n_idx[t], {"obs": n_off[t, 0], "next_obs": n_off[t, 1]})
         stream.synchronize()
-        sink += float(g_rew[0, 0])                   # the step's rewards are on the host here
-    for t in range(3):
-        graph_step(t)
-    barrier()
-    t0 = time.perf_counter()
-    for t in range(3, Ke + 3):
-        graph_step(t)
-    torch.cuda.synchronize(dev)
-    el_g = shard.max_over_ranks(time.perf_counter() - t0, device=dev)
-    # the leanest host path (utils.FastSampler): the draws travel by value in the kernel's parameter block, the kernel writes
-    # the rewards straight into pinned, device-mapped host memory: one ctypes call + one stream synchronize per step
+        sink += float(g_rew[0, 0])
+    el_g = timed(graph_step)
     fs = U.FastSampler(buf, kind="drq", pad=PAD, batch=B, host_reward=True)
     f_rew = fs.reward_host.numpy()
 
@@ -322,49 +379,46 @@ def run_ours(args):
         nonlocal sink
         fs.sample(n_idx[t], {"obs": n_off[t, 0], "next_obs": n_off[t, 1]})
         stream.synchronize()
-        sink += float(f_rew[0, 0])                   # the step's rewards are on the host here
-    for t in range(3):
-        fast_step(t)
-    barrier()
-    t0 = time.perf_counter()
-    for t in range(3, Ke + 3):
-        fast_step(t)
-    torch.cuda.synchronize(dev)
-    el_f = shard.max_over_ranks(time.perf_counter() - t0, device=dev)
-    e2e = {"value": world * Ke * B / el_f, "unit": UNIT, "h2d_bytes_per_step": 24 * B, "d2h_bytes_per_step": B * 4,
-           "steps": Ke, "ms_per_step": 1e3 * el_f / Ke,
-           "api": "utils.FastSampler(buf, kind='drq', host_reward=True).sample(host idxs, host offsets) + stream synchronize + "
-                  "a host read of the step's rewards EVERY step: the host draws (int64 index + 2x2 int32 offsets per sample, "
-                  "24 B/sample) travel host->device by value in the sample kernel's parameter block (augcl_ring_sample_ex, "
-                  "HOST source: no separate copy), and the kernel writes the step's rewards (4 B/sample) device->host "
-                  "straight into pinned, device-mapped memory",
-           "graph_value": world * Ke * B / el_g, "graph_ms_per_step": 1e3 * el_g / Ke,
-           "graph_note": "utils.GraphSampler: draws through one pinned staging block; ONE CUDA graph launch per step holds the "
-                         "H2D copy (24 B/sample), the sample kernel and the D2H copy of the rewards into pinned host memory",
-           "dropin_value": world * Ke * B / el, "dropin_ms_per_step": 1e3 * el / Ke,
-           "dropin_note": "the reference-named call, ReplayBuffer.sample_drq(idxs=host numpy, offsets=host numpy), same copies "
-                          "and per-step synchronize; the host draws travel by value in the kernel's parameter block "
-                          "(augcl_ring_sample_ex HOST), outputs are fresh tensors every call",
+        sink += float(f_rew[0, 0])
+    el_f = timed(fast_step)
+    sampler.stop()
+    e2e = {"value": world * Ke * B / el, "unit": UNIT, "h2d_bytes_per_step": 24 * B, "d2h_bytes_per_step": B * 4,
+           "steps": Ke, "warmup": We, "ms_per_step": 1e3 * el / Ke, "clocks": e2e_clocks,
+           "api": "ReplayBuffer.sample_drq(pad=4, idxs=host numpy, offsets=host numpy) -- the reference-named call "
+                  "(src/utils.py:260-270), fresh output tensors every call -- + D2H copy of the step's rewards into pinned "
+                  "memory + stream synchronize + a host read of the rewards EVERY step; the host draws (int64 index + 2x2 "
+                  "int32 offsets per sample, 24 B/sample) travel host->device by value in the sample kernel's parameter "
+                  "block (augcl_ring_sample_ex, HOST source: no separate copy)",
            "pipelined_value": world * Ke * B / el_p, "pipelined_ms_per_step": 1e3 * el_p / Ke,
-           "pipelined_note": "the drop-in call with each step's rewards read one step late (2 pinned slots + events)"}
+           "pipelined_note": "the same call with each step's rewards read one step late (2 pinned slots + events, no "
+                             "per-step synchronize)",
+           "graph_value": world * Ke * B / el_g, "graph_ms_per_step": 1e3 * el_g / Ke,
+           "graph_note": "extra: utils.GraphSampler, draws through one pinned staging block; ONE CUDA graph launch per step "
+                         "holds the H2D copy (24 B/sample), the sample kernel and the D2H copy of the rewards; outputs are "
+                         "the graph's own tensors (valid until the next call)",
+           "fast_value": world * Ke * B / el_f, "fast_ms_per_step": 1e3 * el_f / Ke,
+           "fast_note": "extra: utils.FastSampler, one ctypes call per step, fixed output tensors (valid until the next "
+                        "call), rewards written by the kernel straight into pinned device-mapped host memory"}
     return dict(buf=buf, dev=dev, world=world, rank=rank, ms=ms, value=value, launches=launches, clocks=clocks, e2e=e2e,
-                step_raw=fn, K=K, W=W, B=B)
+                step_raw=fn, K=K, W=W, B=B, timing=timing, shard=shard, barrier=barrier)
 
 
 def batch_sweep(res, batches=(128, 256, 512, 1024, 2048, 4096, 8192, 16384)):
-    """BASELINE.json configs[4] in brief (extra evidence, not the bench line): same step at larger batches,
-    device-timed, fresh indices each iteration."""
+    """BASELINE.json configs[4] (extra evidence, not the bench line): the same step at larger batches, device-timed,
+    fresh indices each iteration, launches enqueued behind a delay kernel.  Under torchrun every rank runs the sweep on
+    its own shard and the time of a point is the max over ranks (aggregate = world * batch * iters / that)."""
     import torch
     from augcl_b200 import _lib as L
-    buf, dev = res["buf"], res["dev"]
+    buf, dev, world, shard = res["buf"], res["dev"], res["world"], res["shard"]
     peak = load_peaks()[0]
     out = []
-    g = torch.Generator().manual_seed(99)
+    g = torch.Generator().manual_seed(99 + res["rank"])
     stream = torch.cuda.current_stream(dev)
+    lib = L.lib()
     for B in batches:
         iters = max(20, min(400, (1 << 19) // B))
         n_sets = max(2, min(8, (600 << 20) // (2 * B * S8 * 4)))
-        o = [(torch.empty((B, C, S, S), device=dev), torch.empty((B, C, S, S), device=dev)) for _ in range(n_sets)]
+        o = [(torch.zeros((B, C, S, S), device=dev), torch.zeros((B, C, S, S), device=dev)) for _ in range(n_sets)]
         idx = torch.randint(0, CAP, (iters + 3, B), generator=g).to(dev)
         off = torch.randint(0, 2 * PAD + 1, (iters + 3, 2, B, 2), generator=g, dtype=torch.int32).to(dev)
 
@@ -374,17 +428,18 @@ def batch_sweep(res, batches=(128, 256, 512, 1024, 2048, 4096, 8192, 16384)):
                    L.AUG_SHIFT, off[t, 0].data_ptr(), off[t, 1].data_ptr(), PAD, 0, stream.cuda_stream)
         for t in range(3):
             step(t)
-        torch.cuda.synchronize(dev)
+        res["barrier"]()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        lib.augcl_stream_delay(min(45_000_000, 200_000 + 15_000 * iters), stream.cuda_stream)
         e0.record(stream)
         for t in range(3, iters + 3):
             step(t)
         e1.record(stream)
-        torch.cuda.synchronize(dev)
-        ms = e0.elapsed_time(e1) / iters
+        res["barrier"]()
+        ms = shard.max_over_ranks(e0.elapsed_time(e1), device=dev) / iters
         gbs = B * BYTES_PER_SAMPLE / (ms * 1e-3) / 1e9
-        out.append({"batch": B, "us_per_step": round(ms * 1e3, 2), "samples_per_s": round(B / (ms * 1e-3)),
-                    "GB/s": round(gbs, 1), "frac": round(gbs / peak, 4)})
+        out.append({"batch_per_gpu": B, "us_per_step": round(ms * 1e3, 2), "samples_per_s": round(world * B / (ms * 1e-3)),
+                    "GB/s_per_gpu": round(gbs, 1), "frac": round(gbs / peak, 4)})
         del o
     return out
 
@@ -509,6 +564,95 @@ def dedup_ring(res):
     return out
 
 
+def torch_cuda_reference(res):
+    """The reference's OWN code for the path on the same B200 (rank 0, N=1): its torch op sequence on CUDA, run from
+    oracle/_ref (the reference compiled by oracle/build_ref.py; oracle/ref_harness.gpu_*).  Two figures per config:
+    `device_*` = the device-side op sequence alone with its inputs already in HBM (what the kernels replace on the GPU:
+    .float() + F.pad + per-sample crop + stack, and splice + the per-sample conv2d loop), CUDA events; `e2e_*` = the
+    reference's full call from host indices (host gather loop, pageable H2D, ops, rewards back), wall clock with a
+    synchronize every step.  Same batch, offsets, weights and background rows on both sides."""
+    import torch
+    from oracle import ref_harness as R
+    if not R.available():
+        return {"unavailable": "no reference modules on this machine (oracle/_ref not built)"}
+    dev = res["dev"]
+    cap_host, B = 20_000, 128
+    rng = np.random.default_rng(11)
+    frames = rng.integers(0, 256, (cap_host + K_FRAMES, 3, S, S), dtype=np.uint8)
+    buf = R.ref_replay_buffer((C, S, S), (A_DIM,), cap_host, B)
+    act = np.zeros(A_DIM, dtype=np.float32)
+    for t in range(cap_host):
+        buf.add(R.ref_lazy_frames(frames[t:t + K_FRAMES]), act, 0.5, R.ref_lazy_frames(frames[t + 1:t + 1 + K_FRAMES]), False)
+    st = torch.cuda.current_stream(dev)
+    out = {"kind": "reference (oracle/_ref)" if R.ref_dir() == R.REF_BUILT else "reference (/root/reference)",
+           "host_ring": cap_host, "batch": B,
+           "crop": "kornia.augmentation.RandomCrop stand-in, slice mode (kornia >= 0.6 semantics; kornia is absent here)"}
+
+    def dev_time(fn, iters, warm=3):
+        for _ in range(warm):
+            fn()
+        torch.cuda.synchronize(dev)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(st)
+        for _ in range(iters):
+            fn()
+        e1.record(st)
+        torch.cuda.synchronize(dev)
+        return e0.elapsed_time(e1) * 1e3 / iters
+
+    def wall_time(fn, iters, warm=3):
+        for _ in range(warm):
+            fn()
+        torch.cuda.synchronize(dev)
+        t0 = time.perf_counter()
+        for _ in range(iters):
+            fn()
+        torch.cuda.synchronize(dev)
+        return (time.perf_counter() - t0) * 1e6 / iters
+
+    # ---- configs[1]: sample + random_shift(obs), random_shift(next_obs)
+    x8 = [torch.from_numpy(rng.integers(0, 256, (B, C, S, S), dtype=np.uint8)).to(dev) for _ in range(8)]
+    n8 = [torch.from_numpy(rng.integers(0, 256, (B, C, S, S), dtype=np.uint8)).to(dev) for _ in range(8)]
+    o1, o2 = rng.integers(0, 2 * PAD + 1, (B, 2)), rng.integers(0, 2 * PAD + 1, (B, 2))
+    cnt = [0]
+
+    def dev_c1():
+        i = cnt[0] = (cnt[0] + 1) % 8
+        return R.gpu_random_shift(x8[i].float(), o1, PAD), R.gpu_random_shift(n8[i].float(), o2, PAD)
+
+    def e2e_c1():
+        idxs = rng.integers(0, cap_host, size=B)
+        obs, a, r, nxt, nd = R.gpu_sample(buf, idxs)
+        so, sn = R.gpu_random_shift(obs, o1, PAD), R.gpu_random_shift(nxt, o2, PAD)
+        return float(r.cpu()[0, 0])
+    d1, w1 = dev_time(dev_c1, 30), wall_time(e2e_c1, 30)
+    out["configs[1]"] = {"device_us_per_step": round(d1, 1), "device_samples_per_s": round(B / d1 * 1e6),
+                         "e2e_us_per_step": round(w1, 1), "e2e_samples_per_s": round(B / w1 * 1e6),
+                         "ours_device_us_per_step": round(res["ms"] * 1e3 / res["K"], 2),
+                         "ours_e2e_us_per_step": round(res["e2e"]["ms_per_step"] * 1e3, 2),
+                         "speedup_device": round(d1 / (res["ms"] * 1e3 / res["K"]), 1),
+                         "speedup_e2e": round(w1 / (res["e2e"]["ms_per_step"] * 1e3), 1)}
+
+    # ---- configs[3]: AugCL update input = sample + random_shift(obs) + random_conv(splice(obs))
+    imgs = torch.from_numpy(rng.integers(0, 256, (B, 3, S, S), dtype=np.uint8)).to(dev).float() / 255.0
+    wts = list(torch.randn((B, 3, 3, 3, 3), generator=torch.Generator().manual_seed(5)).to(dev))
+    xf = [t.float() for t in x8[:2]]
+
+    def dev_c3():
+        i = cnt[0] = (cnt[0] + 1) % 2
+        return R.gpu_random_shift(xf[i], o1, PAD), R.gpu_splice_conv(xf[i], imgs, wts)
+
+    def e2e_c3():
+        idxs = rng.integers(0, cap_host, size=B)
+        obs, a, r, nxt, nd = R.gpu_sample(buf, idxs)
+        so, sa = R.gpu_random_shift(obs, o1, PAD), R.gpu_splice_conv(obs, imgs, wts)
+        return float(r.cpu()[0, 0])
+    d3, w3 = dev_time(dev_c3, 10, warm=2), wall_time(e2e_c3, 10, warm=2)
+    out["configs[3]"] = {"device_us_per_step": round(d3, 1), "device_samples_per_s": round(B / d3 * 1e6),
+                         "e2e_us_per_step": round(w3, 1), "e2e_samples_per_s": round(B / w3 * 1e6)}
+    return out
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.isfile(p):
@@ -524,6 +668,9 @@ def main():
     import torch
     import torch.distributed as dist
     world, rank, K, B = res["world"], res["rank"], res["K"], res["B"]
+    sweep = None
+    if not args.no_sweep:       # every rank runs it (max over ranks per point); N > 1: three points of configs[4]
+        sweep = batch_sweep(res) if world == 1 else batch_sweep(res, batches=(128, 2048, 16384))
     if rank == 0:
         peak, peak_src = load_peaks()
         us = res["ms"] * 1e3 / K
@@ -539,24 +686,38 @@ def main():
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "kernel": "ring_sample_band_kernel<84,84,84,84,0>", "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": B * BYTES_PER_SAMPLE,
-                         "note": "per-launch time = timed region / steps (one launch per step, CUDA events on the launching stream)",
+                         "note": "per-launch time = timed region / steps (one launch per step, CUDA events on the launching "
+                                 "stream; the K launches are enqueued behind a one-thread delay kernel that ends before the "
+                                 "start event, see `timing`)",
                          "traffic_note": "ncu --set full, one isolated launch (profiles/r01_ncu_ring_sample.csv): 16.2 MB read = the "
                                          "launch's u8 inputs exactly, 8.3 MB written -- the other 57 MB of its 65 MB f32 output are "
                                          "still dirty lines in the 126 MB L2 when the kernel ends and reach DRAM during later "
                                          "launches; no re-reads (traffic below the algorithmic bytes, not above)"},
-            "clocks": res["clocks"], "e2e": res["e2e"], "gpu_launches": res["launches"],
+            "clocks": res["clocks"], "e2e": res["e2e"], "gpu_launches": res["launches"], "timing": res["timing"],
         }
+        if sweep is not None:
+            line["batch_sweep"] = sweep
         if world == 1 and not args.no_sweep:
-            line["batch_sweep"] = batch_sweep(res)
             line["fused_configs"] = fused_configs(res)
             line["dedup_ring"] = dedup_ring(res)
+            if not args.no_gpu_reference:
+                tcr = line["torch_cuda_reference"] = torch_cuda_reference(res)
+                if "configs[3]" in tcr:
+                    ours3 = line["fused_configs"][1]
+                    tcr["configs[3]"].update(ours_device_us_per_step=ours3["us_per_step"], ours_e2e_us_per_step=ours3["e2e_us_per_step"],
+                                             speedup_device=round(tcr["configs[3]"]["device_us_per_step"] / ours3["us_per_step"], 1),
+                                             speedup_e2e=round(tcr["configs[3]"]["e2e_us_per_step"] / ours3["e2e_us_per_step"], 1))
         if world == 1 and not args.no_cpu_baseline:
-            cores = os.cpu_count() or 1
+            cores = host_cores()
             torch.set_num_threads(cores)
             step, kind, desc = cpu_step_factory(B)
             n, el = time_cpu(step, args.cpu_seconds)
+            torch.set_num_threads(1)
+            n1, el1 = time_cpu(step, max(2.0, args.cpu_seconds / 4))
+            torch.set_num_threads(cores)
             line["cpu_baseline"] = {"value": n * B / el, "unit": UNIT, "cores": cores, "kind": kind,
-                                    "sample": f"{n} steps in {el:.1f} s: " + desc}
+                                    "sample": f"{n} steps in {el:.1f} s: " + desc, "cpu_model": cpu_model(),
+                                    "value_1_thread": n1 * B / el1}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()

@@ -66,6 +66,10 @@ const char* augcl_last_error(void);
 /* Number of kernel launches this library has enqueued from the calling process so far
  * (bench.py's "gpu_launches" evidence). */
 int64_t augcl_launch_count(void);
+/* Measurement helper (no reference analogue): enqueue a one-thread kernel that keeps `stream` busy for about
+ * `nanoseconds` (<= 50 ms; it waits on the GPU's clock only).  bench.py puts it in front of the timed region so that every
+ * timed launch is already queued when the GPU reaches the first one.  Not counted by augcl_launch_count. */
+int augcl_stream_delay(uint64_t nanoseconds, augcl_stream stream);
 /* Runtime switches, for A/B measurement: "staging" = "tma" (default; cp.async.bulk + mbarrier
  * pipeline through shared memory) | "generic" (one thread per output element, no staging). */
 int augcl_set_option(const char* key, const char* value);

@@ -158,9 +158,27 @@ def chunk_case(name, seed, cap, k, S, A, saves, B):
     print(name, sorted(os.listdir(out_dir)), [os.path.getsize(os.path.join(out_dir, f)) for f in sorted(os.listdir(out_dir))])
 
 
+def warp_cases(names):
+    """random_shift as the pinned-era environment runs it (setup/conda.yaml:12,22 -> kornia 0.5.x: RandomCrop applies the
+    crop as a bilinear warp, align_corners=True): the reference's random_shift executed with the harness's crop stand-in
+    in "warp" mode on the inputs / offsets of the existing cases.  Kept in its own small file so the other fixtures stay
+    byte-identical."""
+    d = {}
+    for name in names:
+        c = dict(np.load(os.path.join(OUT, name + ".npz")))
+        x = torch.from_numpy(c["x_u8"]).float()
+        d[name] = R.ref_random_shift(x, c["shift_off"], int(c["pad"]), "warp").numpy()
+    path = os.path.join(OUT, "shift_warp.npz")
+    np.savez_compressed(path, **d)
+    print("shift_warp", {k: v.shape for k, v in d.items()}, os.path.getsize(path))
+
+
 if __name__ == "__main__":
     assert R.available(), "needs /root/reference"
     os.makedirs(OUT, exist_ok=True)
+    if "--warp-only" in sys.argv:
+        warp_cases(["aug_84", "aug_small", "aug_rect", "aug_odd"])
+        sys.exit(0)
     case("aug_84", seed=1, n=2, c=9, h=84, w=84, pad=4, crop_from=(100, 84))
     case("aug_small", seed=2, n=5, c=6, h=20, w=20, pad=3, crop_from=(24, 20))
     case("aug_rect", seed=3, n=3, c=3, h=12, w=28, pad=2)          # non-square, w%4==0
@@ -168,3 +186,4 @@ if __name__ == "__main__":
     replay_case("replay_small", seed=5, cap=24, k=3, S=16, A=6, n_add=37, B=10)
     replay_case("replay_84", seed=6, cap=16, k=3, S=84, A=6, n_add=12, B=4)
     chunk_case("chunks_ref", seed=7, cap=40, k=3, S=12, A=4, saves=[10, 25], B=9)
+    warp_cases(["aug_84", "aug_small", "aug_rect", "aug_odd"])

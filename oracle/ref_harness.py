@@ -158,11 +158,9 @@ def load_reference():
 
 
 @contextlib.contextmanager
-def cpu_shims():
-    """Neutralise .cuda()/is_cuda/get_device() and numpy-2 ``copy=False``."""
-    orig_cuda = torch.Tensor.cuda
-    orig_get_device = torch.Tensor.get_device
-    orig_is_cuda = torch.Tensor.is_cuda
+def numpy2_shim():
+    """``np.array(obj, copy=False)`` (src/utils.py:238-239) raises on numpy >= 2 when a copy is needed; numpy 1.19, which
+    the reference pins, copied silently.  Restores that behaviour for the duration of a call."""
     orig_np_array = np.array
 
     def np_array(obj, *a, copy=True, **kw):
@@ -170,17 +168,29 @@ def cpu_shims():
             return np.asarray(obj, *a, **kw)
         return orig_np_array(obj, *a, copy=copy, **kw)
 
-    torch.Tensor.cuda = lambda self, *a, **k: self
-    torch.Tensor.get_device = lambda self: "cpu"
-    torch.Tensor.is_cuda = property(lambda self: True)
     np.array = np_array
     try:
         yield
     finally:
+        np.array = orig_np_array
+
+
+@contextlib.contextmanager
+def cpu_shims():
+    """Neutralise .cuda()/is_cuda/get_device() and numpy-2 ``copy=False``."""
+    orig_cuda = torch.Tensor.cuda
+    orig_get_device = torch.Tensor.get_device
+    orig_is_cuda = torch.Tensor.is_cuda
+    torch.Tensor.cuda = lambda self, *a, **k: self
+    torch.Tensor.get_device = lambda self: "cpu"
+    torch.Tensor.is_cuda = property(lambda self: True)
+    try:
+        with numpy2_shim():
+            yield
+    finally:
         torch.Tensor.cuda = orig_cuda
         torch.Tensor.get_device = orig_get_device
         torch.Tensor.is_cuda = orig_is_cuda
-        np.array = orig_np_array
 
 
 # -------------------------- reference entry points --------------------------
@@ -354,3 +364,38 @@ def ref_random_cutout_color(x, w1, h1, color_ints):
     aug, _ = load_reference()
     with cpu_shims(), _np_random(aug, randint=[np.asarray(w1), np.asarray(h1), np.asarray(color_ints)]):
         return aug.random_cutout_color(x.clone())
+
+
+# -------------------------- the reference on a GPU (bench.py's torch_cuda_reference leg) --------------------------
+# The reference's functions are written for CUDA (.cuda() / is_cuda are hard-coded); on a GPU box they run as they are,
+# with only the kornia stand-in, the numpy-2 shim and the injected draws.
+
+def gpu_sample(buf, idxs):
+    """src/utils.py:272-280 on the GPU: host gather (_encode_obses), pageable H2D, .float()."""
+    with numpy2_shim():
+        return buf.sample(idxs=np.asarray(idxs))
+
+
+def gpu_random_shift(x, offsets, pad=4, mode="slice"):
+    """src/augmentations.py:378-382 on CUDA tensors (F.pad + the kornia crop stand-in)."""
+    aug, _ = load_reference()
+    _RandomCrop._next_offsets = np.asarray(offsets)
+    _RandomCrop._mode = mode
+    try:
+        return aug.random_shift(x, pad)
+    finally:
+        _RandomCrop._next_offsets = None
+
+
+def gpu_splice_conv(x, imgs, weights):
+    """random_conv(splice(x)) of src/augmentations.py:295-306, :265-274 on CUDA tensors: the AugCL strong phase
+    (--data_aug splice-conv through RAD.apply_aug, src/algorithms/rad.py:18-22)."""
+    aug, _ = load_reference()
+    it = iter(weights)
+    orig = aug.torch.randn
+    aug.torch.randn = lambda *shape, **kw: next(it)
+    try:
+        with _bank_batch(aug, imgs):
+            return aug.random_conv(aug.splice(x))
+    finally:
+        aug.torch.randn = orig

@@ -45,6 +45,9 @@ def test_against_reference_golden(A, golden, name):
     try:
         out = A.random_shift(x, int(d["pad"]), offsets=d["shift_off"])
         assert torch.equal(out.cpu(), torch.from_numpy(d["shift_out"]))
+        # the same call as the pinned-era environment runs it (kornia 0.5.x: RandomCrop is a bilinear warp,
+        # /root/reference/src/augmentations.py:382): reference output recorded in warp mode, float tolerance
+        assert norm_err(out, golden("shift_warp")[name]) <= TOL_NORM
         assert norm_err(A.random_conv(x, weights=d["conv_w"]), d["conv_out"]) <= TOL_NORM
         assert norm_err(A.random_overlay(x, bank_idx=rows), d["overlay_out"]) <= TOL_NORM
         for thr, key in [((0, 0, 0.6), "splice_out_06"), ((0, 0, 0.4), "splice_out_04"), ((1.0, 0.2, 0.3), "splice_out_hs")]:

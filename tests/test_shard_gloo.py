@@ -26,6 +26,8 @@ def _worker(rank, world, port, out):
         shard.barrier()
         elapsed = 0.010 * (rank + 1)                      # rank 1 is the slow one
         tmax = shard.max_over_ranks(elapsed)
+        per_rank = shard.gather_over_ranks(elapsed)
+        assert per_rank == [0.010, 0.020]
         idx = O.rng_randint(128, 0, p.capacity, p.draw_seed, 0)
         gathered = [None] * world
         dist.all_gather_object(gathered, (p.ring_seed, p.draw_seed, idx.tolist()))
@@ -56,3 +58,19 @@ def test_single_process_defaults():
     p = shard.plan(10, 4)
     assert (p.rank, p.world, p.global_batch) == (0, 1, 4)
     assert shard.max_over_ranks(1.5) == 1.5
+    assert shard.gather_over_ranks(1.5) == [1.5]
+
+
+def test_core_slices_are_disjoint_and_cover():
+    from augcl_b200 import shard
+    cores = list(range(32))
+    for world in (1, 2, 4, 8):
+        sl = [shard.core_slice(r, world, cores) for r in range(world)]
+        assert all(len(s) == 32 // world for s in sl)
+        flat = [c for s in sl for c in s]
+        assert sorted(flat) == cores                      # disjoint, nothing left idle
+    # more ranks than cores: one core each, wrapping
+    assert [shard.core_slice(r, 4, [5, 9]) for r in range(4)] == [[5], [9], [5], [9]]
+    assert shard.core_slice(0, 2, []) == []
+    got = shard.pin_to_cores(0, 1)                        # whole allowed set: a no-op pin
+    assert got is None or sorted(got) == sorted(os.sched_getaffinity(0))
