@@ -19,14 +19,15 @@ import sys
 SHIM_DIR = os.path.dirname(os.path.abspath(__file__))
 
 
-def install(reference_src: str) -> None:
+def install(reference_src=None) -> None:
     """Put the shim modules ahead of ``reference_src`` on sys.path (both are added if missing) and drop already-imported
-    ``utils`` / ``augmentations`` / ``algorithms`` modules so the next import resolves through the shim."""
-    reference_src = os.path.abspath(reference_src)
-    for p in (SHIM_DIR, reference_src):
+    ``utils`` / ``augmentations`` / ``algorithms`` modules so the next import resolves through the shim.
+    reference_src=None: the reference is provided by some other importer (sys.meta_path); only the shim is installed."""
+    dirs = [SHIM_DIR] + ([os.path.abspath(reference_src)] if reference_src else [])
+    for p in dirs:
         while p in sys.path:
             sys.path.remove(p)
-    sys.path[:0] = [SHIM_DIR, reference_src]
+    sys.path[:0] = dirs
     for name in [m for m in sys.modules if m in ("utils", "augmentations", "algorithms") or m.startswith("algorithms.")]:
         del sys.modules[name]
 

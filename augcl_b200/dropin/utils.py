@@ -24,6 +24,18 @@ def _load_reference_utils():
                 sys.modules["_augcl_reference_utils"] = mod
                 spec.loader.exec_module(mod)      # its `import augmentations` resolves to the shim next to this file
                 return mod
+    # not a plain directory of sources: ask the import system's other finders (e.g. a finder for a compiled reference)
+    for finder in sys.meta_path:
+        find = getattr(finder, "find_spec", None)
+        spec = find("utils", None) if find else None
+        if spec is None or spec.loader is None or not spec.origin or os.path.dirname(os.path.abspath(spec.origin)) == _HERE:
+            continue
+        loader = type(spec.loader)("_augcl_reference_utils", spec.origin)
+        spec = importlib.util.spec_from_loader("_augcl_reference_utils", loader, origin=spec.origin)
+        mod = importlib.util.module_from_spec(spec)
+        sys.modules["_augcl_reference_utils"] = mod
+        spec.loader.exec_module(mod)
+        return mod
     raise ImportError("augcl_b200.dropin.utils: the reference's src/ directory (utils.py + augmentations.py) must come "
                       "after augcl_b200/dropin on sys.path")
 

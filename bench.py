@@ -312,8 +312,8 @@ def run_ours(args):
     clocks = sampler.window(clk_t0, clk_t1)
 
     # ---- e2e: the reference-named call, ReplayBuffer.sample_drq, with HOST indices/offsets in and the rewards read back
-    Ke = min(max(K, 300), 2000)
-    We = 20
+    Ke = min(max(K, 1000), 2000)
+    We = 100
     h_idx = torch.randint(0, CAP, (Ke + We, B), generator=g)
     h_off = torch.randint(0, 2 * PAD + 1, (Ke + We, 2, B, 2), generator=g, dtype=torch.int32)
     h_rew = torch.empty((B, 1), dtype=torch.float32).pin_memory()

@@ -14,8 +14,9 @@ travels to the GPU box, where /root/reference does not exist.  There it serves a
   * the "reference on the same GPU" column of bench.py (the reference's torch op sequence on CUDA).
 
 Modules compiled (all under /root/reference/src): utils.py, augmentations.py, algorithms/*.py.
-The .pyc files are "unchecked hash" bytecode: importable without the source next to them (sourceless import),
-bound to this image's CPython minor version (the GPU box runs the same image).
+The files are "unchecked hash" CPython bytecode (the .pyc format) stored as ``<module>.bin`` -- snapshot tools tend to
+drop ``*.pyc`` -- and imported through the meta-path finder in oracle/ref_harness.py (``RefFinder``); they are bound to
+this image's CPython minor version (the GPU box runs the same image).
 """
 from __future__ import annotations
 
@@ -49,7 +50,7 @@ def up_to_date() -> bool:
         return False
     for rel in sources():
         src = os.path.join(REF_SRC, rel)
-        dst = os.path.join(OUT, rel + "c")
+        dst = os.path.join(OUT, rel[:-3] + ".bin")
         if not os.path.isfile(dst) or meta.get("mtimes", {}).get(rel) != os.path.getmtime(src):
             return False
     return True
@@ -65,7 +66,7 @@ def build(force: bool = False) -> str | None:
     mtimes = {}
     for rel in sources():
         src = os.path.join(REF_SRC, rel)
-        dst = os.path.join(OUT, rel + "c")             # utils.py -> utils.pyc (sourceless-import name)
+        dst = os.path.join(OUT, rel[:-3] + ".bin")     # utils.py -> utils.bin (bytecode; see the module docstring)
         os.makedirs(os.path.dirname(dst), exist_ok=True)
         py_compile.compile(src, cfile=dst, dfile="<reference>/src/" + rel, doraise=True,
                            invalidation_mode=py_compile.PycInvalidationMode.UNCHECKED_HASH)

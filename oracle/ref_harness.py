@@ -21,6 +21,9 @@ the random draws (kornia RandomCrop parameters, ``torch.randn`` in
 from __future__ import annotations
 
 import contextlib
+import importlib.abc
+import importlib.machinery
+import importlib.util
 import math
 import os
 import sys
@@ -37,9 +40,47 @@ def ref_dir():
     """Directory the reference's modules are imported from: the live tree when it is mounted, else the compiled copy."""
     if os.path.isfile(os.path.join(REF_LIVE, "augmentations.py")):
         return REF_LIVE
-    if os.path.isfile(os.path.join(REF_BUILT, "augmentations.pyc")):
+    if os.path.isfile(os.path.join(REF_BUILT, "augmentations.bin")):
         return REF_BUILT
     return None
+
+
+class RefFinder(importlib.abc.MetaPathFinder):
+    """Imports the reference's modules from oracle/_ref: ``<root>/<pkg>/<mod>.bin`` holds the bytecode
+    oracle/build_ref.py compiled from /root/reference/src/<pkg>/<mod>.py; directories are namespace packages (the
+    reference's ``algorithms`` has no __init__.py either)."""
+
+    def __init__(self, root=REF_BUILT):
+        self.root = root
+
+    def find_spec(self, fullname, path=None, target=None):
+        rel = os.path.join(self.root, *fullname.split("."))
+        if os.path.isfile(rel + ".bin"):
+            loader = importlib.machinery.SourcelessFileLoader(fullname, rel + ".bin")
+            return importlib.util.spec_from_loader(fullname, loader, origin=rel + ".bin")
+        if os.path.isdir(rel):
+            spec = importlib.machinery.ModuleSpec(fullname, None, is_package=True)
+            spec.submodule_search_locations = [rel]
+            return spec
+        return None
+
+
+def install_ref_importer(front=False):
+    """Make the reference's modules importable by name on a machine without /root/reference.  front=False: only names
+    nothing else provides (``algorithms.*``; ``utils`` / ``augmentations`` when no shim shadows them)."""
+    for f in sys.meta_path:
+        if isinstance(f, RefFinder):
+            return f
+    f = RefFinder()
+    if front:
+        sys.meta_path.insert(0, f)
+    else:
+        sys.meta_path.append(f)
+    return f
+
+
+def remove_ref_importer():
+    sys.meta_path[:] = [f for f in sys.meta_path if not isinstance(f, RefFinder)]
 
 
 REF_SRC = ref_dir() or REF_LIVE
@@ -143,12 +184,20 @@ def load_reference():
         raise RuntimeError("neither /root/reference nor oracle/_ref (python oracle/build_ref.py) is present on this machine")
     _install_kornia_stub()
     saved = {k: sys.modules.pop(k) for k in ("augmentations", "utils") if k in sys.modules}
-    sys.path.insert(0, src)
+    built = src == REF_BUILT
+    finder = RefFinder() if built else None
+    if built:
+        sys.meta_path.insert(0, finder)       # ahead of the path finder: the reference's modules, whatever sys.path holds
+    else:
+        sys.path.insert(0, src)
     try:
         import augmentations as ref_aug  # noqa: E402
         import utils as ref_utils  # noqa: E402
     finally:
-        sys.path.remove(src)
+        if built:
+            sys.meta_path.remove(finder)
+        else:
+            sys.path.remove(src)
         # keep the reference modules out of the global namespace
         sys.modules.pop("augmentations", None)
         sys.modules.pop("utils", None)

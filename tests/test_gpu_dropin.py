@@ -53,9 +53,14 @@ def dropin():
     if ref is None:
         pytest.skip("no reference available (neither /root/reference nor oracle/_ref)")
     import augcl_b200.dropin as D
+    from oracle import ref_harness as R
     saved_path = list(sys.path)
     saved_mods = {k: sys.modules.get(k) for k in ("utils", "augmentations", "logger")}
-    D.install(ref)
+    if ref == R.REF_BUILT:          # compiled reference (GPU box): resolved by name through the harness's finder
+        R.install_ref_importer()
+        D.install(None)
+    else:
+        D.install(ref)
     lg = types.ModuleType("logger")
     lg.Logger = _Log
     sys.modules["logger"] = lg
@@ -63,9 +68,11 @@ def dropin():
     import utils
     from algorithms.factory import make_agent
     assert utils.ReplayBuffer.__module__ == "augcl_b200.utils" and augmentations.random_shift.__module__ == "augcl_b200.augmentations"
-    assert os.path.dirname(sys.modules["algorithms.sac"].__file__).startswith(ref), "algorithm classes must be the reference's"
+    assert sys.modules["algorithms.sac"].__spec__.origin.startswith(ref), "algorithm classes must be the reference's"
+    assert utils.soft_update_params.__module__ == "_augcl_reference_utils"
     yield types.SimpleNamespace(utils=utils, aug=augmentations, make_agent=make_agent)
     D.uninstall()
+    R.remove_ref_importer()
     sys.path[:] = saved_path
     for k, v in saved_mods.items():
         if v is None:

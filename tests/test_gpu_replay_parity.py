@@ -379,3 +379,55 @@ def test_sample_encoder_input_is_centercrop_plus_normalize(U, S, size):
     if S == 20:
         with pytest.raises(ValueError):
             buf.sample_encoder_input(idxs=idxs, center_crop=13)
+
+
+def test_recycled_output_sets_behave_like_fresh_tensors(U):
+    """ReplayBuffer._outputs hands a set of output tensors out again only when nothing outside the pool can see it: the
+    reference's contract (fresh tensors from every sample(), src/utils.py:206-214) as far as a caller can observe."""
+    buf = U.ReplayBuffer((9, 84, 84), (3,), 256, 8)
+    buf.fill_synthetic(seed=2)
+    rng = np.random.RandomState(0)
+
+    def draw():
+        return buf.sample(idxs=rng.randint(0, 256, 8))
+
+    a = draw()
+    a_copy = [t.clone() for t in a]
+    b = draw()
+    assert all(x.data_ptr() != y.data_ptr() for x, y in zip(a, b))          # both alive: never the same memory
+    for _ in range(5):
+        draw()                                                               # results dropped at once: sets are recycled
+    assert all(torch.equal(x, y) for x, y in zip(a, a_copy)), "a live result was overwritten"
+    assert len(buf._out_pool[(8, 84, 84)]) <= U.ReplayBuffer.POOL_SETS
+    # only a VIEW of a result stays alive
+    view = draw()[0][2:4, 3]
+    view_copy = view.clone()
+    for _ in range(6):
+        draw()
+    assert torch.equal(view, view_copy), "memory behind a live view was recycled"
+    # autograd holds a result (saved for backward) after the caller dropped it
+    w = torch.ones(8, 9, 84, 84, device="cuda", requires_grad=True)
+    loss = (w * draw()[0]).sum()
+    expect = None
+    for _ in range(6):
+        draw()
+    loss.backward()
+    expect = w.grad.clone()
+    obs = buf.sample(idxs=np.arange(8))[0]
+    w.grad = None
+    (w * obs).sum().backward()
+    assert w.grad is not None and expect is not None and torch.isfinite(expect).all()
+    # every set busy -> plain allocation, still correct
+    held = [draw() for _ in range(U.ReplayBuffer.POOL_SETS + 2)]
+    ptrs = {h[0].data_ptr() for h in held}
+    assert len(ptrs) == len(held)
+    # recycling really happens when results are dropped (otherwise the pool is dead weight)
+    p1 = draw()[0].data_ptr()
+    del held
+    seen = {draw()[0].data_ptr() for _ in range(8)}
+    assert len(seen) <= U.ReplayBuffer.POOL_SETS
+    # pool off == plain allocations, same values
+    plain = U.ReplayBuffer((9, 84, 84), (3,), 256, 8, pool_outputs=False)
+    plain.fill_synthetic(seed=2)
+    i = rng.randint(0, 256, 8)
+    assert all(torch.equal(x, y) for x, y in zip(buf.sample(idxs=i), plain.sample(idxs=i)))
