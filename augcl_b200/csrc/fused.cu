@@ -15,8 +15,12 @@
 // they land in a 2-deep stage ring guarded by mbarriers while the CTA works on the previous unit.
 //   phase A (elementwise): thread = 4 pixels x 3 channels of one tile row.  Plain word = 1 LDS.32; shifted word =
 //     2 LDS.32 + funnel shift + PRMT replicate selector (as in ring_sample_band_kernel); HSV mask / overlay in
-//     registers; direct outputs are STG.128; the conv input goes to an f32 tile ([3][rows+2][W+8]) in shared memory.
-//   phase B (conv): the 2x4x3 register-blocked loop of random_conv_tma_kernel on that tile (weights / 255).
+//     registers; direct outputs are STG.128; the conv input goes to an f32 tile in shared memory.
+//   phase B (conv): packed FFMA2 (fma.rn.f32x2) on ROW PAIRS (a, a+6) of the 12-row band.  The tile stores tile rows
+//     y and y+6 interleaved -- element (yp, c) is the float2 (x[yp][c], x[yp+6][c]) -- so every FFMA2 operand is an
+//     aligned register pair straight out of an LDS.128 (no re-packing MOVs; the weight is the scalar-broadcast
+//     operand form `R.F32`), thread = 4 pixels x 2 rows x 3 output channels = 12 float2 accumulators: per input
+//     channel 108 FFMA2 + 18 LDS.128 (the scalar version: 216 FFMA + 21 LDS with 4-way conflicts on its edge loads).
 #include "pixel.cuh"
 #include "ring.cuh"
 
@@ -46,7 +50,7 @@ struct FusedParams {
   const float* weights;
   int64_t bank_len;
   SpliceThr thr;
-  float thr_byte;           // kPreSpliceFast: smallest byte value b with b/255 > thr.val (256 = none)
+  uint32_t thr_k, thr_c7;   // kPreSpliceFast: the byte threshold t (smallest b with b/255 > thr.val) as SWAR constants
   float oma, alpha;
   int ops;                  // AUGCL_OP_*
   int aug_shifted;          // chain input: 0 plain, 1 shifted
@@ -80,6 +84,45 @@ __device__ __forceinline__ float4 fin4(float4 v) {
 // chain stage before the conv
 enum { kPreNone = 0, kPreSplice = 1, kPreSpliceFast = 2, kPreOverlay = 3 };
 
+// ---- conv tile: [3 ci][kFPairs row pairs][TROW floats].  Row pair yp holds tile rows yp (lane .x) and yp + kFHalf
+// (lane .y) of the (kFBand + 2)-row band; tile row t = band row t - 1 (halo).  Columns c' = c + 1 (c = -1 .. W) as float2,
+// split into two arrays of 16-byte chunks so that the three LDS.128 of lane q4 (c' = 4q4 .. 4q4+5) are 16 B apart
+// between lanes (conflict-free):  A0[q] = {T[4q], T[4q+1]} at float 4q (q = 0 .. nq),  A1[q] = {T[4q+2], T[4q+3]} at
+// float 4(nq+1) + 4q.  A thread reads A0[q4], A1[q4], A0[q4+1].
+constexpr int kFHalf = kFBand / 2;           // output rows a and a + kFHalf share a thread
+constexpr int kFPairs = kFHalf + 2;        // row pairs per channel
+__host__ __device__ constexpr int tile_row_floats(int W) { return (2 * (W >> 2) + 1) * 4; }
+
+// conv weights are stored pre-multiplied by -log2(e) / 255: acc = -log2(e) * conv(x / 255), so
+// sigmoid(conv) * 255 = 255 / (1 + 2^acc) = rcp(fma(2^acc, 1/255, 1/255)): MUFU.EX2, FFMA, MUFU.RCP.
+constexpr float kConvWScale = -1.4426950408889634f / 255.0f;
+template <bool NORM>
+__device__ __forceinline__ float conv_sigmoid(float acc) {
+  float e, r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(acc));
+  const float d = NORM ? 1.0f + e : fmaf(e, 0.00392156862745098f, 0.00392156862745098f);
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(d));
+  return r;
+}
+
+// Default-threshold splice mask on four u8 pixels at once (one 32-bit word per channel), SWAR on the byte MSBs:
+//   keep = max > min  and not (r == max and g == b)  and  max >= t
+//        = (g != b  or  r < g)  and  (r >= t or g >= t or b >= t)          (g == b: r == max <=> r >= g)
+// K, C7 encode the threshold t in 1 .. 255: c = 256 - t, K = (c & 0x7f) * 0x01010101, C7 = c & 0x80 ? 0x80808080 : 0;
+// x >= t <=> the 8-bit add x + c carries out = maj(x7, c7, carry into bit 7).  Returns 0xff in the bytes to keep.
+__device__ __forceinline__ uint32_t splice_keep_bytes(uint32_t r, uint32_t g, uint32_t b, uint32_t K, uint32_t C7) {
+  const uint32_t L = 0x7f7f7f7fu, H = 0x80808080u;
+  const uint32_t x = g ^ b;
+  const uint32_t ne = ((x & L) + L) | x;                       // bit 7: g != b
+  const uint32_t d = (r | H) - (g & L);                        // bit 7: (r & 0x7f) >= (g & 0x7f); no borrow between bytes
+  const uint32_t lt = (~r & g) | (~(r ^ g) & ~d);              // bit 7: r < g
+  const uint32_t sr = (r & L) + K, sg = (g & L) + K, sb = (b & L) + K;
+  const uint32_t ge = ((r & sr) | (C7 & (r | sr))) | ((g & sg) | (C7 & (g | sg))) | ((b & sb) | (C7 & (b | sb)));
+  uint32_t m;   // replicate each byte's MSB over the byte (prmt's sign-replicate selector bit; __byte_perm documents 3 bits only)
+  asm("prmt.b32 %0, %1, 0, 0xba98;" : "=r"(m) : "r"((ne | lt) & ge));
+  return m;
+}
+
 // PRE, CONV: the aug chain (compile time: every variant is straight-line code, a few hundred SASS instructions
 // instead of one 5 000-instruction kernel that thrashes the instruction cache).  WC: image width (0 = p.sp.W).
 template <int PRE, bool CONV, bool NORM, int WC>
@@ -92,14 +135,15 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
   int* valid = reinterpret_cast<int*>(smem + 256 + 432);              // [4]: stage holds a unit (dynamic schedule)
   uint8_t* stage = smem + kFHeader;                                   // NS x stage_bytes (704 = 16 * 44: 16-B aligned)
   const int NS = p.stages;
-  float* tile = reinterpret_cast<float*>(stage + NS * p.stage_bytes); // [3][kFBand+2][tile_rs]
+  float* tile = reinterpret_cast<float*>(stage + NS * p.stage_bytes); // [3][kFPairs][TROW] (layout above)
   const int tid = threadIdx.x;
   const int H = WC ? WC : p.sp.H, W = WC ? WC : p.sp.W, nq = W >> 2;   // WC != 0: square WC x WC frames
   // fixed thread -> (row slot, 4-pixel group) mapping: no per-task division, constant address increments
   const int RPR = kFThreads / nq;            // rows per round (7 at W = 84)
   const int row0 = tid / nq, q4 = tid - row0 * nq;
   const bool active = row0 < RPR;
-  const int TRS = WC ? ((WC + 8) & ~3) : p.tile_rs;
+  const int TROW = WC ? tile_row_floats(WC) : p.tile_rs;   // floats per tile row pair
+  const int TA1 = (nq + 1) * 4;                            // float offset of chunk array A1 inside a row pair
   constexpr bool kSplice = PRE == kPreSplice || PRE == kPreSpliceFast;
   constexpr bool kBank = PRE != kPreNone;
   constexpr int hal = CONV ? 1 : 0;
@@ -269,7 +313,7 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
     if (CONV && tid < 81) {
       // weights[sample][co][ci][ky][kx] / 255 -> wsm[(ci*9 + ky*3 + kx)*4 + co]
       const int co = tid / 27, tap = tid - co * 27;
-      wsm[tap * 4 + co] = __fdiv_rn(p.weights[(int64_t)m.sample * 81 + tid], 255.0f);
+      wsm[tap * 4 + co] = p.weights[(int64_t)m.sample * 81 + tid] * kConvWScale;
     }
     for (int pr = active ? row0 : trows; pr < trows; pr += RPR) {
       const int r = clampi(m.r0 + pr - hal, 0, H - 1);
@@ -285,58 +329,71 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
         if (own && m.o_plain) store3(m.o_plain, oo, Aw);
         if (own && m.o_shift) { load_shift(r, q4, Ow); store3(m.o_shift, oo, Ow); }
       }
-      float a[3][4], v[3][4];
-#pragma unroll
-      for (int ci = 0; ci < 3; ++ci) {
-        const float4 t4 = bytes_to_float4(Aw[ci]);
-        a[ci][0] = t4.x; a[ci][1] = t4.y; a[ci][2] = t4.z; a[ci][3] = t4.w;
-      }
-      if (kBank) {
-        float g[3][4];
+      float v[3][4];
+      if (PRE == kPreSpliceFast) {
+        // default thresholds (hue = sat = 0): the HSV test of pixel.cuh:hsv_gt only compares, and v -> v/255 is strictly
+        // increasing, so mask and select run on the raw bytes, four pixels per instruction (splice_keep_bytes);
+        // tests/: all 2^24 colours against the float path.
         const int ga = m.gkoff + r * W + 4 * q4;
+        const uint32_t keep = splice_keep_bytes(Aw[0], Aw[1], Aw[2], p.thr_k, p.thr_c7);
 #pragma unroll
         for (int ci = 0; ci < 3; ++ci) {
-          const float4 g4 = bytes_to_float4(*reinterpret_cast<const uint32_t*>(gb + ci * p.bank_stage + ga));
-          g[ci][0] = g4.x; g[ci][1] = g4.y; g[ci][2] = g4.z; g[ci][3] = g4.w;
-        }
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          if (PRE == kPreOverlay) {
-#pragma unroll
-            for (int ci = 0; ci < 3; ++ci) v[ci][j] = overlay_px(a[ci][j], div255(g[ci][j]), p.oma, p.alpha);
-          } else {
-            bool keep;
-            if (PRE == kPreSpliceFast) {
-              // default thresholds (hue = sat = 0) on u8 pixels: the HSV test of pixel.cuh:hsv_gt only compares, and
-              // v -> v/255 is strictly increasing, so it can run on the raw byte values; thr_byte = the smallest
-              // byte whose /255 exceeds val_thres (host).  tests/: all 2^24 colours against the float path.
-              const float mx = fmaxf(fmaxf(a[0][j], a[1][j]), a[2][j]), mn = fminf(fminf(a[0][j], a[1][j]), a[2][j]);
-              keep = mx > mn && !(a[0][j] == mx && a[1][j] == a[2][j]) && mx >= p.thr_byte;
-            } else {
-              keep = splice_keep(div255(a[0][j]), div255(a[1][j]), div255(a[2][j]), p.thr);
-            }
-#pragma unroll
-            for (int ci = 0; ci < 3; ++ci) {
-              const float sel = keep ? a[ci][j] : g[ci][j];
-              // splice returns (x/255 or bg/255) * 255; as conv input the raw byte is the same value to 1 ulp
-              v[ci][j] = CONV ? sel : div255(sel) * 255.0f;
-            }
-          }
+          const uint32_t gw = *reinterpret_cast<const uint32_t*>(gb + ci * p.bank_stage + ga);
+          const float4 t4 = bytes_to_float4((Aw[ci] & keep) | (gw & ~keep));
+          // splice returns (x/255 or bg/255) * 255; as conv input the raw byte is the same value to 1 ulp
+          v[ci][0] = CONV ? t4.x : div255(t4.x) * 255.0f; v[ci][1] = CONV ? t4.y : div255(t4.y) * 255.0f;
+          v[ci][2] = CONV ? t4.z : div255(t4.z) * 255.0f; v[ci][3] = CONV ? t4.w : div255(t4.w) * 255.0f;
         }
       } else {
-#pragma unroll
-        for (int ci = 0; ci < 3; ++ci)
-#pragma unroll
-          for (int j = 0; j < 4; ++j) v[ci][j] = a[ci][j];
-      }
-      if (CONV) {
+        float a[3][4];
 #pragma unroll
         for (int ci = 0; ci < 3; ++ci) {
-          float* trow = tile + (ci * (kFBand + 2) + pr) * TRS;
-          *reinterpret_cast<float4*>(trow + 4 + 4 * q4) = make_float4(v[ci][0], v[ci][1], v[ci][2], v[ci][3]);
-          if (q4 == 0) trow[3] = v[ci][0];
-          if (q4 == nq - 1) trow[4 + W] = v[ci][3];
+          const float4 t4 = bytes_to_float4(Aw[ci]);
+          a[ci][0] = t4.x; a[ci][1] = t4.y; a[ci][2] = t4.z; a[ci][3] = t4.w;
         }
+        if (kBank) {
+          float g[3][4];
+          const int ga = m.gkoff + r * W + 4 * q4;
+#pragma unroll
+          for (int ci = 0; ci < 3; ++ci) {
+            const float4 g4 = bytes_to_float4(*reinterpret_cast<const uint32_t*>(gb + ci * p.bank_stage + ga));
+            g[ci][0] = g4.x; g[ci][1] = g4.y; g[ci][2] = g4.z; g[ci][3] = g4.w;
+          }
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            if (PRE == kPreOverlay) {
+#pragma unroll
+              for (int ci = 0; ci < 3; ++ci) v[ci][j] = overlay_px(a[ci][j], div255(g[ci][j]), p.oma, p.alpha);
+            } else {
+              const bool keep = splice_keep(div255(a[0][j]), div255(a[1][j]), div255(a[2][j]), p.thr);
+#pragma unroll
+              for (int ci = 0; ci < 3; ++ci) {
+                const float sel = keep ? a[ci][j] : g[ci][j];
+                v[ci][j] = CONV ? sel : div255(sel) * 255.0f;
+              }
+            }
+          }
+        } else {
+#pragma unroll
+          for (int ci = 0; ci < 3; ++ci)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) v[ci][j] = a[ci][j];
+        }
+      }
+      if (CONV) {
+        // tile row pr -> lane .x of row pair pr (pr < kFPairs) and / or lane .y of row pair pr - kFHalf (pr >= kFHalf);
+        // pixels 4q4 .. 4q4+3 are columns c' = 4q4+1 .. 4q4+4: A0[q4].hi, A1[q4].lo, A1[q4].hi, A0[q4+1].lo
+        auto put = [&](float* tb) {
+#pragma unroll
+          for (int ci = 0; ci < 3; ++ci) {
+            float* t = tb + ci * kFPairs * TROW;
+            t[2] = v[ci][0]; t[TA1] = v[ci][1]; t[TA1 + 2] = v[ci][2]; t[4] = v[ci][3];
+            if (q4 == 0) t[0] = v[ci][0];              // column -1: replicate
+            if (q4 == nq - 1) t[6] = v[ci][3];         // column W
+          }
+        };
+        if (pr < kFPairs) put(tile + pr * TROW + 4 * q4);
+        if (pr >= kFHalf) put(tile + (pr - kFHalf) * TROW + 4 * q4 + 1);
       } else {
 #pragma unroll
         for (int ci = 0; ci < 3; ++ci)
@@ -348,50 +405,47 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
     if (tid == 0 && kk + NS < nun) issue(kk + NS, s, kFetch);
     // ---------------- phase B: conv on the tile ----------------
     if (CONV) {
-      const int npair = (m.rows + 1) >> 1;
-      for (int rp = active ? row0 : npair; rp < npair; rp += RPR) {
-        const int r = rp * 2;
-        float acc[2][3][4];
+      const int na = min(kFHalf, m.rows);
+      for (int a = active ? row0 : na; a < na; a += RPR) {
+        float2 acc[3][4];   // [co][pixel] = (band row a, band row a + kFHalf)
 #pragma unroll
-        for (int a = 0; a < 2; ++a)
+        for (int co = 0; co < 3; ++co)
 #pragma unroll
-          for (int co = 0; co < 3; ++co)
-#pragma unroll
-            for (int j = 0; j < 4; ++j) acc[a][co][j] = 0.0f;
+          for (int j = 0; j < 4; ++j) acc[co][j] = make_float2(0.0f, 0.0f);
 #pragma unroll 1
         for (int ci = 0; ci < 3; ++ci) {
-          float x[4][6];
-#pragma unroll
-          for (int y = 0; y < 4; ++y) {
-            const float* trow = tile + (ci * (kFBand + 2) + r + y) * TRS + q4 * 4;
-            const float4 a = *reinterpret_cast<const float4*>(trow + 4);
-            x[y][0] = trow[3]; x[y][1] = a.x; x[y][2] = a.y; x[y][3] = a.z; x[y][4] = a.w; x[y][5] = trow[8];
-          }
 #pragma unroll
           for (int ky = 0; ky < 3; ++ky) {
+            const float* rb = tile + ((ci * kFPairs + a + ky) * TROW + 4 * q4);
+            const float4 X0 = *reinterpret_cast<const float4*>(rb);
+            const float4 X1 = *reinterpret_cast<const float4*>(rb + TA1);
+            const float4 X2 = *reinterpret_cast<const float4*>(rb + 4);
+            const float2 xs[6] = {make_float2(X0.x, X0.y), make_float2(X0.z, X0.w), make_float2(X1.x, X1.y),
+                                  make_float2(X1.z, X1.w), make_float2(X2.x, X2.y), make_float2(X2.z, X2.w)};
 #pragma unroll
             for (int kx = 0; kx < 3; ++kx) {
               const float4 wv = *reinterpret_cast<const float4*>(wsm + (ci * 9 + ky * 3 + kx) * 4);
 #pragma unroll
-              for (int a = 0; a < 2; ++a)
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                  acc[a][0][j] = fmaf(x[a + ky][j + kx], wv.x, acc[a][0][j]);
-                  acc[a][1][j] = fmaf(x[a + ky][j + kx], wv.y, acc[a][1][j]);
-                  acc[a][2][j] = fmaf(x[a + ky][j + kx], wv.z, acc[a][2][j]);
-                }
+              for (int j = 0; j < 4; ++j) {
+                acc[0][j] = __ffma2_rn(xs[j + kx], make_float2(wv.x, wv.x), acc[0][j]);
+                acc[1][j] = __ffma2_rn(xs[j + kx], make_float2(wv.y, wv.y), acc[1][j]);
+                acc[2][j] = __ffma2_rn(xs[j + kx], make_float2(wv.z, wv.z), acc[2][j]);
+              }
             }
           }
         }
+        float* orow = m.o_aug + (size_t)(m.r0 + a) * W + 4 * q4;
 #pragma unroll
-        for (int a = 0; a < 2; ++a) {
-          if (r + a >= m.rows) break;
+        for (int co = 0; co < 3; ++co)
+          st_global_f4(reinterpret_cast<float4*>(orow + co * HW),
+                       make_float4(conv_sigmoid<NORM>(acc[co][0].x), conv_sigmoid<NORM>(acc[co][1].x),
+                                   conv_sigmoid<NORM>(acc[co][2].x), conv_sigmoid<NORM>(acc[co][3].x)));
+        if (a + kFHalf < m.rows) {
 #pragma unroll
-          for (int co = 0; co < 3; ++co) {
-            float4* dst = reinterpret_cast<float4*>(m.o_aug + co * HW + (size_t)(m.r0 + r + a) * W) + q4;
-            st_global_f4(dst, fin4<NORM>(make_float4(sigmoid255(acc[a][co][0]), sigmoid255(acc[a][co][1]),
-                                                     sigmoid255(acc[a][co][2]), sigmoid255(acc[a][co][3]))));
-          }
+          for (int co = 0; co < 3; ++co)
+            st_global_f4(reinterpret_cast<float4*>(orow + co * HW + (size_t)kFHalf * W),
+                         make_float4(conv_sigmoid<NORM>(acc[co][0].y), conv_sigmoid<NORM>(acc[co][1].y),
+                                     conv_sigmoid<NORM>(acc[co][2].y), conv_sigmoid<NORM>(acc[co][3].y)));
         }
       }
       __syncthreads();   // tile and wsm are free again
@@ -505,11 +559,15 @@ extern "C" int augcl_ring_sample_fused(augcl_ring* r, const augcl_fused_desc* d,
   if (ops & AUGCL_OP_SPLICE) {
     // default hue/sat thresholds: integer-exact mask on the raw bytes (kernel comment); anything else: float HSV
     pre = (d->hue_thres == 0.0f && d->sat_thres == 0.0f && g_fused_fast_mask.load()) ? kPreSpliceFast : kPreSplice;
-    p.thr_byte = 256.0f;
+    int t = 256;
     for (int b = 255; b >= 0; --b) {
       volatile float q = (float)b / 255.0f;      // IEEE division, as div255 / torch
-      if (q > d->val_thres) p.thr_byte = (float)b; else break;
+      if (q > d->val_thres) t = b; else break;
     }
+    if (t < 1 || t > 255) pre = kPreSplice;      // every / no pixel passes the value test: the float path handles it
+    const uint32_t c = (uint32_t)(256 - t) & 0xffu;
+    p.thr_k = (c & 0x7fu) * 0x01010101u;
+    p.thr_c7 = (c & 0x80u) ? 0x80808080u : 0u;
   }
   p.alpha = d->alpha; p.oma = (float)(1.0 - (double)d->alpha);
   p.ops = ops; p.aug_shifted = d->aug_input == AUGCL_AUG_INPUT_SHIFTED ? 1 : 0;
@@ -537,8 +595,8 @@ extern "C" int augcl_ring_sample_fused(augcl_ring* r, const augcl_fused_desc* d,
   p.plane_stage = ((rows_max * r->W + 30 + 15) & ~15) + 16;
   p.bank_stage = (ops & 7) ? ((((band + halo2) * r->W + 30 + 15) & ~15) + 16) : 0;
   p.stage_bytes = 3 * (p.plane_stage + p.bank_stage);
-  p.tile_rs = (r->W + 8) & ~3;
-  const size_t tile_bytes = has_conv ? 3 * (size_t)(kFBand + 2) * p.tile_rs * sizeof(float) : 0;
+  p.tile_rs = tile_row_floats(r->W);
+  const size_t tile_bytes = has_conv ? 3 * (size_t)kFPairs * p.tile_rs * sizeof(float) : 0;
   // conv chains are issue / barrier bound: 2 stages and the smaller footprint; elementwise chains wait on HBM: deeper
   // (measured, scripts/bench_fused.py --opts: 4 stages x 6 CTAs/SM with a bank, 3 x 7 for plain copies)
   p.stages = g_fused_stages.load() > 0 ? g_fused_stages.load() : (has_conv ? 2 : ((ops & 7) ? 4 : 3));
