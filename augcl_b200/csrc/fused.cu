@@ -27,17 +27,17 @@
 namespace augcl {
 
 std::atomic<int> g_fused_ctas_per_sm{0};   // 0 = auto
-std::atomic<int> g_fused_cost_obs{0};    // 0 = auto
-std::atomic<int> g_fused_cost_next{0};
 std::atomic<int> g_fused_stages{0};      // 0 = auto
-std::atomic<int> g_fused_dynamic{1};     // 1: atomic-ticket unit schedule, 0: static cost partition
+std::atomic<int> g_fused_batch{0};       // units the producer warp decodes side by side (0 = auto)
+std::atomic<int> g_fused_interleave{-1}; // obs / next_obs units alternate in ticket order (-1 = auto: conv chains only)
+std::atomic<int> g_fused_ahead{-1};      // producer fetches the next pass's draws before it issues the current one (-1 = auto)
+std::atomic<int> g_fused_wait_hint{0};   // ns a waiting warp may stay suspended per mbarrier.try_wait (0 = default)
 std::atomic<int> g_fused_band{0};        // 0 = auto (non-conv chains: 14 or 7 rows)
 std::atomic<int> g_fused_fast_mask{1};   // 0: always the float HSV path (A/B and the exhaustive equivalence test)
 
-constexpr int kFHeader = 256 + 432 + 16;   // mbarriers + metas + conv weights + per-stage "holds a unit" flags
+constexpr int kFHeader = 3072;   // mbarriers, per-stage flags and metas, tile metas, conv weights (per stage and per tile)
 constexpr int kFBand = 12;        // conv chains: 12 rows + 2 halo rows = 14 tile rows = two rounds of 7 rows
 constexpr int kFBandNoConv = 14;  // every other chain: 14 rows = two full rounds, 84 = 6 bands
-constexpr int kFThreads = 160;   // 147 = 7 rows x 21 quads work at W = 84: a 14-row tile is exactly two rounds
 
 struct FusedParams {
   SampleParams sp;          // stores, draw sources, scalar gather (sp.out unused)
@@ -56,10 +56,11 @@ struct FusedParams {
   int aug_shifted;          // chain input: 0 plain, 1 shifted
   int k, bands, band;       // frames per stack, bands per frame, rows per band
   int64_t units_obs, units_next;
-  int cost_obs, cost_next;
   int plane_stage, bank_stage, stage_bytes, tile_rs, stages;
-  uint32_t* sched;          // dynamic schedule: {next ticket, CTAs done}; NULL = static cost partition
+  uint32_t* sched;          // unit schedule: {next ticket, CTAs done}
   int normalize;
+  int batch, wait_hint, interleave, ahead;
+  double rcp_bands, rcp_k, rcp_B;   // exact small-divisor division in the producer warp (udiv_small)
 };
 
 struct FusedMeta {
@@ -71,7 +72,7 @@ struct FusedMeta {
   int dy, dx;
   int r0, rows;     // band
   int sample;
-  int pad_;
+  int wkoff;        // conv weights of the sample inside the stage's weight block: float offset 0..3, -1 = read them from global
 };
 
 template <bool NORM>
@@ -123,149 +124,364 @@ __device__ __forceinline__ uint32_t splice_keep_bytes(uint32_t r, uint32_t g, ui
   return m;
 }
 
+// ---- CTA roles (warp-specialised; every hand-over is an mbarrier, there is no CTA-wide barrier after start-up) ----
+//   producer warp (the last one): takes unit tickets, decodes them, stages the conv weights of the unit's sample and starts
+//     the bulk copies of stage s as soon as the A-warps have released it (empty[s]); the ticket atomic and the dependent
+//     index / table loads of unit n+1 run while the other warps work on unit n.
+//   A-warps: wait full[s]; elementwise phase (copy units: next_obs and un-augmented obs; aug units: phase A).  Conv chains
+//     write the conv input into tile[t] (two tiles) after tempty[t], then arrive on tfull[t]; every A-warp releases the
+//     stage (empty[s]) when its own reads are done.
+//   B-warps (conv chains): wait tfull[t]; phase B on tile[t]; arrive on tempty[t].
+// The first round-2 kernel ran both phases on all warps with two __syncthreads per unit: ncu showed 38 % of the warp
+// samples parked on those barriers (24 % on the one after phase B alone, most of it waiting for warp 0, whose lane 0
+// was still decoding the next unit: ~2.9 k cycles per unit), issue slots 48 % busy.
+constexpr int kFWarpsAConv = 4, kFWarpsBConv = 4, kFWarpsAPlain = 8;
+constexpr int kFThreads = 32 * (kFWarpsAConv + kFWarpsBConv + 1);   // = 32 * (kFWarpsAPlain + 1)
+static_assert(kFWarpsAConv + kFWarpsBConv == kFWarpsAPlain, "one block size for every chain");
+constexpr int kFMaxStages = 4;
+
+struct TileMeta {
+  float* o_aug;     // plane 0 of the frame in the augmented output
+  int r0, rows;     // band
+  int valid;        // 0: no more tiles (the B-warps leave)
+  int pad_;
+};
+
+// floor(u / d) for u < 2^31 through d's double reciprocal: (u + 0.5) / d is never within 2^-40 of an integer, so the
+// rounding of the reciprocal and of the product cannot carry it across one.  Three instructions instead of the ~25 of
+// a 32-bit division by a run-time divisor (the producer warp decodes every unit with three of them).
+__device__ __forceinline__ uint32_t udiv_small(uint32_t u, double rcp) {
+  return (uint32_t)__double2uint_rz(((double)u + 0.5) * rcp);
+}
+
 // PRE, CONV: the aug chain (compile time: every variant is straight-line code, a few hundred SASS instructions
 // instead of one 5 000-instruction kernel that thrashes the instruction cache).  WC: image width (0 = p.sp.W).
 template <int PRE, bool CONV, bool NORM, int WC>
-__global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const __grid_constant__ FusedParams p,
-                                                                         const __grid_constant__ InlineDraws<kInlineMax> inl) {
+__global__ void __launch_bounds__(kFThreads, CONV ? 3 : 4)
+ring_sample_fused_kernel(const __grid_constant__ FusedParams p, const __grid_constant__ InlineDraws<kInlineMax> inl) {
   extern __shared__ __align__(128) uint8_t smem[];
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem);                 // <= 4 mbarriers
-  FusedMeta* meta = reinterpret_cast<FusedMeta*>(smem + 32);          // <= 4 metas (4 x 56 B = 224 B)
-  float* wsm = reinterpret_cast<float*>(smem + 256);                  // [27][4] conv weights / 255
-  int* valid = reinterpret_cast<int*>(smem + 256 + 432);              // [4]: stage holds a unit (dynamic schedule)
-  uint8_t* stage = smem + kFHeader;                                   // NS x stage_bytes (704 = 16 * 44: 16-B aligned)
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem);                 // [4] stage s holds a unit (tx bytes) / end marker
+  uint64_t* empty = full + kFMaxStages;                               // [4] every A-warp is done with stage s
+  uint64_t* tfull = full + 2 * kFMaxStages;                           // [2] tile t written by every A-warp
+  uint64_t* tempty = tfull + 2;                                       // [2] tile t read by every B-warp
+  int* valid = reinterpret_cast<int*>(smem + 96);                     // [4]
+  TileMeta* tmeta = reinterpret_cast<TileMeta*>(smem + 128);          // [2]
+  FusedMeta* meta = reinterpret_cast<FusedMeta*>(smem + 192);         // [4] (4 x 56 B)
+  float* wsm = reinterpret_cast<float*>(smem + 448);                  // [2][27][4] conv weights of tile t (scaled)
+  float* wst = reinterpret_cast<float*>(smem + 1312);                 // [4][96] a sample's 81 raw conv weights + <= 3 floats of lead, staged with stage s
+  uint8_t* stage = smem + kFHeader;                                   // NS x stage_bytes
   const int NS = p.stages;
-  float* tile = reinterpret_cast<float*>(stage + NS * p.stage_bytes); // [3][kFPairs][TROW] (layout above)
-  const int tid = threadIdx.x;
+  float* tiles = reinterpret_cast<float*>(stage + NS * p.stage_bytes); // [2][3][kFPairs][TROW] (layout above)
+  constexpr int NAW = CONV ? kFWarpsAConv : kFWarpsAPlain, NBW = CONV ? kFWarpsBConv : 0;
+  constexpr int NTA = NAW * 32, NTB = NBW * 32;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int H = WC ? WC : p.sp.H, W = WC ? WC : p.sp.W, nq = W >> 2;   // WC != 0: square WC x WC frames
-  // fixed thread -> (row slot, 4-pixel group) mapping: no per-task division, constant address increments
-  const int RPR = kFThreads / nq;            // rows per round (7 at W = 84)
-  const int row0 = tid / nq, q4 = tid - row0 * nq;
-  const bool active = row0 < RPR;
   const int TROW = WC ? tile_row_floats(WC) : p.tile_rs;   // floats per tile row pair
   const int TA1 = (nq + 1) * 4;                            // float offset of chunk array A1 inside a row pair
+  const int TILEF = 3 * kFPairs * TROW;
   constexpr bool kSplice = PRE == kPreSplice || PRE == kPreSpliceFast;
   constexpr bool kBank = PRE != kPreNone;
   constexpr int hal = CONV ? 1 : 0;
-
-  // ---- static partition of the cost line [0, T) over the CTAs; a CTA owns the units whose start falls in its range
-  const int64_t T = p.units_obs * p.cost_obs + p.units_next * p.cost_next;
-  const int64_t c0 = T * blockIdx.x / gridDim.x, c1 = T * (blockIdx.x + 1) / gridDim.x;
-  auto first_unit_at = [&](int64_t c) -> int64_t {   // smallest unit whose start cost >= c
-    const int64_t To = p.units_obs * p.cost_obs;
-    if (c <= To) return (c + p.cost_obs - 1) / p.cost_obs;
-    return p.units_obs + (c - To + p.cost_next - 1) / p.cost_next;
-  };
-  const bool dyn = p.sched != nullptr;
-  const int64_t u0 = first_unit_at(c0), u1 = first_unit_at(c1);
-  // dynamic schedule: units are handed out one at a time, in order (heavy obs units first, next_obs copies fill the
-  // tail), by an atomic ticket counter; the loop below then runs until a stage comes back empty
-  const int nun = dyn ? 0x7fffffff : (int)(u1 - u0);
   const uint32_t total_units = (uint32_t)(p.units_obs + p.units_next);
 
   if (tid == 0) {
-    for (int s = 0; s < NS; ++s) mbar_init(&bars[s], 1);
+    for (int s = 0; s < kFMaxStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], NAW); }
+    for (int t = 0; t < 2; ++t) { mbar_init(&tfull[t], NAW); mbar_init(&tempty[t], NBW > 0 ? NBW : 1); }
     mbar_fence_init();
   }
   __syncthreads();
   pdl_wait();
-
-  constexpr uint32_t kFetch = 0xffffffffu;
-  // one lane: decode unit u0+kk (static) / the next ticket (dynamic), write its meta, start its copies into stage s
-  auto issue = [&](int kk, int s, uint32_t ticket) {
-    uint32_t u = (uint32_t)(u0 + kk);          // host: units_obs + units_next < 2^31 -> 32-bit divisions
-    if (dyn) {
-      u = ticket != kFetch ? ticket : atomicAdd(p.sched, 1u);
-      valid[s] = u < total_units;
-      if (u >= total_units) return;
-    }
-    const int t = u >= (uint32_t)p.units_obs ? 1 : 0;
-    if (t) u -= (uint32_t)p.units_obs;
-    const uint32_t fr = u / (uint32_t)p.bands;  // frame row of x.reshape(B*k, 3, H, W)
-    const int band = (int)(u - fr * (uint32_t)p.bands);
-    const int b = (int)(fr / (uint32_t)p.k), f = (int)(fr - (uint32_t)b * (uint32_t)p.k);
-    const int BAND = CONV ? kFBand : p.band;
-    const int r0 = band * BAND, rows = min(BAND, H - r0);
-    const int64_t slot = sample_index(p.sp, inl, b);
-    int dy, dx;
-    sample_offset(p.sp, inl, t, b, dy, dx);
-    const bool want_aug = t == 0 && p.o_aug != nullptr;
-    const bool want_shift = p.o_shift[t] != nullptr;
-    const bool want_plain = p.o_plain[t] != nullptr;
-    // hull of the source rows this unit touches
-    int lo = H, hi = -1;
-    if (want_plain || (want_aug && !p.aug_shifted)) {
-      const int h2 = (want_aug && !p.aug_shifted) ? hal : 0;
-      lo = min(lo, max(r0 - h2, 0)); hi = max(hi, min(r0 + rows - 1 + h2, H - 1));
-    }
-    if (want_shift || (want_aug && p.aug_shifted)) {
-      const int h2 = (want_aug && p.aug_shifted) ? hal : 0;
-      const int a = clampi(max(r0 - h2, 0) + dy, 0, H - 1), z = clampi(min(r0 + rows - 1 + h2, H - 1) + dy, 0, H - 1);
-      lo = min(lo, a); hi = max(hi, z);
-    }
-    const int64_t P = (int64_t)H * W;
-    const size_t fo = (((size_t)b * p.sp.C + (size_t)f * 3) * H) * W;
-    FusedMeta m;
-    m.o_plain = want_plain ? p.o_plain[t] + fo : nullptr;
-    m.o_shift = want_shift ? p.o_shift[t] + fo : nullptr;
-    m.o_aug = want_aug ? p.o_aug + fo : nullptr;
-    m.dy = dy; m.dx = dx; m.r0 = r0; m.rows = rows; m.sample = b; m.pad_ = 0;
-    const uint8_t* src = plane_ptr(p.sp, t, slot, f * 3, P);   // plane 0 of the frame (its 3 planes are contiguous)
-    const uintptr_t a0 = reinterpret_cast<uintptr_t>(src + (int64_t)lo * W) & ~(uintptr_t)15;
-    const uintptr_t a1 = (reinterpret_cast<uintptr_t>(src + (int64_t)(hi + 1) * W) + 15) & ~(uintptr_t)15;
-    m.koff = (int)((intptr_t)reinterpret_cast<uintptr_t>(src) - (intptr_t)a0);
-    const uint32_t sbytes = (uint32_t)(a1 - a0);
-    uint32_t gbytes = 0;
-    uintptr_t g0 = 0;
-    m.gkoff = 0;
-    if (kBank && want_aug) {
-      const int64_t j = kSplice ? (int64_t)(fr % (uint32_t)p.sp.B) : b;   // batch-tiled (splice) vs channel-tiled (overlay)
-      int64_t row = p.bank_idx ? p.bank_idx[j]
-                               : (int64_t)(((uint64_t)philox_word((uint64_t)j, p.bank_subseq, p.sp.seed) * (uint64_t)p.bank_len) >> 32);
-      row = row < 0 ? 0 : (row >= p.bank_len ? p.bank_len - 1 : row);
-      const uint8_t* g = p.bank + row * 3 * P;
-      const int glo = max(r0 - hal, 0), ghi = min(r0 + rows - 1 + hal, H - 1);
-      g0 = reinterpret_cast<uintptr_t>(g + (int64_t)glo * W) & ~(uintptr_t)15;
-      const uintptr_t g1 = (reinterpret_cast<uintptr_t>(g + (int64_t)(ghi + 1) * W) + 15) & ~(uintptr_t)15;
-      m.gkoff = (int)((intptr_t)reinterpret_cast<uintptr_t>(g) - (intptr_t)g0);
-      gbytes = (uint32_t)(g1 - g0);
-    }
-    meta[s] = m;
-    mbar_expect_tx(&bars[s], 3 * (sbytes + gbytes));   // P % 16 == 0: the three planes share lead and length
-    uint8_t* sb = stage + (size_t)s * p.stage_bytes;
-#pragma unroll
-    for (int ci = 0; ci < 3; ++ci)
-      bulk_g2s(sb + ci * p.plane_stage, reinterpret_cast<const void*>(a0 + (uintptr_t)(ci * P)), sbytes, &bars[s]);
-    if (gbytes) {
-      uint8_t* gb = sb + 3 * p.plane_stage;
-#pragma unroll
-      for (int ci = 0; ci < 3; ++ci)
-        bulk_g2s(gb + ci * p.bank_stage, reinterpret_cast<const void*>(g0 + (uintptr_t)(ci * P)), gbytes, &bars[s]);
-    }
-  };
-
-  if (tid < 32) {   // the prologue copies are prepared by NS lanes in parallel (dynamic: NS consecutive tickets, in stage order)
-    uint32_t base = 0;
-    if (dyn) {
-      if (tid == 0) base = atomicAdd(p.sched, (uint32_t)NS);
-      base = __shfl_sync(0xffffffffu, base, 0);
-    }
-    if (tid < NS && tid < nun) issue(tid, tid, base + tid);
-  }
-  if (dyn) __syncthreads();                     // valid[] of the prologue stages
   pdl_launch_dependents();
-  gather_scalars(p.sp, inl);
+  const uint32_t hint = (uint32_t)p.wait_hint;
+  auto WAIT = [&](uint64_t* bar, uint32_t parity) { if (hint) mbar_wait_hint(bar, parity, hint); else mbar_wait(bar, parity); };
 
-  uint32_t phase = 0;
-  int s = 0;
-  auto next_stage = [&]() { if (++s == NS) { s = 0; phase ^= 1; } };
-  for (int kk = 0; kk < nun; ++kk) {
-    if (dyn && !valid[s]) break;   // written >= one __syncthreads ago (NS >= 2 in this mode)
-    mbar_wait(&bars[s], phase);
+  if (warp == NAW + NBW) {
+    // =============================== producer warp ===============================
+    // One pass = G units (G <= NS): lane i < G owns ticket t0 + i.  A pass is prepared in two steps so that no load
+    // latency sits between the release of a stage and the start of its refill:
+    //   fetch  (one pass AHEAD): ticket -> (tensor, sample, frame, band); the draws that are loads -- ring slot, shift
+    //          offsets, background row -- and, by all 32 lanes, three of the 81 conv weights per unit, into registers;
+    //   finish (when the pass is due): address arithmetic on those registers, then for each unit in order: wait for
+    //          the A-warps to release the stage, store the weights, write the meta, start the bulk copies.
+    // Tickets: guided self-scheduling on one global counter.  A CTA claims a CHUNK of consecutive tickets per atomic --
+    // about 1/(2 gridDim) of what is left, between one pass (G tickets: fine balance at the tail) and 8 -- and works
+    // through it in passes of G; the next chunk is requested while the last pass of the current one is handed out, and
+    // the first chunk of every CTA is static (no queue on the counter at launch).  The CTAs thus sweep the unit list as
+    // one narrow window (neighbouring bands of a frame are fetched and written at about the same time: DRAM pages stay
+    // open), with ~1/8 of the atomics.  Measured alternatives: one ticket per atomic -- a same-address atomic is served
+    // every ~11 cycles, so the 43 k claims of a batch-1024 launch took as long as the kernel and every producer saw
+    // ~5 k cycles of queueing per ticket; 3/4 of the passes static round-robin + a dynamic tail -- no queueing, but the
+    // CTAs drift apart over the list and the elementwise chains lost 5-10 % at batch 4096 (0.88 vs 0.97 of HBM peak).
+    const uint32_t G = (uint32_t)p.batch;   // 1 .. NS
+    const uint32_t npair = p.interleave ? (uint32_t)min(p.units_obs, p.units_next) : 0u;
+    const int64_t P = (int64_t)H * W;
+    auto chunk_for = [&](uint32_t claimed) -> uint32_t {   // tickets to claim when `claimed` of them are already handed out
+      const uint32_t left = claimed < total_units ? total_units - claimed : 0u;
+      uint32_t c = left / (2u * gridDim.x);
+      c = c > 8u ? 8u : c;
+      c -= c % G;
+      return c < G ? G : c;
+    };
+    const uint32_t c0 = chunk_for(0);
+    uint32_t cur = blockIdx.x * c0, end = cur + c0;   // static first chunk; the counter hands out dyn0 + ...
+    const uint32_t dyn0 = gridDim.x * c0;
+    // up to two claims in flight (an atomic on the contended counter takes longer than one short pass)
+    uint32_t nb0 = 0, ns0 = 0, nb1 = 0, ns1 = 0, claimed = dyn0;   // claimed: newest known value of the global counter
+    int npend = 0;
+    auto request = [&]() {
+      const uint32_t sz = chunk_for(claimed);
+      uint32_t b = 0;
+      if (lane == 0) b = atomicAdd(p.sched, sz);
+      if (npend == 0) { nb0 = b; ns0 = sz; } else { nb1 = b; ns1 = sz; }
+      ++npend;
+      claimed += sz;   // a lower bound of the counter after this claim (other CTAs claim too)
+    };
+    auto next_pass = [&]() -> uint32_t {   // first ticket of the next pass (warp-uniform)
+      if (cur == end) {
+        if (npend == 0) request();   // (not reached: requests are always outstanding when the local range runs dry)
+        cur = dyn0 + __shfl_sync(0xffffffffu, nb0, 0);
+        end = cur + ns0;
+        if (end > claimed) claimed = end;
+        nb0 = nb1; ns0 = ns1;
+        --npend;
+      }
+      const uint32_t t0 = cur;
+      cur += G;
+      // keep two passes' worth of tickets in hand or on the way
+      while (npend < 2 && (end - cur) + (npend > 0 ? ns0 : 0u) <= G) request();
+      return t0;
+    };
+    struct Draw {
+      int live, dy, dx;
+      int t, band, b, f;
+      uint32_t fr;
+      int64_t slot, row;
+    };
+    auto fetch = [&](uint32_t t0) -> Draw {
+      Draw d{};
+      uint32_t u = t0 + (uint32_t)lane;
+      d.live = (uint32_t)lane < G && u < total_units;
+      if (d.live) {
+        // ticket -> unit: obs and next_obs units alternate (conv chains: the A-warps copy a next_obs band while the
+        // B-warps convolve the obs band before it; neither role has a phase without work), then the longer list's rest
+        if (u < 2u * npair) { d.t = (int)(u & 1u); u >>= 1; }
+        else if (p.interleave) { d.t = p.units_obs > p.units_next ? 0 : 1; u -= npair; }
+        else { d.t = u >= (uint32_t)p.units_obs ? 1 : 0; if (d.t) u -= (uint32_t)p.units_obs; }   // obs units first
+        d.fr = udiv_small(u, p.rcp_bands);   // frame row of x.reshape(B*k, 3, H, W)
+        d.band = (int)(u - d.fr * (uint32_t)p.bands);
+        d.b = (int)udiv_small(d.fr, p.rcp_k);
+        d.f = (int)(d.fr - (uint32_t)d.b * (uint32_t)p.k);
+        const int t = d.t, b = d.b;
+        // raw draws only: nothing here may USE a loaded value (that would stall the fetch on the load)
+        if (p.sp.idx_mode == kSrcInline) d.slot = (int64_t)inl.idx[b];
+        else if (p.sp.idx_mode == AUGCL_SRC_PHILOX)   // same values as augcl_rng_fill_indices(out, B, 0, idx_hi, seed, subseq)
+          d.slot = (int64_t)(((uint64_t)philox_word((uint64_t)b, p.sp.subseq, p.sp.seed) * p.sp.idx_hi) >> 32);
+        else d.slot = p.sp.idx[b];
+        const int om = p.sp.off_mode[t];
+        d.dy = p.sp.pad; d.dx = p.sp.pad;   // kSrcNone: no shift
+        if (om == AUGCL_SRC_PHILOX) {        // same values as augcl_rng_fill_offsets(out, 2B, 0, off_range, seed, subseq+1+t)
+          const uint4 r4 = philox4x32_10((uint64_t)(b >> 1), p.sp.subseq + 1 + t, p.sp.seed);
+          d.dy = (int)__umulhi((b & 1) ? r4.z : r4.x, p.sp.off_range);
+          d.dx = (int)__umulhi((b & 1) ? r4.w : r4.y, p.sp.off_range);
+        } else if (om == kSrcInline) {
+          d.dy = inl.off[t][b][0]; d.dx = inl.off[t][b][1];
+        } else if (om != kSrcNone) {
+          d.dy = p.sp.off[t][2 * b]; d.dx = p.sp.off[t][2 * b + 1];
+        }
+        if (kBank && t == 0 && p.o_aug != nullptr) {
+          // batch-tiled (splice: frame row fr takes background fr mod B) vs channel-tiled (overlay: the sample's)
+          const int64_t j = kSplice ? (int64_t)(d.fr - udiv_small(d.fr, p.rcp_B) * (uint32_t)p.sp.B) : (int64_t)b;
+          d.row = p.bank_idx ? p.bank_idx[j]
+                             : (int64_t)(((uint64_t)philox_word((uint64_t)j, p.bank_subseq, p.sp.seed) * (uint64_t)p.bank_len) >> 32);
+        }
+      }
+      return d;
+    };
+    Draw nx = fetch(next_pass());
+    bool first = true;
+    int s = 0;
+    uint32_t eph = 1;   // parity of the previous phase of empty[s]: passes at once while the ring fills for the first time
+    for (bool more = true; more;) {
+      Draw d;
+      if (p.ahead) {
+        d = nx;
+        if (__any_sync(0xffffffffu, d.live)) nx = fetch(next_pass());   // the next pass's loads travel during this one
+      } else {
+        d = first ? nx : fetch(next_pass());
+        first = false;
+      }
+      FusedMeta m{};
+      uintptr_t a0 = 0, g0 = 0;
+      uint32_t sbytes = 0, gbytes = 0, wbytes = 0;
+      uintptr_t w0 = 0;
+      if (d.live) {
+        const int t = d.t, band = d.band, b = d.b, f = d.f;
+        const int BAND = CONV ? kFBand : p.band;
+        const int r0 = band * BAND, rows = min(BAND, H - r0);
+        const int dy = d.dy - p.sp.pad, dx = d.dx - p.sp.pad;   // source coordinate = output coordinate + (dy, dx), clamped
+        const bool want_aug = t == 0 && p.o_aug != nullptr;
+        const bool want_shift = p.o_shift[t] != nullptr;
+        const bool want_plain = p.o_plain[t] != nullptr;
+        // hull of the source rows this unit touches
+        int lo = H, hi = -1;
+        if (want_plain || (want_aug && !p.aug_shifted)) {
+          const int h2 = (want_aug && !p.aug_shifted) ? hal : 0;
+          lo = min(lo, max(r0 - h2, 0)); hi = max(hi, min(r0 + rows - 1 + h2, H - 1));
+        }
+        if (want_shift || (want_aug && p.aug_shifted)) {
+          const int h2 = (want_aug && p.aug_shifted) ? hal : 0;
+          const int a = clampi(max(r0 - h2, 0) + dy, 0, H - 1), z = clampi(min(r0 + rows - 1 + h2, H - 1) + dy, 0, H - 1);
+          lo = min(lo, a); hi = max(hi, z);
+        }
+        const size_t fo = (((size_t)b * p.sp.C + (size_t)f * 3) * H) * W;
+        m.o_plain = want_plain ? p.o_plain[t] + fo : nullptr;
+        m.o_shift = want_shift ? p.o_shift[t] + fo : nullptr;
+        m.o_aug = want_aug ? p.o_aug + fo : nullptr;
+        m.dy = dy; m.dx = dx; m.r0 = r0; m.rows = rows; m.sample = b; m.wkoff = -1;
+        const uint8_t* src = plane_ptr(p.sp, t, clamp_idx(d.slot, p.sp.capacity), f * 3, P);   // plane 0 of the frame (its 3 planes are contiguous)
+        a0 = reinterpret_cast<uintptr_t>(src + (int64_t)lo * W) & ~(uintptr_t)15;
+        const uintptr_t a1 = (reinterpret_cast<uintptr_t>(src + (int64_t)(hi + 1) * W) + 15) & ~(uintptr_t)15;
+        m.koff = (int)((intptr_t)reinterpret_cast<uintptr_t>(src) - (intptr_t)a0);
+        sbytes = (uint32_t)(a1 - a0);
+        m.gkoff = 0;
+        if (kBank && want_aug) {
+          const int64_t row = d.row < 0 ? 0 : (d.row >= p.bank_len ? p.bank_len - 1 : d.row);
+          const uint8_t* g = p.bank + row * 3 * P;
+          const int glo = max(r0 - hal, 0), ghi = min(r0 + rows - 1 + hal, H - 1);
+          g0 = reinterpret_cast<uintptr_t>(g + (int64_t)glo * W) & ~(uintptr_t)15;
+          const uintptr_t g1 = (reinterpret_cast<uintptr_t>(g + (int64_t)(ghi + 1) * W) + 15) & ~(uintptr_t)15;
+          m.gkoff = (int)((intptr_t)reinterpret_cast<uintptr_t>(g) - (intptr_t)g0);
+          gbytes = (uint32_t)(g1 - g0);
+        }
+        if (CONV && want_aug && b + 1 < p.sp.B) {
+          // weights[sample][co][ci][ky][kx]: the 16-byte hull of the sample's 324 bytes travels with the stage (the last
+          // sample's hull could end past the array: its units read the weights from global in the A-warps instead)
+          const uintptr_t wa = reinterpret_cast<uintptr_t>(p.weights + (int64_t)b * 81);
+          w0 = wa & ~(uintptr_t)15;
+          wbytes = (uint32_t)(((wa + 324 + 15) & ~(uintptr_t)15) - w0);
+          m.wkoff = (int)((wa - w0) >> 2);
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < kFMaxStages; ++i) {
+        if ((uint32_t)i >= G) break;
+        const bool live_i = __shfl_sync(0xffffffffu, d.live, i) != 0;
+        WAIT(&empty[s], eph);        // every A-warp has released the stage's previous unit
+        if (!live_i) {               // end marker
+          if (lane == 0) { valid[s] = 0; mbar_arrive(&full[s]); }
+          more = false;
+          break;
+        }
+        if (lane == i) {
+          meta[s] = m;
+          valid[s] = 1;
+          mbar_expect_tx(&full[s], 3 * (sbytes + gbytes) + wbytes);   // P % 16 == 0: the three planes share lead and length
+          if (wbytes) bulk_g2s(wst + s * 96, reinterpret_cast<const void*>(w0), wbytes, &full[s]);
+          uint8_t* sb = stage + (size_t)s * p.stage_bytes;
+#pragma unroll
+          for (int ci = 0; ci < 3; ++ci)
+            bulk_g2s(sb + ci * p.plane_stage, reinterpret_cast<const void*>(a0 + (uintptr_t)(ci * P)), sbytes, &full[s]);
+          if (gbytes) {
+            uint8_t* gb = sb + 3 * p.plane_stage;
+#pragma unroll
+            for (int ci = 0; ci < 3; ++ci)
+              bulk_g2s(gb + ci * p.bank_stage, reinterpret_cast<const void*>(g0 + (uintptr_t)(ci * P)), gbytes, &full[s]);
+          }
+        }
+        __syncwarp();
+        if (++s == NS) { s = 0; eph ^= 1; }
+      }
+    }
+    if (lane == 0) {
+      // the last CTA to run out of units re-arms the counters for the next launch on this ring (launches of one ring
+      // are stream-ordered, and a PDL successor takes its first ticket only after griddepcontrol.wait)
+      __threadfence();
+      if (atomicAdd(p.sched + 1, 1u) == gridDim.x - 1) {
+        p.sched[0] = 0;
+        p.sched[1] = 0;
+        __threadfence();
+      }
+    }
+    return;
+  }
+
+  if (CONV && warp >= NAW) {
+    // =============================== B-warps: conv on tile t ===============================
+    const int bt = tid - NTA;
+    gather_scalars_part(p.sp, inl, blockIdx.x * NTB + bt, gridDim.x * NTB);
+    const int a0 = bt / nq, q4 = bt - a0 * nq;
+    const int ARPR = NTB / nq;                      // band rows per round (6 at W = 84: one round)
+    const size_t HW = (size_t)H * W;
+    for (int tc = 0;; ++tc) {
+      const int t = tc & 1;
+      WAIT(&tfull[t], (uint32_t)(tc >> 1) & 1u);
+      const TileMeta tm = tmeta[t];
+      if (!tm.valid) break;
+      const float* tile = tiles + t * TILEF;
+      const float* wt = wsm + t * 108;
+      const int na = min(kFHalf, tm.rows);
+      for (int a = a0 < ARPR ? a0 : na; a < na; a += ARPR) {
+        float2 acc[3][4];   // [co][pixel] = (band row a, band row a + kFHalf)
+#pragma unroll
+        for (int co = 0; co < 3; ++co)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) acc[co][j] = make_float2(0.0f, 0.0f);
+#pragma unroll 1
+        for (int ci = 0; ci < 3; ++ci) {
+#pragma unroll
+          for (int ky = 0; ky < 3; ++ky) {
+            const float* rb = tile + ((ci * kFPairs + a + ky) * TROW + 4 * q4);
+            const float4 X0 = *reinterpret_cast<const float4*>(rb);
+            const float4 X1 = *reinterpret_cast<const float4*>(rb + TA1);
+            const float4 X2 = *reinterpret_cast<const float4*>(rb + 4);
+            const float2 xs[6] = {make_float2(X0.x, X0.y), make_float2(X0.z, X0.w), make_float2(X1.x, X1.y),
+                                  make_float2(X1.z, X1.w), make_float2(X2.x, X2.y), make_float2(X2.z, X2.w)};
+#pragma unroll
+            for (int kx = 0; kx < 3; ++kx) {
+              const float4 wv = *reinterpret_cast<const float4*>(wt + (ci * 9 + ky * 3 + kx) * 4);
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                acc[0][j] = __ffma2_rn(xs[j + kx], make_float2(wv.x, wv.x), acc[0][j]);
+                acc[1][j] = __ffma2_rn(xs[j + kx], make_float2(wv.y, wv.y), acc[1][j]);
+                acc[2][j] = __ffma2_rn(xs[j + kx], make_float2(wv.z, wv.z), acc[2][j]);
+              }
+            }
+          }
+        }
+        float* orow = tm.o_aug + (size_t)(tm.r0 + a) * W + 4 * q4;
+#pragma unroll
+        for (int co = 0; co < 3; ++co)
+          st_global_f4(reinterpret_cast<float4*>(orow + co * HW),
+                       make_float4(conv_sigmoid<NORM>(acc[co][0].x), conv_sigmoid<NORM>(acc[co][1].x),
+                                   conv_sigmoid<NORM>(acc[co][2].x), conv_sigmoid<NORM>(acc[co][3].x)));
+        if (a + kFHalf < tm.rows) {
+#pragma unroll
+          for (int co = 0; co < 3; ++co)
+            st_global_f4(reinterpret_cast<float4*>(orow + co * HW + (size_t)kFHalf * W),
+                         make_float4(conv_sigmoid<NORM>(acc[co][0].y), conv_sigmoid<NORM>(acc[co][1].y),
+                                     conv_sigmoid<NORM>(acc[co][2].y), conv_sigmoid<NORM>(acc[co][3].y)));
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty[t]);
+    }
+    return;
+  }
+
+  // =============================== A-warps: elementwise phase ===============================
+  if (!CONV) gather_scalars_part(p.sp, inl, blockIdx.x * NTA + tid, gridDim.x * NTA);
+  // items of a unit = (row, 4-pixel group), handed out flat over the NTA threads: no per-item division
+  const int pr0 = tid / nq, q0 = tid - pr0 * nq;
+  const int dpr = NTA / nq, dq = NTA - dpr * nq;
+  const size_t HW = (size_t)H * W;
+  const int PS = p.plane_stage;
+  int s = 0, tcount = 0;
+  uint32_t fph = 0;
+  for (;;) {
+    WAIT(&full[s], fph);
+    if (!valid[s]) break;
     const FusedMeta m = meta[s];
     const uint8_t* sb = stage + (size_t)s * p.stage_bytes;
-    const size_t HW = (size_t)H * W;
-    const int PS = p.plane_stage;
 
     // one 4-pixel word of each of the 3 planes: un-shifted, and shifted (2 LDS.32 + funnel shift + replicate selector)
     auto load_plain = [&](int r, int q4, uint32_t (&w)[3]) {
@@ -293,29 +509,37 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
 
     if (m.o_aug == nullptr) {
       // ---------------- copy unit (next_obs, or obs without an augmented output) ----------------
-      for (int pr = active ? row0 : m.rows; pr < m.rows; pr += RPR) {
+      for (int pr = pr0, q4 = q0; pr < m.rows;) {
         const int r = m.r0 + pr;
         const size_t oo = (size_t)r * W + 4 * q4;
         uint32_t w[3];
         if (m.o_plain) { load_plain(r, q4, w); store3(m.o_plain, oo, w); }
         if (m.o_shift) { load_shift(r, q4, w); store3(m.o_shift, oo, w); }
+        q4 += dq; pr += dpr;
+        if (q4 >= nq) { q4 -= nq; ++pr; }
       }
-      __syncthreads();   // stage s consumed
-      if (tid == 0 && kk + NS < nun) issue(kk + NS, s, kFetch);
-      next_stage();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[s]);
+      if (++s == NS) { s = 0; fph ^= 1; }
       continue;
     }
 
-    // ---------------- augmented obs unit, phase A: elementwise ----------------
+    // ---------------- augmented obs unit: elementwise chain (conv chains: phase A into tile t) ----------------
     const uint8_t* gb = sb + 3 * PS;
     const int trows = m.rows + 2 * hal;
     const bool aug_sh = p.aug_shifted != 0;
-    if (CONV && tid < 81) {
-      // weights[sample][co][ci][ky][kx] / 255 -> wsm[(ci*9 + ky*3 + kx)*4 + co]
-      const int co = tid / 27, tap = tid - co * 27;
-      wsm[tap * 4 + co] = p.weights[(int64_t)m.sample * 81 + tid] * kConvWScale;
+    const int t = tcount & 1;
+    float* tile = tiles + t * TILEF;
+    if (CONV) {
+      if (tcount >= 2) WAIT(&tempty[t], (uint32_t)((tcount >> 1) - 1) & 1u);   // the B-warps have left tile t
+      if (tid < 81) {   // [co][ci][ky][kx] -> [(ci*9 + ky*3 + kx)*4 + co], scaled for conv_sigmoid
+        const int co = tid / 27, tap = tid - co * 27;
+        const float w = m.wkoff >= 0 ? wst[s * 96 + m.wkoff + tid] : p.weights[(int64_t)m.sample * 81 + tid];
+        wsm[t * 108 + tap * 4 + co] = w * kConvWScale;
+      }
+      if (tid == 0) { TileMeta tm; tm.o_aug = m.o_aug; tm.r0 = m.r0; tm.rows = m.rows; tm.valid = 1; tm.pad_ = 0; tmeta[t] = tm; }
     }
-    for (int pr = active ? row0 : trows; pr < trows; pr += RPR) {
+    for (int pr = pr0, q4 = q0; pr < trows;) {
       const int r = clampi(m.r0 + pr - hal, 0, H - 1);
       const bool own = !CONV || (pr >= 1 && pr <= m.rows);   // halo rows only feed the conv tile
       const size_t oo = (size_t)r * W + 4 * q4;              // offset inside plane 0; planes are H*W apart
@@ -386,10 +610,10 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
         auto put = [&](float* tb) {
 #pragma unroll
           for (int ci = 0; ci < 3; ++ci) {
-            float* t = tb + ci * kFPairs * TROW;
-            t[2] = v[ci][0]; t[TA1] = v[ci][1]; t[TA1 + 2] = v[ci][2]; t[4] = v[ci][3];
-            if (q4 == 0) t[0] = v[ci][0];              // column -1: replicate
-            if (q4 == nq - 1) t[6] = v[ci][3];         // column W
+            float* tp = tb + ci * kFPairs * TROW;
+            tp[2] = v[ci][0]; tp[TA1] = v[ci][1]; tp[TA1 + 2] = v[ci][2]; tp[4] = v[ci][3];
+            if (q4 == 0) tp[0] = v[ci][0];              // column -1: replicate
+            if (q4 == nq - 1) tp[6] = v[ci][3];         // column W
           }
         };
         if (pr < kFPairs) put(tile + pr * TROW + 4 * q4);
@@ -400,67 +624,24 @@ __global__ void __launch_bounds__(kFThreads, 6) ring_sample_fused_kernel(const _
           st_global_f4(reinterpret_cast<float4*>(m.o_aug + oo + ci * HW),
                        fin4<NORM>(make_float4(v[ci][0], v[ci][1], v[ci][2], v[ci][3])));
       }
+      q4 += dq; pr += dpr;
+      if (q4 >= nq) { q4 -= nq; ++pr; }
     }
-    __syncthreads();   // stage s consumed (refill may start), tile + wsm complete
-    if (tid == 0 && kk + NS < nun) issue(kk + NS, s, kFetch);
-    // ---------------- phase B: conv on the tile ----------------
-    if (CONV) {
-      const int na = min(kFHalf, m.rows);
-      for (int a = active ? row0 : na; a < na; a += RPR) {
-        float2 acc[3][4];   // [co][pixel] = (band row a, band row a + kFHalf)
-#pragma unroll
-        for (int co = 0; co < 3; ++co)
-#pragma unroll
-          for (int j = 0; j < 4; ++j) acc[co][j] = make_float2(0.0f, 0.0f);
-#pragma unroll 1
-        for (int ci = 0; ci < 3; ++ci) {
-#pragma unroll
-          for (int ky = 0; ky < 3; ++ky) {
-            const float* rb = tile + ((ci * kFPairs + a + ky) * TROW + 4 * q4);
-            const float4 X0 = *reinterpret_cast<const float4*>(rb);
-            const float4 X1 = *reinterpret_cast<const float4*>(rb + TA1);
-            const float4 X2 = *reinterpret_cast<const float4*>(rb + 4);
-            const float2 xs[6] = {make_float2(X0.x, X0.y), make_float2(X0.z, X0.w), make_float2(X1.x, X1.y),
-                                  make_float2(X1.z, X1.w), make_float2(X2.x, X2.y), make_float2(X2.z, X2.w)};
-#pragma unroll
-            for (int kx = 0; kx < 3; ++kx) {
-              const float4 wv = *reinterpret_cast<const float4*>(wsm + (ci * 9 + ky * 3 + kx) * 4);
-#pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                acc[0][j] = __ffma2_rn(xs[j + kx], make_float2(wv.x, wv.x), acc[0][j]);
-                acc[1][j] = __ffma2_rn(xs[j + kx], make_float2(wv.y, wv.y), acc[1][j]);
-                acc[2][j] = __ffma2_rn(xs[j + kx], make_float2(wv.z, wv.z), acc[2][j]);
-              }
-            }
-          }
-        }
-        float* orow = m.o_aug + (size_t)(m.r0 + a) * W + 4 * q4;
-#pragma unroll
-        for (int co = 0; co < 3; ++co)
-          st_global_f4(reinterpret_cast<float4*>(orow + co * HW),
-                       make_float4(conv_sigmoid<NORM>(acc[co][0].x), conv_sigmoid<NORM>(acc[co][1].x),
-                                   conv_sigmoid<NORM>(acc[co][2].x), conv_sigmoid<NORM>(acc[co][3].x)));
-        if (a + kFHalf < m.rows) {
-#pragma unroll
-          for (int co = 0; co < 3; ++co)
-            st_global_f4(reinterpret_cast<float4*>(orow + co * HW + (size_t)kFHalf * W),
-                         make_float4(conv_sigmoid<NORM>(acc[co][0].y), conv_sigmoid<NORM>(acc[co][1].y),
-                                     conv_sigmoid<NORM>(acc[co][2].y), conv_sigmoid<NORM>(acc[co][3].y)));
-        }
-      }
-      __syncthreads();   // tile and wsm are free again
+    __syncwarp();
+    if (lane == 0) {
+      mbar_arrive(&empty[s]);
+      if (CONV) mbar_arrive(&tfull[t]);
     }
-    next_stage();
+    ++tcount;
+    if (++s == NS) { s = 0; fph ^= 1; }
   }
-  if (dyn && tid == 0) {
-    // the last CTA to run out of units re-arms the counters for the next launch on this ring (launches of one ring
-    // are stream-ordered, and a PDL successor takes its first ticket only after griddepcontrol.wait)
-    __threadfence();
-    if (atomicAdd(p.sched + 1, 1u) == gridDim.x - 1) {
-      p.sched[0] = 0;
-      p.sched[1] = 0;
-      __threadfence();
-    }
+  if (CONV) {
+    // end marker for the B-warps, in the tile slot the next unit would have used
+    const int t = tcount & 1;
+    if (tcount >= 2) WAIT(&tempty[t], (uint32_t)((tcount >> 1) - 1) & 1u);
+    if (tid == 0) tmeta[t].valid = 0;
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&tfull[t]);
   }
 }
 
@@ -580,14 +761,6 @@ extern "C" int augcl_ring_sample_fused(augcl_ring* r, const augcl_fused_desc* d,
   p.units_obs = any_obs ? (int64_t)B * r->k * p.bands : 0;
   p.units_next = any_next ? (int64_t)B * r->k * p.bands : 0;
   AUGCL_REQUIRE(p.units_obs + p.units_next < (1ll << 31), "%s: batch too large", who);
-  // cost of a unit ~ the f32 planes it writes (+ the conv's arithmetic, worth about one and a half more)
-  const int n_obs = (d->out_obs ? 1 : 0) + (d->out_obs_shift ? 1 : 0) + (d->out_obs_aug ? 1 : 0);
-  const int n_next = (d->out_next ? 1 : 0) + (d->out_next_shift ? 1 : 0);
-  p.cost_obs = g_fused_cost_obs.load() > 0 ? g_fused_cost_obs.load()
-                                          : 4 * n_obs + ((ops & AUGCL_OP_CONV) ? 6 : 0) + ((ops & 7) ? 1 : 0) + 1;
-  p.cost_next = g_fused_cost_next.load() > 0 ? g_fused_cost_next.load() : 4 * n_next + 1;
-  if (!any_obs) p.cost_obs = 1;
-  if (!any_next) p.cost_next = 1;
   p.normalize = d->normalize ? 1 : 0;
   const bool has_conv = (ops & AUGCL_OP_CONV) != 0;
   const int halo2 = has_conv ? 2 : 0;
@@ -596,13 +769,21 @@ extern "C" int augcl_ring_sample_fused(augcl_ring* r, const augcl_fused_desc* d,
   p.bank_stage = (ops & 7) ? ((((band + halo2) * r->W + 30 + 15) & ~15) + 16) : 0;
   p.stage_bytes = 3 * (p.plane_stage + p.bank_stage);
   p.tile_rs = tile_row_floats(r->W);
-  const size_t tile_bytes = has_conv ? 3 * (size_t)kFPairs * p.tile_rs * sizeof(float) : 0;
-  // conv chains are issue / barrier bound: 2 stages and the smaller footprint; elementwise chains wait on HBM: deeper
-  // (measured, scripts/bench_fused.py --opts: 4 stages x 6 CTAs/SM with a bank, 3 x 7 for plain copies)
-  p.stages = g_fused_stages.load() > 0 ? g_fused_stages.load() : (has_conv ? 2 : ((ops & 7) ? 4 : 3));
-  while (p.stages > 1 && kFHeader + (size_t)p.stages * p.stage_bytes + tile_bytes > 100 * 1024) --p.stages;
+  const size_t tile_bytes = has_conv ? 2 * 3 * (size_t)kFPairs * p.tile_rs * sizeof(float) : 0;   // two tiles
+  // stage ring depth: the producer warp runs this many units ahead of the A-warps (scripts/bench_fused.py --opts)
+  p.stages = g_fused_stages.load() > 0 ? g_fused_stages.load() : 3;
+  if (p.stages > kFMaxStages) p.stages = kFMaxStages;
+  const size_t budget = (228 * 1024) / (has_conv ? 3 : 4) - 1024;   // 3 (conv) / 4 CTAs per SM
+  while (p.stages > 1 && kFHeader + (size_t)p.stages * p.stage_bytes + tile_bytes > budget) --p.stages;
   const size_t smem = kFHeader + (size_t)p.stages * p.stage_bytes + tile_bytes;
-  p.sched = (g_fused_dynamic.load() && p.stages >= 2) ? r->sched : nullptr;
+  p.sched = r->sched;
+  p.rcp_bands = 1.0 / (double)p.bands; p.rcp_k = 1.0 / (double)p.k; p.rcp_B = 1.0 / (double)B;
+  // conv chains: pairs (an obs band for the B-warps + a next_obs band) so every pass feeds both roles; other chains: one
+  p.batch = g_fused_batch.load() > 0 ? g_fused_batch.load() : (has_conv ? 2 : 1);
+  if (p.batch > p.stages) p.batch = p.stages;
+  p.wait_hint = g_fused_wait_hint.load();
+  p.interleave = g_fused_interleave.load() >= 0 ? g_fused_interleave.load() : ((has_conv || B <= 512) ? 1 : 0);
+  p.ahead = g_fused_ahead.load() >= 0 ? g_fused_ahead.load() : 1;
   if (smem > 200 * 1024) AUGCL_FAIL(AUGCL_ERR_UNSUPPORTED, "%s: geometry needs %zu B of shared memory", who, smem);
 
   DeviceGuard g(r->device);
@@ -664,7 +845,7 @@ extern "C" int augcl_ring_sample_fused(augcl_ring* r, const augcl_fused_desc* d,
     return rc;
   }
   int per_sm = g_fused_ctas_per_sm.load();
-  if (per_sm <= 0) per_sm = ops == 0 ? 7 : 6;
+  if (per_sm <= 0) per_sm = has_conv ? 3 : 4;
   const int fit = (int)((228 * 1024) / (smem + 1024));
   if (per_sm > fit) per_sm = fit < 1 ? 1 : fit;
   int64_t grid = (int64_t)kNumSMs * per_sm;

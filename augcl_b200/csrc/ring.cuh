@@ -126,11 +126,12 @@ __device__ __forceinline__ void sample_offset(const SampleParams& p, const Inl& 
   dy = oy - p.pad; dx = ox - p.pad;
 }
 
+// actions / rewards / not_dones rows (src/utils.py:210-212): a few hundred floats, done by a grid-stride loop over
+// `nthreads` threads of the grid (`first` = this thread's index among them)
 template <class Inl>
-__device__ __forceinline__ void gather_scalars(const SampleParams& p, const Inl& inl) {
-  // actions / rewards / not_dones rows (src/utils.py:210-212): a few hundred floats, done by a grid-stride loop
+__device__ __forceinline__ void gather_scalars_part(const SampleParams& p, const Inl& inl, int first, int nthreads) {
   const int per = p.A + 2;
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < p.B * per; i += gridDim.x * blockDim.x) {
+  for (int i = first; i < p.B * per; i += nthreads) {
     const int b = i / per, j = i - b * per;
     const int64_t s = sample_index(p, inl, b);
     if (j < p.A) {
@@ -141,6 +142,10 @@ __device__ __forceinline__ void gather_scalars(const SampleParams& p, const Inl&
       if (p.out_nd) p.out_nd[b] = p.nd[s];
     }
   }
+}
+template <class Inl>
+__device__ __forceinline__ void gather_scalars(const SampleParams& p, const Inl& inl) {
+  gather_scalars_part(p, inl, blockIdx.x * blockDim.x + threadIdx.x, gridDim.x * blockDim.x);
 }
 
 // First byte of u8 plane `ch` of tensor t (0 obs, 1 next_obs) of ring slot `row`; P = H*W.

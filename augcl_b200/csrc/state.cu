@@ -12,14 +12,15 @@ std::atomic<int> g_sample_pdl{1};
 std::atomic<int> g_sample_band{1};
 std::atomic<int> g_sample_fused_min_batch{256};   // augcl_ring_sample*: batches >= this use the fused.cu kernel (0 = never)
 extern std::atomic<int> g_fused_ctas_per_sm;   // fused.cu
-extern std::atomic<int> g_fused_cost_obs;
-extern std::atomic<int> g_fused_cost_next;
 extern std::atomic<int> g_fused_fast_mask;
 extern std::atomic<int> g_fused_stages;
+extern std::atomic<int> g_fused_batch;
+extern std::atomic<int> g_fused_wait_hint;
+extern std::atomic<int> g_fused_interleave;
+extern std::atomic<int> g_fused_ahead;
 extern std::atomic<int> g_fused_band;
 extern std::atomic<int> g_bil_tma;
 extern std::atomic<int> g_conv_part;
-extern std::atomic<int> g_fused_dynamic;
 static thread_local std::string t_error;
 void set_error(const std::string& msg) { t_error = msg; }
 
@@ -117,13 +118,24 @@ int augcl_set_option(const char* key, const char* value) {
     AUGCL_REQUIRE(v >= 0 && v <= 16, "fused_ctas_per_sm must be in [0,16] (0 = auto)");
     g_fused_ctas_per_sm = v; return AUGCL_OK;
   }
-  if (!strcmp(key, "fused_cost_obs")) { g_fused_cost_obs = atoi(value); return AUGCL_OK; }     // 0 = auto
+  if (!strcmp(key, "fused_cost_obs") || !strcmp(key, "fused_cost_next") || !strcmp(key, "fused_dynamic")) return AUGCL_OK;   // retired (round-1 static schedule)
   if (!strcmp(key, "fused_stages")) {
     int v = atoi(value);
     AUGCL_REQUIRE(v >= 0 && v <= 4, "fused_stages must be in [0,4] (0 = auto)");
     g_fused_stages = v; return AUGCL_OK;
   }
-  if (!strcmp(key, "fused_dynamic")) { g_fused_dynamic = atoi(value) != 0; return AUGCL_OK; }
+  if (!strcmp(key, "fused_batch")) {
+    const int v = atoi(value);
+    AUGCL_REQUIRE(v >= 0 && v <= 4, "fused_batch must be in [0,4] (0 = auto)");
+    g_fused_batch = v; return AUGCL_OK;
+  }
+  if (!strcmp(key, "fused_interleave")) { g_fused_interleave = atoi(value); return AUGCL_OK; }   // -1 = auto
+  if (!strcmp(key, "fused_ahead")) { g_fused_ahead = atoi(value); return AUGCL_OK; }             // -1 = auto
+  if (!strcmp(key, "fused_wait_hint")) {
+    const int v = atoi(value);
+    AUGCL_REQUIRE(v >= 0 && v <= 1000000, "fused_wait_hint must be in [0,1000000] ns (0 = default)");
+    g_fused_wait_hint = v; return AUGCL_OK;
+  }
   if (!strcmp(key, "fused_band")) {
     int v = atoi(value);
     AUGCL_REQUIRE(v >= 0 && v <= 14, "fused_band must be in [0,14] (0 = auto)");
@@ -132,7 +144,6 @@ int augcl_set_option(const char* key, const char* value) {
   if (!strcmp(key, "conv_part")) { g_conv_part = atoi(value); return AUGCL_OK; }   // 0 off, 1 auto, >= 2 parts
   if (!strcmp(key, "bilinear_tma")) { g_bil_tma = atoi(value) != 0; return AUGCL_OK; }
   if (!strcmp(key, "fused_fast_mask")) { g_fused_fast_mask = atoi(value) != 0; return AUGCL_OK; }
-  if (!strcmp(key, "fused_cost_next")) { g_fused_cost_next = atoi(value); return AUGCL_OK; }
   AUGCL_FAIL(AUGCL_ERR_BAD_ARG, "augcl_set_option: unknown key '%s'", key);
 }
 
