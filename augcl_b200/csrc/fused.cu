@@ -31,11 +31,12 @@ std::atomic<int> g_fused_stages{0};      // 0 = auto
 std::atomic<int> g_fused_batch{0};       // units the producer warp decodes side by side (0 = auto)
 std::atomic<int> g_fused_interleave{-1}; // obs / next_obs units alternate in ticket order (-1 = auto: conv chains only)
 std::atomic<int> g_fused_ahead{-1};      // producer fetches the next pass's draws before it issues the current one (-1 = auto)
+std::atomic<int> g_fused_skip{0};        // TIMING EXPERIMENTS ONLY (wrong results): 1 = no conv arithmetic, 2 = no tile stores, 4 = no direct obs stores
 std::atomic<int> g_fused_wait_hint{0};   // ns a waiting warp may stay suspended per mbarrier.try_wait (0 = default)
 std::atomic<int> g_fused_band{0};        // 0 = auto (non-conv chains: 14 or 7 rows)
 std::atomic<int> g_fused_fast_mask{1};   // 0: always the float HSV path (A/B and the exhaustive equivalence test)
 
-constexpr int kFHeader = 3072;   // mbarriers, per-stage flags and metas, tile metas, conv weights (per stage and per tile)
+constexpr int kFHeader = 1664;   // mbarriers, per-stage flags and metas, tile metas, conv weights (per stage and per tile)
 constexpr int kFBand = 12;        // conv chains: 12 rows + 2 halo rows = 14 tile rows = two rounds of 7 rows
 constexpr int kFBandNoConv = 14;  // every other chain: 14 rows = two full rounds, 84 = 6 bands
 
@@ -59,7 +60,7 @@ struct FusedParams {
   int plane_stage, bank_stage, stage_bytes, tile_rs, stages;
   uint32_t* sched;          // unit schedule: {next ticket, CTAs done}
   int normalize;
-  int batch, wait_hint, interleave, ahead;
+  int batch, wait_hint, interleave, ahead, skip;
   double rcp_bands, rcp_k, rcp_B;   // exact small-divisor division in the producer warp (udiv_small)
 };
 
@@ -72,7 +73,7 @@ struct FusedMeta {
   int dy, dx;
   int r0, rows;     // band
   int sample;
-  int wkoff;        // conv weights of the sample inside the stage's weight block: float offset 0..3, -1 = read them from global
+  int pad_[3];
 };
 
 template <bool NORM>
@@ -80,6 +81,26 @@ __device__ __forceinline__ float fin(float v) { return NORM ? div255(v) : v; }  
 template <bool NORM>
 __device__ __forceinline__ float4 fin4(float4 v) {
   return make_float4(fin<NORM>(v.x), fin<NORM>(v.y), fin<NORM>(v.z), fin<NORM>(v.w));
+}
+
+static_assert(sizeof(FusedMeta) == 64, "FusedMeta travels through shared memory as four 16-byte words");
+__device__ __forceinline__ void meta_store(uint4* dst, const FusedMeta& m) {
+  const uint64_t a = reinterpret_cast<uint64_t>(m.o_plain), b = reinterpret_cast<uint64_t>(m.o_shift), c = reinterpret_cast<uint64_t>(m.o_aug);
+  dst[0] = make_uint4((uint32_t)a, (uint32_t)(a >> 32), (uint32_t)b, (uint32_t)(b >> 32));
+  dst[1] = make_uint4((uint32_t)c, (uint32_t)(c >> 32), (uint32_t)m.koff, (uint32_t)m.gkoff);
+  dst[2] = make_uint4((uint32_t)m.dy, (uint32_t)m.dx, (uint32_t)m.r0, (uint32_t)m.rows);
+  dst[3] = make_uint4((uint32_t)m.sample, 0u, 0u, 0u);
+}
+__device__ __forceinline__ FusedMeta meta_load(const uint4* src) {
+  const uint4 v0 = src[0], v1 = src[1], v2 = src[2], v3 = src[3];
+  FusedMeta m;
+  m.o_plain = reinterpret_cast<float*>((uint64_t)v0.x | ((uint64_t)v0.y << 32));
+  m.o_shift = reinterpret_cast<float*>((uint64_t)v0.z | ((uint64_t)v0.w << 32));
+  m.o_aug = reinterpret_cast<float*>((uint64_t)v1.x | ((uint64_t)v1.y << 32));
+  m.koff = (int)v1.z; m.gkoff = (int)v1.w;
+  m.dy = (int)v2.x; m.dx = (int)v2.y; m.r0 = (int)v2.z; m.rows = (int)v2.w;
+  m.sample = (int)v3.x; m.pad_[0] = 0; m.pad_[1] = 0; m.pad_[2] = 0;
+  return m;
 }
 
 // chain stage before the conv
@@ -135,9 +156,11 @@ __device__ __forceinline__ uint32_t splice_keep_bytes(uint32_t r, uint32_t g, ui
 // The first round-2 kernel ran both phases on all warps with two __syncthreads per unit: ncu showed 38 % of the warp
 // samples parked on those barriers (24 % on the one after phase B alone, most of it waiting for warp 0, whose lane 0
 // was still decoding the next unit: ~2.9 k cycles per unit), issue slots 48 % busy.
-constexpr int kFWarpsAConv = 4, kFWarpsBConv = 4, kFWarpsAPlain = 8;
-constexpr int kFThreads = 32 * (kFWarpsAConv + kFWarpsBConv + 1);   // = 32 * (kFWarpsAPlain + 1)
-static_assert(kFWarpsAConv + kFWarpsBConv == kFWarpsAPlain, "one block size for every chain");
+// conv chains: 5 A-warps (the 294 items of a 14-row tile = two rounds of 160), 4 B-warps (126 tasks), 3 CTAs per SM at 64
+// registers; the first split was 4 + 4: ncu showed the A-warps busy 74 % (and waiting for data the rest), the B-warps 59 %.
+constexpr int kFWarpsAConv = 5, kFWarpsBConv = 4, kFWarpsAPlain = 8;
+constexpr int fused_threads(bool conv) { return 32 * ((conv ? kFWarpsAConv + kFWarpsBConv : kFWarpsAPlain) + 1); }
+constexpr int kFMetaRing = 8;   // unit metas live in their own ring: written a pass at a time, before the stages are free
 constexpr int kFMaxStages = 4;
 
 struct TileMeta {
@@ -157,7 +180,7 @@ __device__ __forceinline__ uint32_t udiv_small(uint32_t u, double rcp) {
 // PRE, CONV: the aug chain (compile time: every variant is straight-line code, a few hundred SASS instructions
 // instead of one 5 000-instruction kernel that thrashes the instruction cache).  WC: image width (0 = p.sp.W).
 template <int PRE, bool CONV, bool NORM, int WC>
-__global__ void __launch_bounds__(kFThreads, CONV ? 3 : 4)
+__global__ void __launch_bounds__(fused_threads(CONV), CONV ? 3 : 4)
 ring_sample_fused_kernel(const __grid_constant__ FusedParams p, const __grid_constant__ InlineDraws<kInlineMax> inl) {
   extern __shared__ __align__(128) uint8_t smem[];
   uint64_t* full = reinterpret_cast<uint64_t*>(smem);                 // [4] stage s holds a unit (tx bytes) / end marker
@@ -166,9 +189,8 @@ ring_sample_fused_kernel(const __grid_constant__ FusedParams p, const __grid_con
   uint64_t* tempty = tfull + 2;                                       // [2] tile t read by every B-warp
   int* valid = reinterpret_cast<int*>(smem + 96);                     // [4]
   TileMeta* tmeta = reinterpret_cast<TileMeta*>(smem + 128);          // [2]
-  FusedMeta* meta = reinterpret_cast<FusedMeta*>(smem + 192);         // [4] (4 x 56 B)
-  float* wsm = reinterpret_cast<float*>(smem + 448);                  // [2][27][4] conv weights of tile t (scaled)
-  float* wst = reinterpret_cast<float*>(smem + 1312);                 // [4][96] a sample's 81 raw conv weights + <= 3 floats of lead, staged with stage s
+  uint4* meta = reinterpret_cast<uint4*>(smem + 192);                 // [kFMetaRing][4]: FusedMeta of unit n at slot n % 8
+  float* wsm = reinterpret_cast<float*>(smem + 704);                  // [2][27][4] conv weights of tile t (scaled)
   uint8_t* stage = smem + kFHeader;                                   // NS x stage_bytes
   const int NS = p.stages;
   float* tiles = reinterpret_cast<float*>(stage + NS * p.stage_bytes); // [2][3][kFPairs][TROW] (layout above)
@@ -185,15 +207,13 @@ ring_sample_fused_kernel(const __grid_constant__ FusedParams p, const __grid_con
   const uint32_t total_units = (uint32_t)(p.units_obs + p.units_next);
 
   if (tid == 0) {
-    for (int s = 0; s < kFMaxStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], NAW); }
+    for (int s = 0; s < kFMaxStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], NAW); valid[s] = 1; }   // valid: cleared by the end marker
     for (int t = 0; t < 2; ++t) { mbar_init(&tfull[t], NAW); mbar_init(&tempty[t], NBW > 0 ? NBW : 1); }
     mbar_fence_init();
   }
   __syncthreads();
   pdl_wait();
   pdl_launch_dependents();
-  const uint32_t hint = (uint32_t)p.wait_hint;
-  auto WAIT = [&](uint64_t* bar, uint32_t parity) { if (hint) mbar_wait_hint(bar, parity, hint); else mbar_wait(bar, parity); };
 
   if (warp == NAW + NBW) {
     // =============================== producer warp ===============================
@@ -298,22 +318,16 @@ ring_sample_fused_kernel(const __grid_constant__ FusedParams p, const __grid_con
       return d;
     };
     Draw nx = fetch(next_pass());
-    bool first = true;
+    uint32_t un = 0;   // units issued so far
     int s = 0;
     uint32_t eph = 1;   // parity of the previous phase of empty[s]: passes at once while the ring fills for the first time
     for (bool more = true; more;) {
-      Draw d;
-      if (p.ahead) {
-        d = nx;
-        if (__any_sync(0xffffffffu, d.live)) nx = fetch(next_pass());   // the next pass's loads travel during this one
-      } else {
-        d = first ? nx : fetch(next_pass());
-        first = false;
-      }
+      const Draw d = nx;
+      const uint32_t lmask = __ballot_sync(0xffffffffu, d.live);
+      if (lmask) nx = fetch(next_pass());   // the next pass's loads travel during this one
       FusedMeta m{};
       uintptr_t a0 = 0, g0 = 0;
-      uint32_t sbytes = 0, gbytes = 0, wbytes = 0;
-      uintptr_t w0 = 0;
+      uint32_t sbytes = 0, gbytes = 0;
       if (d.live) {
         const int t = d.t, band = d.band, b = d.b, f = d.f;
         const int BAND = CONV ? kFBand : p.band;
@@ -337,7 +351,7 @@ ring_sample_fused_kernel(const __grid_constant__ FusedParams p, const __grid_con
         m.o_plain = want_plain ? p.o_plain[t] + fo : nullptr;
         m.o_shift = want_shift ? p.o_shift[t] + fo : nullptr;
         m.o_aug = want_aug ? p.o_aug + fo : nullptr;
-        m.dy = dy; m.dx = dx; m.r0 = r0; m.rows = rows; m.sample = b; m.wkoff = -1;
+        m.dy = dy; m.dx = dx; m.r0 = r0; m.rows = rows; m.sample = b; m.pad_[0] = 0; m.pad_[1] = 0; m.pad_[2] = 0;
         const uint8_t* src = plane_ptr(p.sp, t, clamp_idx(d.slot, p.sp.capacity), f * 3, P);   // plane 0 of the frame (its 3 planes are contiguous)
         a0 = reinterpret_cast<uintptr_t>(src + (int64_t)lo * W) & ~(uintptr_t)15;
         const uintptr_t a1 = (reinterpret_cast<uintptr_t>(src + (int64_t)(hi + 1) * W) + 15) & ~(uintptr_t)15;
@@ -353,30 +367,22 @@ ring_sample_fused_kernel(const __grid_constant__ FusedParams p, const __grid_con
           m.gkoff = (int)((intptr_t)reinterpret_cast<uintptr_t>(g) - (intptr_t)g0);
           gbytes = (uint32_t)(g1 - g0);
         }
-        if (CONV && want_aug && b + 1 < p.sp.B) {
-          // weights[sample][co][ci][ky][kx]: the 16-byte hull of the sample's 324 bytes travels with the stage (the last
-          // sample's hull could end past the array: its units read the weights from global in the A-warps instead)
-          const uintptr_t wa = reinterpret_cast<uintptr_t>(p.weights + (int64_t)b * 81);
-          w0 = wa & ~(uintptr_t)15;
-          wbytes = (uint32_t)(((wa + 324 + 15) & ~(uintptr_t)15) - w0);
-          m.wkoff = (int)((wa - w0) >> 2);
-        }
       }
+      // metas of the pass, all lanes at once: slot (n + i) % 8 last held unit n + i - 8, consumed long ago (G + NS <= 8)
+      if (d.live) meta_store(meta + ((un + (uint32_t)lane) % kFMetaRing) * 4, m);
+      un += G;
+      __syncwarp();
 #pragma unroll
       for (int i = 0; i < kFMaxStages; ++i) {
         if ((uint32_t)i >= G) break;
-        const bool live_i = __shfl_sync(0xffffffffu, d.live, i) != 0;
-        WAIT(&empty[s], eph);        // every A-warp has released the stage's previous unit
-        if (!live_i) {               // end marker
+        mbar_wait(&empty[s], eph);   // every A-warp has released the stage's previous unit
+        if (!((lmask >> i) & 1u)) {  // end marker
           if (lane == 0) { valid[s] = 0; mbar_arrive(&full[s]); }
           more = false;
           break;
         }
         if (lane == i) {
-          meta[s] = m;
-          valid[s] = 1;
-          mbar_expect_tx(&full[s], 3 * (sbytes + gbytes) + wbytes);   // P % 16 == 0: the three planes share lead and length
-          if (wbytes) bulk_g2s(wst + s * 96, reinterpret_cast<const void*>(w0), wbytes, &full[s]);
+          mbar_expect_tx(&full[s], 3 * (sbytes + gbytes));   // P % 16 == 0: the three planes share lead and length
           uint8_t* sb = stage + (size_t)s * p.stage_bytes;
 #pragma unroll
           for (int ci = 0; ci < 3; ++ci)
@@ -414,13 +420,13 @@ ring_sample_fused_kernel(const __grid_constant__ FusedParams p, const __grid_con
     const size_t HW = (size_t)H * W;
     for (int tc = 0;; ++tc) {
       const int t = tc & 1;
-      WAIT(&tfull[t], (uint32_t)(tc >> 1) & 1u);
+      mbar_wait(&tfull[t], (uint32_t)(tc >> 1) & 1u);
       const TileMeta tm = tmeta[t];
       if (!tm.valid) break;
       const float* tile = tiles + t * TILEF;
       const float* wt = wsm + t * 108;
       const int na = min(kFHalf, tm.rows);
-      for (int a = a0 < ARPR ? a0 : na; a < na; a += ARPR) {
+      for (int a = (a0 < ARPR && !(p.skip & 1)) ? a0 : na; a < na; a += ARPR) {
         float2 acc[3][4];   // [co][pixel] = (band row a, band row a + kFHalf)
 #pragma unroll
         for (int co = 0; co < 3; ++co)
@@ -476,11 +482,15 @@ ring_sample_fused_kernel(const __grid_constant__ FusedParams p, const __grid_con
   const size_t HW = (size_t)H * W;
   const int PS = p.plane_stage;
   int s = 0, tcount = 0;
-  uint32_t fph = 0;
+  uint32_t fph = 0, un = 0;   // un: units consumed so far
   for (;;) {
-    WAIT(&full[s], fph);
+    mbar_wait(&full[s], fph);
     if (!valid[s]) break;
-    const FusedMeta m = meta[s];
+    const FusedMeta m = meta_load(meta + (un % kFMetaRing) * 4);
+    ++un;
+    // conv weights[sample][co][ci][ky][kx]: one per thread, requested now and stored (scaled, transposed) after the items
+    float wreg = 0.0f;
+    if (CONV && m.o_aug != nullptr && tid < 81) wreg = __ldg(p.weights + (int64_t)m.sample * 81 + tid);
     const uint8_t* sb = stage + (size_t)s * p.stage_bytes;
 
     // one 4-pixel word of each of the 3 planes: un-shifted, and shifted (2 LDS.32 + funnel shift + replicate selector)
@@ -531,17 +541,12 @@ ring_sample_fused_kernel(const __grid_constant__ FusedParams p, const __grid_con
     const int t = tcount & 1;
     float* tile = tiles + t * TILEF;
     if (CONV) {
-      if (tcount >= 2) WAIT(&tempty[t], (uint32_t)((tcount >> 1) - 1) & 1u);   // the B-warps have left tile t
-      if (tid < 81) {   // [co][ci][ky][kx] -> [(ci*9 + ky*3 + kx)*4 + co], scaled for conv_sigmoid
-        const int co = tid / 27, tap = tid - co * 27;
-        const float w = m.wkoff >= 0 ? wst[s * 96 + m.wkoff + tid] : p.weights[(int64_t)m.sample * 81 + tid];
-        wsm[t * 108 + tap * 4 + co] = w * kConvWScale;
-      }
+      if (tcount >= 2) mbar_wait(&tempty[t], (uint32_t)((tcount >> 1) - 1) & 1u);   // the B-warps have left tile t
       if (tid == 0) { TileMeta tm; tm.o_aug = m.o_aug; tm.r0 = m.r0; tm.rows = m.rows; tm.valid = 1; tm.pad_ = 0; tmeta[t] = tm; }
     }
     for (int pr = pr0, q4 = q0; pr < trows;) {
       const int r = clampi(m.r0 + pr - hal, 0, H - 1);
-      const bool own = !CONV || (pr >= 1 && pr <= m.rows);   // halo rows only feed the conv tile
+      const bool own = (!CONV || (pr >= 1 && pr <= m.rows)) && !(p.skip & 4);   // halo rows only feed the conv tile
       const size_t oo = (size_t)r * W + 4 * q4;              // offset inside plane 0; planes are H*W apart
       uint32_t Aw[3], Ow[3];
       if (aug_sh) {
@@ -616,8 +621,11 @@ ring_sample_fused_kernel(const __grid_constant__ FusedParams p, const __grid_con
             if (q4 == nq - 1) tp[6] = v[ci][3];         // column W
           }
         };
-        if (pr < kFPairs) put(tile + pr * TROW + 4 * q4);
-        if (pr >= kFHalf) put(tile + (pr - kFHalf) * TROW + 4 * q4 + 1);
+        // every tile row has one home (branch-free); tile rows kFHalf, kFHalf + 1 are also lane .y of row pairs 0, 1
+        if (!(p.skip & 2)) {
+          put(tile + (pr < kFPairs ? pr * TROW : (pr - kFHalf) * TROW + 1) + 4 * q4);
+          if (pr >= kFHalf && pr < kFPairs) put(tile + (pr - kFHalf) * TROW + 4 * q4 + 1);
+        }
       } else {
 #pragma unroll
         for (int ci = 0; ci < 3; ++ci)
@@ -626,6 +634,10 @@ ring_sample_fused_kernel(const __grid_constant__ FusedParams p, const __grid_con
       }
       q4 += dq; pr += dpr;
       if (q4 >= nq) { q4 -= nq; ++pr; }
+    }
+    if (CONV && tid < 81) {   // -> [(ci*9 + ky*3 + kx)*4 + co], scaled for conv_sigmoid
+      const int co = tid / 27, tap = tid - co * 27;
+      wsm[t * 108 + tap * 4 + co] = wreg * kConvWScale;
     }
     __syncwarp();
     if (lane == 0) {
@@ -638,7 +650,7 @@ ring_sample_fused_kernel(const __grid_constant__ FusedParams p, const __grid_con
   if (CONV) {
     // end marker for the B-warps, in the tile slot the next unit would have used
     const int t = tcount & 1;
-    if (tcount >= 2) WAIT(&tempty[t], (uint32_t)((tcount >> 1) - 1) & 1u);
+    if (tcount >= 2) mbar_wait(&tempty[t], (uint32_t)((tcount >> 1) - 1) & 1u);
     if (tid == 0) tmeta[t].valid = 0;
     __syncwarp();
     if (lane == 0) mbar_arrive(&tfull[t]);
@@ -782,6 +794,7 @@ extern "C" int augcl_ring_sample_fused(augcl_ring* r, const augcl_fused_desc* d,
   p.batch = g_fused_batch.load() > 0 ? g_fused_batch.load() : (has_conv ? 2 : 1);
   if (p.batch > p.stages) p.batch = p.stages;
   p.wait_hint = g_fused_wait_hint.load();
+  p.skip = g_fused_skip.load();
   p.interleave = g_fused_interleave.load() >= 0 ? g_fused_interleave.load() : ((has_conv || B <= 512) ? 1 : 0);
   p.ahead = g_fused_ahead.load() >= 0 ? g_fused_ahead.load() : 1;
   if (smem > 200 * 1024) AUGCL_FAIL(AUGCL_ERR_UNSUPPORTED, "%s: geometry needs %zu B of shared memory", who, smem);
@@ -853,7 +866,7 @@ extern "C" int augcl_ring_sample_fused(augcl_ring* r, const augcl_fused_desc* d,
   if (grid > units) grid = units;
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3((unsigned)grid);
-  cfg.blockDim = dim3(kFThreads);
+  cfg.blockDim = dim3(fused_threads(has_conv));
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];

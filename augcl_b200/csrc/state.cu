@@ -16,6 +16,7 @@ extern std::atomic<int> g_fused_fast_mask;
 extern std::atomic<int> g_fused_stages;
 extern std::atomic<int> g_fused_batch;
 extern std::atomic<int> g_fused_wait_hint;
+extern std::atomic<int> g_fused_skip;
 extern std::atomic<int> g_fused_interleave;
 extern std::atomic<int> g_fused_ahead;
 extern std::atomic<int> g_fused_band;
@@ -131,6 +132,7 @@ int augcl_set_option(const char* key, const char* value) {
   }
   if (!strcmp(key, "fused_interleave")) { g_fused_interleave = atoi(value); return AUGCL_OK; }   // -1 = auto
   if (!strcmp(key, "fused_ahead")) { g_fused_ahead = atoi(value); return AUGCL_OK; }             // -1 = auto
+  if (!strcmp(key, "fused_skip")) { g_fused_skip = atoi(value); return AUGCL_OK; }   // timing experiments only
   if (!strcmp(key, "fused_wait_hint")) {
     const int v = atoi(value);
     AUGCL_REQUIRE(v >= 0 && v <= 1000000, "fused_wait_hint must be in [0,1000000] ns (0 = default)");
