@@ -562,7 +562,7 @@ __global__ void __launch_bounds__(kPartThreads, 4) random_conv_part_kernel(const
     if (tid < 81) {
       // weights[sample][co][ci][ky][kx] / 255 -> wsm[(ci*9 + ky*3 + kx)*4 + co]
       const int co = tid / 27, tap = tid - co * 27;
-      wsm[tap * 4 + co] = __fdiv_rn(weights[(int64_t)sample * 81 + tid], 255.0f);
+      wsm[tap * 4 + co] = weights[(int64_t)sample * 81 + tid] * kConvWScale;   // scaled for conv_sigmoid
     }
     __syncthreads();
     mbar_wait(bar, (uint32_t)n & 1u);
@@ -574,13 +574,14 @@ __global__ void __launch_bounds__(kPartThreads, 4) random_conv_part_kernel(const
       int trow_off[4];
 #pragma unroll
       for (int y = 0; y < 4; ++y) trow_off[y] = (clampi(r0 + r + y - 1, 0, h - 1) - lo) * w + q4 * 4;
-      float acc[2][3][4];
+      // output channels 0 and 1 share one packed FFMA2 per (pixel, tap): the weight pair (w0, w1) is an aligned register
+      // pair out of the LDS.128, the pixel is FFMA2's scalar-broadcast operand -- no re-packing; channel 2 is a plain FFMA
+      float2 acc01[2][4];
+      float acc2[2][4];
 #pragma unroll
       for (int a = 0; a < 2; ++a)
 #pragma unroll
-        for (int co = 0; co < 3; ++co)
-#pragma unroll
-          for (int j = 0; j < 4; ++j) acc[a][co][j] = 0.0f;
+        for (int j = 0; j < 4; ++j) { acc01[a][j] = make_float2(0.0f, 0.0f); acc2[a][j] = 0.0f; }
 #pragma unroll 1
       for (int ci = 0; ci < 3; ++ci) {
         const float* pl = tile + ci * (R + 2) * w;
@@ -601,9 +602,9 @@ __global__ void __launch_bounds__(kPartThreads, 4) random_conv_part_kernel(const
             for (int a = 0; a < 2; ++a)
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
-                acc[a][0][j] = fmaf(x[a + ky][j + kx], wv.x, acc[a][0][j]);
-                acc[a][1][j] = fmaf(x[a + ky][j + kx], wv.y, acc[a][1][j]);
-                acc[a][2][j] = fmaf(x[a + ky][j + kx], wv.z, acc[a][2][j]);
+                const float xv = x[a + ky][j + kx];
+                acc01[a][j] = __ffma2_rn(make_float2(xv, xv), make_float2(wv.x, wv.y), acc01[a][j]);
+                acc2[a][j] = fmaf(xv, wv.z, acc2[a][j]);
               }
           }
         }
@@ -611,12 +612,14 @@ __global__ void __launch_bounds__(kPartThreads, 4) random_conv_part_kernel(const
 #pragma unroll
       for (int a = 0; a < 2; ++a) {
         if (r + a >= rows) break;
-#pragma unroll
-        for (int co = 0; co < 3; ++co) {
-          float4* dst = reinterpret_cast<float4*>(out + (((int64_t)frame * 3 + co) * h + (r0 + r + a)) * w) + q4;
-          st_global_f4(dst, make_float4(sigmoid255(acc[a][co][0]), sigmoid255(acc[a][co][1]), sigmoid255(acc[a][co][2]),
-                                        sigmoid255(acc[a][co][3])));
-        }
+        float4* dst = reinterpret_cast<float4*>(out + (((int64_t)frame * 3) * h + (r0 + r + a)) * w) + q4;
+        const int64_t pl4 = (int64_t)h * w / 4;
+        st_global_f4(dst, make_float4(conv_sigmoid<false>(acc01[a][0].x), conv_sigmoid<false>(acc01[a][1].x),
+                                      conv_sigmoid<false>(acc01[a][2].x), conv_sigmoid<false>(acc01[a][3].x)));
+        st_global_f4(dst + pl4, make_float4(conv_sigmoid<false>(acc01[a][0].y), conv_sigmoid<false>(acc01[a][1].y),
+                                            conv_sigmoid<false>(acc01[a][2].y), conv_sigmoid<false>(acc01[a][3].y)));
+        st_global_f4(dst + 2 * pl4, make_float4(conv_sigmoid<false>(acc2[a][0]), conv_sigmoid<false>(acc2[a][1]),
+                                                conv_sigmoid<false>(acc2[a][2]), conv_sigmoid<false>(acc2[a][3])));
       }
     }
   }

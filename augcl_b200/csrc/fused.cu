@@ -115,18 +115,6 @@ constexpr int kFHalf = kFBand / 2;           // output rows a and a + kFHalf sha
 constexpr int kFPairs = kFHalf + 2;        // row pairs per channel
 __host__ __device__ constexpr int tile_row_floats(int W) { return (2 * (W >> 2) + 1) * 4; }
 
-// conv weights are stored pre-multiplied by -log2(e) / 255: acc = -log2(e) * conv(x / 255), so
-// sigmoid(conv) * 255 = 255 / (1 + 2^acc) = rcp(fma(2^acc, 1/255, 1/255)): MUFU.EX2, FFMA, MUFU.RCP.
-constexpr float kConvWScale = -1.4426950408889634f / 255.0f;
-template <bool NORM>
-__device__ __forceinline__ float conv_sigmoid(float acc) {
-  float e, r;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(acc));
-  const float d = NORM ? 1.0f + e : fmaf(e, 0.00392156862745098f, 0.00392156862745098f);
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(d));
-  return r;
-}
-
 // Default-threshold splice mask on four u8 pixels at once (one 32-bit word per channel), SWAR on the byte MSBs:
 //   keep = max > min  and not (r == max and g == b)  and  max >= t
 //        = (g != b  or  r < g)  and  (r >= t or g >= t or b >= t)          (g == b: r == max <=> r >= g)

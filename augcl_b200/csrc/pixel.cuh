@@ -16,6 +16,18 @@ __device__ __forceinline__ float sigmoid255(float v) {
   return r * 255.0f;
 }
 
+// conv weights are stored pre-multiplied by -log2(e) / 255: acc = -log2(e) * conv(x / 255), so
+// sigmoid(conv) * 255 = 255 / (1 + 2^acc) = rcp(fma(2^acc, 1/255, 1/255)): MUFU.EX2, FFMA, MUFU.RCP.
+constexpr float kConvWScale = -1.4426950408889634f / 255.0f;
+template <bool NORM>
+__device__ __forceinline__ float conv_sigmoid(float acc) {
+  float e, r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(acc));
+  const float d = NORM ? 1.0f + e : fmaf(e, 0.00392156862745098f, 0.00392156862745098f);
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(d));
+  return r;
+}
+
 // x / 255 correctly rounded (== __fdiv_rn(x, 255.0f) for every x whose quotient is a normal float) in three
 // FP ops: Markstein's correction of q0 = x * fl(1/255) by the exact remainder.  tests/ checks it against IEEE
 // division over all integers 0..255 and 2^24 random floats.
