@@ -36,6 +36,7 @@ class FusedDesc(C.Structure):
         ("bank", _p), ("bank_len", _i64), ("bank_idx", _p), ("conv_weights", _p),
         ("hue_thres", _f), ("sat_thres", _f), ("val_thres", _f), ("alpha", _f),
         ("bank_subsequence", _u64),
+        ("conv_subsequence", _u64),
     ]
 
 

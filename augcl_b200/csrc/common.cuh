@@ -102,6 +102,18 @@ __device__ __forceinline__ uint4 philox4x32_10(uint64_t blk, uint64_t subseq, ui
   return make_uint4(c0, c1, c2, c3);
 }
 
+// Box-Muller on an exactly representable pair: u1 in (0,1] from w0, u2 in [0,1) from w1 (24 bits each).
+// One definition for augcl_rng_fill_normal and the in-kernel conv-weight draw of the fused sampler: same values.
+__device__ __forceinline__ void normal_pair(uint32_t w0, uint32_t w1, float& n_cos, float& n_sin) {
+  const float u1 = (float)((w0 >> 8) + 1u) * (1.0f / 16777216.0f);
+  const float u2 = (float)(w1 >> 8) * (1.0f / 16777216.0f);
+  const float rad = sqrtf(-2.0f * logf(u1));
+  float sn, cs;
+  sincospif(2.0f * u2, &sn, &cs);
+  n_cos = rad * cs;
+  n_sin = rad * sn;
+}
+
 // ---- mbarrier + 1-D bulk copy (TMA engine, SASS: UBLKCP) ----
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 

@@ -48,6 +48,7 @@ struct FusedParams {
   const uint8_t* bank;
   const int64_t* bank_idx;
   uint64_t bank_subseq;     // bank_idx == nullptr: rows drawn here, same values as augcl_rng_fill_indices
+  uint64_t conv_subseq;     // weights == nullptr: conv weights drawn here, same values as augcl_rng_fill_normal
   const float* weights;
   int64_t bank_len;
   SpliceThr thr;
@@ -155,7 +156,7 @@ struct TileMeta {
   float* o_aug;     // plane 0 of the frame in the augmented output
   int r0, rows;     // band
   int valid;        // 0: no more tiles (the B-warps leave)
-  int pad_;
+  int sample;
 };
 
 // floor(u / d) for u < 2^31 through d's double reciprocal: (u + 0.5) / d is never within 2^-40 of an integer, so the
@@ -413,6 +414,19 @@ ring_sample_fused_kernel(const __grid_constant__ FusedParams p, const __grid_con
       if (!tm.valid) break;
       const float* tile = tiles + t * TILEF;
       const float* wt = wsm + t * 108;
+      if (p.weights == nullptr) {
+        // the sample's 81 N(0,1) weights, element e = 81 * sample + i of the stream augcl_rng_fill_normal(.., seed,
+        // conv_subseq) writes: Philox block e / 4, Box-Muller pair (e % 4) / 2, cos for even e, sin for odd
+        if (bt < 81) {
+          const uint64_t e = (uint64_t)tm.sample * 81u + (uint64_t)bt;
+          const uint4 r4 = philox4x32_10(e >> 2, p.conv_subseq, p.sp.seed);
+          float nc, ns;
+          if (e & 2) normal_pair(r4.z, r4.w, nc, ns); else normal_pair(r4.x, r4.y, nc, ns);
+          const int co = bt / 27, tap = bt - co * 27;
+          wsm[t * 108 + tap * 4 + co] = ((e & 1) ? ns : nc) * kConvWScale;
+        }
+        asm volatile("bar.sync 1, %0;" ::"n"(NTB) : "memory");   // the B-warps only
+      }
       const int na = min(kFHalf, tm.rows);
       for (int a = (a0 < ARPR && !(p.skip & 1)) ? a0 : na; a < na; a += ARPR) {
         float2 acc[3][4];   // [co][pixel] = (band row a, band row a + kFHalf)
@@ -478,7 +492,7 @@ ring_sample_fused_kernel(const __grid_constant__ FusedParams p, const __grid_con
     ++un;
     // conv weights[sample][co][ci][ky][kx]: one per thread, requested now and stored (scaled, transposed) after the items
     float wreg = 0.0f;
-    if (CONV && m.o_aug != nullptr && tid < 81) wreg = __ldg(p.weights + (int64_t)m.sample * 81 + tid);
+    if (CONV && p.weights != nullptr && m.o_aug != nullptr && tid < 81) wreg = __ldg(p.weights + (int64_t)m.sample * 81 + tid);
     const uint8_t* sb = stage + (size_t)s * p.stage_bytes;
 
     // one 4-pixel word of each of the 3 planes: un-shifted, and shifted (2 LDS.32 + funnel shift + replicate selector)
@@ -530,7 +544,7 @@ ring_sample_fused_kernel(const __grid_constant__ FusedParams p, const __grid_con
     float* tile = tiles + t * TILEF;
     if (CONV) {
       if (tcount >= 2) mbar_wait(&tempty[t], (uint32_t)((tcount >> 1) - 1) & 1u);   // the B-warps have left tile t
-      if (tid == 0) { TileMeta tm; tm.o_aug = m.o_aug; tm.r0 = m.r0; tm.rows = m.rows; tm.valid = 1; tm.pad_ = 0; tmeta[t] = tm; }
+      if (tid == 0) { TileMeta tm; tm.o_aug = m.o_aug; tm.r0 = m.r0; tm.rows = m.rows; tm.valid = 1; tm.sample = m.sample; tmeta[t] = tm; }
     }
     for (int pr = pr0, q4 = q0; pr < trows;) {
       const int r = clampi(m.r0 + pr - hal, 0, H - 1);
@@ -623,7 +637,7 @@ ring_sample_fused_kernel(const __grid_constant__ FusedParams p, const __grid_con
       q4 += dq; pr += dpr;
       if (q4 >= nq) { q4 -= nq; ++pr; }
     }
-    if (CONV && tid < 81) {   // -> [(ci*9 + ky*3 + kx)*4 + co], scaled for conv_sigmoid
+    if (CONV && p.weights != nullptr && tid < 81) {   // -> [(ci*9 + ky*3 + kx)*4 + co], scaled for conv_sigmoid
       const int co = tid / 27, tap = tid - co * 27;
       wsm[t * 108 + tap * 4 + co] = wreg * kConvWScale;
     }
@@ -700,7 +714,6 @@ extern "C" int augcl_ring_sample_fused(augcl_ring* r, const augcl_fused_desc* d,
       AUGCL_REQUIRE(d->bank && d->bank_len > 0 && d->bank_len <= (1ll << 32), "%s: splice / overlay need bank and bank_len", who);
       if (!aligned(d->bank, 16)) AUGCL_FAIL(AUGCL_ERR_BAD_ALIGN, "%s: bank must be 16-byte aligned", who);
     }
-    if (ops & AUGCL_OP_CONV) AUGCL_REQUIRE(d->conv_weights, "%s: CONV needs conv_weights", who);
   }
   if (r->cpf != 3) AUGCL_FAIL(AUGCL_ERR_UNSUPPORTED, "%s: needs RGB frames (c_per_frame == 3)", who);
   if ((r->W & 3) || ((r->H * r->W) & 15) || r->W > 128 || r->W < 8)
@@ -732,7 +745,7 @@ extern "C" int augcl_ring_sample_fused(augcl_ring* r, const augcl_fused_desc* d,
   p.o_plain[0] = d->out_obs; p.o_plain[1] = d->out_next;
   p.o_shift[0] = d->out_obs_shift; p.o_shift[1] = d->out_next_shift;
   p.o_aug = d->out_obs_aug;
-  p.bank = d->bank; p.bank_idx = d->bank_idx; p.bank_subseq = d->bank_subsequence; p.bank_len = d->bank_len; p.weights = d->conv_weights;
+  p.bank = d->bank; p.bank_idx = d->bank_idx; p.bank_subseq = d->bank_subsequence; p.conv_subseq = d->conv_subsequence; p.bank_len = d->bank_len; p.weights = d->conv_weights;
   p.thr = SpliceThr{d->hue_thres, d->sat_thres, d->val_thres, (ops & AUGCL_OP_CS_SPLICE) ? AUGCL_CS_SPLICE : AUGCL_SPLICE};
   int pre = kPreNone;
   if (ops & AUGCL_OP_OVERLAY) pre = kPreOverlay;

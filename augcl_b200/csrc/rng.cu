@@ -30,15 +30,11 @@ __global__ void __launch_bounds__(256) fill_normal_kernel(float* out, int64_t co
     const uint32_t wds[4] = {r.x, r.y, r.z, r.w};
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
-      // Box-Muller on an exactly representable pair: u1 in (0,1], u2 in [0,1)
-      const float u1 = (float)((wds[2 * j] >> 8) + 1u) * (1.0f / 16777216.0f);
-      const float u2 = (float)(wds[2 * j + 1] >> 8) * (1.0f / 16777216.0f);
-      const float rad = sqrtf(-2.0f * logf(u1));
-      float sn, cs;
-      sincospif(2.0f * u2, &sn, &cs);
+      float nc, ns;
+      normal_pair(wds[2 * j], wds[2 * j + 1], nc, ns);
       const int64_t e = b * 4 + 2 * j;
-      if (e < count) out[e] = rad * cs;
-      if (e + 1 < count) out[e + 1] = rad * sn;
+      if (e < count) out[e] = nc;
+      if (e + 1 < count) out[e + 1] = ns;
     }
   }
 }

@@ -743,15 +743,15 @@ class ReplayBuffer(object):
                         d.val_thres = float(prm.get("val_thres", dflt[2]))
                 if "conv" in keys:
                     if weights is None:
-                        wt = torch.empty((B, 3, 3, 3, 3), dtype=torch.float32, device=dev)
-                        L.call("augcl_rng_fill_normal", wt.data_ptr(), wt.numel(), augmentations._seed,
-                               augmentations._next_subsequence(), _raw_stream(self._dev_index))
+                        # drawn inside the kernel: the values augcl_rng_fill_normal would write for this subsequence
+                        d.conv_weights = None
+                        d.conv_subsequence = augmentations._next_subsequence()
                     else:
                         wt = torch.as_tensor(weights).to(device=dev, dtype=torch.float32).contiguous()
                         if tuple(wt.shape) != (B, 3, 3, 3, 3):
                             raise ValueError(f"sample_fused: weights must be ({B},3,3,3,3), got {tuple(wt.shape)}")
-                    d.conv_weights = wt.data_ptr()
-                    keep.append(wt)
+                        d.conv_weights = wt.data_ptr()
+                        keep.append(wt)
             rc = L.lib().augcl_ring_sample_fused(self._ring, C.byref(d), _raw_stream(self._dev_index))
             if rc != 0:
                 e = L.lib().augcl_last_error().decode(errors="replace")
@@ -1043,8 +1043,8 @@ class FastSampler(object):
 class FastFusedSampler(object):
     """``sample_augcl`` / ``sample_svea_aug`` with the per-call Python work taken out (batch <= 256): fixed output tensors,
     a cached ``augcl_fused_desc``, the host indices by value in the launch.  Per step: the bank-row and conv-weight draws
-    (bank rows inside the kernel, conv weights by one small Philox launch; the same subsequences ``sample_fused`` uses) and
-    ONE fused sample kernel.
+    (both inside the kernel; the same Philox subsequences ``sample_fused`` uses) and ONE fused sample kernel -- one launch
+    per update.
 
         fs = FastFusedSampler(buf, kind="augcl", data_aug="splice-conv")          # once
         obs_shift, obs_aug, action, reward, next_obs, not_done = fs.sample()      # every update (src/algorithms/augcl.py:69-72)
@@ -1082,7 +1082,7 @@ class FastFusedSampler(object):
             ops |= ReplayBuffer._FUSED_OPS[k]
         d.aug_ops = ops
         d.aug_input = L.AUG_INPUT_SHIFTED if kind == "svea_aug" else L.AUG_INPUT_PLAIN
-        self._rows = self._wt = None
+        self._rows = None
         pre = next((k for k in keys if k != "conv"), None)
         if pre is not None:
             prm = aug_params.get(pre, {})
@@ -1099,11 +1099,9 @@ class FastFusedSampler(object):
                 d.hue_thres = float(prm.get("hue_thres", dflt[0]))
                 d.sat_thres = float(prm.get("sat_thres", dflt[1]))
                 d.val_thres = float(prm.get("val_thres", dflt[2]))
-        if "conv" in keys:
-            self._wt = torch.empty((B, 3, 3, 3, 3), dtype=torch.float32, device=dev)
-            d.conv_weights = self._wt.data_ptr()
+        self._conv = "conv" in keys   # weights are drawn inside the kernel (conv_weights NULL)
         lib = L.lib()
-        self._fill_idx, self._fill_normal, self._fused = lib.augcl_rng_fill_indices, lib.augcl_rng_fill_normal, lib.augcl_ring_sample_fused
+        self._fill_idx, self._fused = lib.augcl_rng_fill_indices, lib.augcl_ring_sample_fused
         self._dref = C.byref(d)
         self._dev_index = buf._dev_index
 
@@ -1125,10 +1123,9 @@ class FastFusedSampler(object):
         rc = 0
         if self._rows is not None:
             d.bank_subsequence = augmentations._next_subsequence()
-        if self._wt is not None:
-            rc = self._fill_normal(self._wt.data_ptr(), self.B * 81, d.seed, augmentations._next_subsequence(), st)
-        if rc == 0:
-            rc = self._fused(buf._ring, self._dref, st)
+        if self._conv:
+            d.conv_subsequence = augmentations._next_subsequence()
+        rc = self._fused(buf._ring, self._dref, st)
         if rc != 0:
             raise L.AugclError("augcl_ring_sample_fused", rc, L.lib().augcl_last_error().decode(errors="replace"))
         return self.out

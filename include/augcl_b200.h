@@ -237,10 +237,12 @@ typedef struct augcl_fused_desc {
                               /* uses bank_idx[(s*k+f) mod B] for frame f (the reference's tiling quirks).       */
                               /* NULL = drawn in the kernel: the values augcl_rng_fill_indices(out, B, 0,        */
                               /* bank_len, seed, bank_subsequence) would write (no extra launch)                 */
-  const float* conv_weights;  /* device f32 [B,3,3,3,3] (CONV)                                                   */
+  const float* conv_weights;  /* device f32 [B,3,3,3,3] (CONV).  NULL = drawn in the kernel: the values             */
+                              /* augcl_rng_fill_normal(out, B*81, seed, conv_subsequence) would write               */
   float hue_thres, sat_thres, val_thres;   /* splice thresholds (src/augmentations.py:295 / :309)               */
   float alpha;                /* overlay alpha (0.5 in the reference)                                            */
   uint64_t bank_subsequence;  /* Philox subsequence of the in-kernel bank row draw (bank_idx == NULL)            */
+  uint64_t conv_subsequence;  /* Philox subsequence of the in-kernel conv weight draw (conv_weights == NULL)     */
 } augcl_fused_desc;
 
 int augcl_ring_sample_fused(augcl_ring* ring, const augcl_fused_desc* desc, augcl_stream stream);

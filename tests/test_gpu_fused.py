@@ -239,6 +239,36 @@ def test_fast_splice_mask_equals_float_hsv_on_all_colours(U, A):
         A.set_background_bank(None)
 
 
+def test_in_kernel_conv_weights_equal_explicit_weights(U, A):
+    """desc.conv_weights == NULL: the 81 N(0,1) weights per sample are drawn inside the fused kernel (by the B-warps) and
+    are the values augcl_rng_fill_normal(out, B*81, seed, conv_subsequence) writes -- AugCL's update is ONE launch."""
+    from augcl_b200 import _lib as L
+    S, cap, B = 84, 90, 23
+    buf = U.ReplayBuffer((9, S, S), (4,), cap, B)
+    buf.fill_synthetic(seed=5)
+    bank = torch.randint(0, 256, (11, 3, S, S), dtype=torch.uint8, device="cuda")
+    A.set_background_bank(bank)
+    try:
+        idxs = np.random.RandomState(8).randint(0, cap, size=B)
+        off = {"obs": np.random.RandomState(9).randint(0, 9, (B, 2))}
+        rows = torch.from_numpy(np.random.RandomState(10).randint(0, 11, size=B)).cuda()
+        for chain, fn in (("splice-conv", "sample_augcl"), ("conv", "sample_svea_aug")):
+            A.seed(33)
+            n0 = L.lib().augcl_launch_count()
+            got = getattr(buf, fn)(idxs=idxs, data_aug=chain, offsets=off, bank_idx=rows)
+            assert L.lib().augcl_launch_count() - n0 == 1, "one launch per update"
+            # the call reserves subsequences 0..2 for its own draws; explicit bank rows take none; the weights take 3
+            wt = torch.empty((B, 3, 3, 3, 3), device="cuda")
+            L.call("augcl_rng_fill_normal", wt.data_ptr(), wt.numel(), 33, 3, torch.cuda.current_stream().cuda_stream)
+            A.seed(33)
+            want = getattr(buf, fn)(idxs=idxs, data_aug=chain, offsets=off, bank_idx=rows, weights=wt)
+            for a, b in zip(got, want):
+                assert torch.equal(a, b), chain
+            assert float(wt.std()) > 0.8
+    finally:
+        A.set_background_bank(None)
+
+
 @pytest.mark.parametrize("chain,fn", [("overlay", "sample_svea_aug"), ("splice", "sample_augcl")])
 def test_in_kernel_bank_rows_equal_explicit_rows(U, A, chain, fn):
     """desc.bank_idx == NULL: the background rows are drawn inside the fused kernel and are the values
