@@ -65,6 +65,21 @@ def main():
             "random_overlay_u8bank": (2 * S32 + F, lambda t: lib.augcl_random_overlay(xs[t % n_sets].data_ptr(), outs[t % n_sets].data_ptr(), B, C, S, S, bank.data_ptr(), 0, 4096, rows.data_ptr(), 0.5, sp)),
             "splice_u8bank": (2 * S32 + 3 * F, lambda t: lib.augcl_splice(xs[t % n_sets].data_ptr(), outs[t % n_sets].data_ptr(), B, C, S, S, bank.data_ptr(), 0, 4096, rows.data_ptr(), 0.0, 0.0, 0.6, 0, sp)),
         }
+        # the remaining aug_to_func entries (csrc/augment2.cu), through the module functions (device draws; the output tensor
+        # comes from torch's caching allocator, so small batches also show the host side of the call)
+        def mod(f):
+            def run(t):
+                f(xs[t % n_sets])
+                return 0
+            return run
+        cases.update({
+            "random_grayscale": (2 * S32, mod(lambda x: A.random_grayscale(x, p=0.3))),
+            "random_flip": (2 * S32, mod(lambda x: A.random_flip(x, p=0.2))),
+            "random_rotation": (2 * S32, mod(lambda x: A.random_rotation(x, p=0.3))),
+            "random_cutout_color": (2 * S32, mod(lambda x: A.random_cutout_color(x))),
+            "color_jitter": (2 * S32, mod(lambda x: A.color_jitter(x))),
+            "CS_splice_u8bank": (2 * S32 + 3 * F, mod(lambda x: A.CS_splice(x))),
+        })
         for name, (bytes_per_sample, fn) in cases.items():
             if a.only and a.only not in name:
                 continue

@@ -239,6 +239,49 @@ def test_fast_splice_mask_equals_float_hsv_on_all_colours(U, A):
         A.set_background_bank(None)
 
 
+def _ring_stacks(buf, idxs):
+    """u8 (obs, next_obs) stacks of the sampled slots, read back slot by slot with augcl_ring_get (host tensors)."""
+    from augcl_b200 import _lib as L
+    c, h, w = buf.obs_shape
+    obs = torch.empty((len(idxs), c, h, w), dtype=torch.uint8, device="cuda")
+    nxt = torch.empty_like(obs)
+    st = torch.cuda.current_stream().cuda_stream
+    for j, i in enumerate(idxs):
+        L.call("augcl_ring_get", buf._ring, int(i), 1, obs[j].data_ptr(), nxt[j].data_ptr(), None, None, None, st)
+    torch.cuda.synchronize()
+    return obs.cpu().float(), nxt.cpu().float()
+
+
+@pytest.mark.parametrize("chain,aug_input,B", [("overlay", "shift", 256), ("splice-conv", "plain", 128)])
+def test_fused_against_oracle_at_baseline_sizes(U, A, O, chain, aug_input, B):
+    """BASELINE.json configs[2] (SVEA shift + overlay, batch 256) and configs[3] (AugCL splice-conv, batch 128) at
+    full size -- 100k ring, 9x84x84 -- against the ORACLE chain (not the unfused product), fed with the u8 stacks read
+    back from the sampled ring slots."""
+    cap, S, k, pad = 100_000, 84, 3, 4
+    buf = U.ReplayBuffer((3 * k, S, S), (6,), cap, B)
+    buf.fill_synthetic(seed=17)
+    g = torch.Generator().manual_seed(1)
+    bank = torch.randint(0, 256, (64, 3, S, S), generator=g, dtype=torch.uint8)
+    A.set_background_bank(bank.cuda())
+    try:
+        idxs = torch.randint(0, cap, (B,), generator=g).numpy()
+        off = {"obs": torch.randint(0, 2 * pad + 1, (B, 2), generator=g).numpy()}
+        rows = torch.randint(0, 64, (B,), generator=g).numpy()
+        wt = torch.randn((B, 3, 3, 3, 3), generator=g)
+        out = buf.sample_fused(idxs=idxs, pad=pad, data_aug=chain, aug_input=aug_input, offsets=off, bank_idx=rows, weights=wt,
+                               want=("obs_shift", "obs_aug", "next_obs"))
+        o_obs, o_next = _ring_stacks(buf, idxs)
+        o_shift = O.random_shift_int(o_obs, off["obs"], pad)
+        assert torch.equal(out["obs_shift"].cpu(), o_shift)
+        assert torch.equal(out["next_obs"].cpu(), o_next)
+        imgs = O.bank_rows_f32(bank, rows)
+        want = oracle_chain(O, o_shift if aug_input == "shift" else o_obs, chain.split("-"), imgs, wt, {})
+        err = (out["obs_aug"].cpu() - want).abs().max().item() / 255.0
+        assert err <= TOL_NORM, f"{chain}: {err}"
+    finally:
+        A.set_background_bank(None)
+
+
 def test_in_kernel_conv_weights_equal_explicit_weights(U, A):
     """desc.conv_weights == NULL: the 81 N(0,1) weights per sample are drawn inside the fused kernel (by the B-warps) and
     are the values augcl_rng_fill_normal(out, B*81, seed, conv_subsequence) writes -- AugCL's update is ONE launch."""
