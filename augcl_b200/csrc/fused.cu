@@ -201,7 +201,11 @@ ring_sample_fused_kernel(const __grid_constant__ FusedParams p, const __grid_con
     mbar_fence_init();
   }
   __syncthreads();
-  pdl_wait();
+  // Programmatic dependent launch: a CTA that became resident while the previous kernel of the stream drains may READ
+  // (ring, refs table, draws, background bank, conv weights: nothing a sample kernel -- the only kind that lets its
+  // successor start early -- ever writes) but must not store, nor touch the ticket counter the predecessor re-arms at
+  // its end, before griddepcontrol.wait.  The producer's first chunk of tickets is static, so its first copies are in
+  // flight before that point; each role waits right before its first store / atomic.
   pdl_launch_dependents();
 
   if (warp == NAW + NBW) {
@@ -237,9 +241,11 @@ ring_sample_fused_kernel(const __grid_constant__ FusedParams p, const __grid_con
     // up to two claims in flight (an atomic on the contended counter takes longer than one short pass)
     uint32_t nb0 = 0, ns0 = 0, nb1 = 0, ns1 = 0, claimed = dyn0;   // claimed: newest known value of the global counter
     int npend = 0;
+    bool pdl_done = false;
     auto request = [&]() {
       const uint32_t sz = chunk_for(claimed);
       uint32_t b = 0;
+      if (!pdl_done) { pdl_wait(); pdl_done = true; }   // the predecessor re-arms the counter at its very end
       if (lane == 0) b = atomicAdd(p.sched, sz);
       if (npend == 0) { nb0 = b; ns0 = sz; } else { nb1 = b; ns1 = sz; }
       ++npend;
@@ -313,7 +319,7 @@ ring_sample_fused_kernel(const __grid_constant__ FusedParams p, const __grid_con
     for (bool more = true; more;) {
       const Draw d = nx;
       const uint32_t lmask = __ballot_sync(0xffffffffu, d.live);
-      if (lmask) nx = fetch(next_pass());   // the next pass's loads travel during this one
+      if (pdl_done && lmask) nx = fetch(next_pass());   // the next pass's loads travel during this one
       FusedMeta m{};
       uintptr_t a0 = 0, g0 = 0;
       uint32_t sbytes = 0, gbytes = 0;
@@ -386,7 +392,13 @@ ring_sample_fused_kernel(const __grid_constant__ FusedParams p, const __grid_con
         __syncwarp();
         if (++s == NS) { s = 0; eph ^= 1; }
       }
+      if (!pdl_done) {   // the first pass (static tickets) is on its way: now wait for the predecessor, then go on as usual
+        pdl_wait();
+        pdl_done = true;
+        if (lmask && more) nx = fetch(next_pass());
+      }
     }
+    if (!pdl_done) pdl_wait();
     if (lane == 0) {
       // the last CTA to run out of units re-arms the counters for the next launch on this ring (launches of one ring
       // are stream-ordered, and a PDL successor takes its first ticket only after griddepcontrol.wait)
@@ -403,6 +415,7 @@ ring_sample_fused_kernel(const __grid_constant__ FusedParams p, const __grid_con
   if (CONV && warp >= NAW) {
     // =============================== B-warps: conv on tile t ===============================
     const int bt = tid - NTA;
+    pdl_wait();
     gather_scalars_part(p.sp, inl, blockIdx.x * NTB + bt, gridDim.x * NTB);
     const int a0 = bt / nq, q4 = bt - a0 * nq;
     const int ARPR = NTB / nq;                      // band rows per round (6 at W = 84: one round)
@@ -477,7 +490,8 @@ ring_sample_fused_kernel(const __grid_constant__ FusedParams p, const __grid_con
   }
 
   // =============================== A-warps: elementwise phase ===============================
-  if (!CONV) gather_scalars_part(p.sp, inl, blockIdx.x * NTA + tid, gridDim.x * NTA);
+  bool pdl_done = false;
+  if (!CONV) { pdl_wait(); pdl_done = true; gather_scalars_part(p.sp, inl, blockIdx.x * NTA + tid, gridDim.x * NTA); }
   // items of a unit = (row, 4-pixel group), handed out flat over the NTA threads: no per-item division
   const int pr0 = tid / nq, q0 = tid - pr0 * nq;
   const int dpr = NTA / nq, dq = NTA - dpr * nq;
@@ -487,6 +501,7 @@ ring_sample_fused_kernel(const __grid_constant__ FusedParams p, const __grid_con
   uint32_t fph = 0, un = 0;   // un: units consumed so far
   for (;;) {
     mbar_wait(&full[s], fph);
+    if (!pdl_done) { pdl_wait(); pdl_done = true; }   // first stores below
     if (!valid[s]) break;
     const FusedMeta m = meta_load(meta + (un % kFMetaRing) * 4);
     ++un;

@@ -46,7 +46,6 @@ __global__ void __launch_bounds__(256, 6) ring_sample_tma_kernel(const SamplePar
     mbar_fence_init();
   }
   __syncthreads();
-  pdl_wait();
 
   auto issue = [&](int item, int s) {   // tid 0 only
     const int ch = item % p.C;
@@ -71,6 +70,7 @@ __global__ void __launch_bounds__(256, 6) ring_sample_tma_kernel(const SamplePar
       if (item < total) issue(item, j);
     }
   }
+  pdl_wait();   // the read-only prologue above may overlap the previous kernel's tail (see ring_sample_band_kernel)
   pdl_launch_dependents();
 
   gather_scalars(p, none);
@@ -154,7 +154,6 @@ __global__ void __launch_bounds__(256, 6) ring_sample_band_kernel(const SamplePa
     mbar_fence_init();
   }
   __syncthreads();
-  pdl_wait();   // everything above overlaps the tail of the previous kernel in the stream (PDL launches only)
 
   auto issue = [&](int k, int s) {   // one lane
     const int64_t plane = pl0 + k;
@@ -183,6 +182,11 @@ __global__ void __launch_bounds__(256, 6) ring_sample_band_kernel(const SamplePa
   };
 
   if (tid < S && tid < nseg) issue(tid, tid);   // the S prologue copies are prepared by S lanes in parallel
+  // Everything above -- the draws, the slot -> address arithmetic, the first S bulk copies -- overlaps the tail of the
+  // previous kernel in the stream when this one was launched programmatically (PDL): it only READS the ring, the refs
+  // table and the draws, and the only kernels that let a successor start early (griddepcontrol.launch_dependents) are
+  // this library's sample kernels, which write nothing but their outputs.  The first STORE waits for the predecessor.
+  pdl_wait();
   pdl_launch_dependents();
   gather_scalars(p, inl);
 

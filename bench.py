@@ -249,7 +249,7 @@ def run_ours(args):
     outs = [(torch.zeros((B, C, S, S), dtype=torch.float32, device=dev), torch.zeros((B, C, S, S), dtype=torch.float32, device=dev),
              torch.zeros((B, A_DIM), device=dev), torch.zeros((B, 1), device=dev), torch.zeros((B, 1), device=dev))
             for _ in range(n_sets)]       # zeros, not empty: every page of the 8 output sets is touched before warm-up
-    T = W + R * K
+    T = W + R * K + 10        # + 10 isolated launches
     idx = torch.randint(0, CAP, (T, B), generator=g).to(dev)                       # resident before the timed region
     off = torch.randint(0, 2 * PAD + 1, (T, 2, B, 2), generator=g, dtype=torch.int32).to(dev)
     stream = torch.cuda.current_stream(dev)
@@ -298,6 +298,16 @@ def run_ours(args):
         if r == 0:
             launches = L.launch_count() - l0
             clk_t1 = time.perf_counter()
+    # one launch at a time (synchronize between launches: nothing overlaps), for comparison with the back-to-back figure
+    iso = []
+    for t in range(10):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        step(W + R * K + t)
+        e1.record(stream)
+        torch.cuda.synchronize(dev)
+        iso.append(e0.elapsed_time(e1))
+    iso_ms = sorted(iso)[len(iso) // 2]
     ms_rank = blocks[0]
     per_rank = shard.gather_over_ranks(ms_rank, device=dev)                    # off the data path, after timing stops
     ms = max(per_rank)
@@ -306,9 +316,12 @@ def run_ours(args):
     timing = {"per_rank_ms": [round(x, 5) for x in per_rank], "blocks_ms_per_step": [round(b / K, 6) for b in blocks_max],
               "enqueue_ms_rank0": [round(x, 4) for x in enq], "delay_kernel_ns": delay_ns,
               "cores_rank0": [cores[0], cores[-1]] if cores else None,
+              "isolated_launch_ms": round(iso_ms, 6),
               "note": "block 0 (the first K steps after warm-up) is ms_per_step / value; blocks 1.. repeat the same K-step "
                       "measurement on fresh indices to show its spread; each block's K launches are enqueued behind a "
-                      "one-thread delay kernel that ends before the start event"}
+                      "one-thread delay kernel that ends before the start event; isolated_launch_ms = median of 10 single "
+                      "launches with a synchronize after each (events around one launch: includes the launch's own ramp-up "
+                      "and tail, which back-to-back launches overlap through programmatic dependent launch)"}
     clocks = sampler.window(clk_t0, clk_t1)
 
     # ---- e2e: the reference-named call, ReplayBuffer.sample_drq, with HOST indices/offsets in and the rewards read back
@@ -688,7 +701,9 @@ def main():
                          "algorithmic_bytes_per_launch": B * BYTES_PER_SAMPLE,
                          "note": "per-launch time = timed region / steps (one launch per step, CUDA events on the launching "
                                  "stream; the K launches are enqueued behind a one-thread delay kernel that ends before the "
-                                 "start event, see `timing`)",
+                                 "start event, see `timing`).  Consecutive launches overlap: with programmatic dependent launch "
+                                 "the read-only start of launch n+1 (draws, first bulk copies) runs during the tail of launch n; "
+                                 "every store waits for launch n to complete.  One launch alone: timing.isolated_launch_ms",
                          "traffic_note": "ncu --set full, one isolated launch (profiles/r01_ncu_ring_sample.csv): 16.2 MB read = the "
                                          "launch's u8 inputs exactly, 8.3 MB written -- the other 57 MB of its 65 MB f32 output are "
                                          "still dirty lines in the 126 MB L2 when the kernel ends and reach DRAM during later "

@@ -138,7 +138,12 @@ int augcl_ring_fill_synthetic(augcl_ring* ring, int64_t count, uint64_t seed, au
  *              [0, W-size) -- the reference's window view has H-size positions, the last geometric one is excluded
  *              (src/augmentations.py:416-433); HOST offsets outside are AUGCL_ERR_BAD_ARG, DEVICE offsets are trusted
  *              (clamped per pixel for memory safety); must not be NULL for a tensor that is written.
- *   pad_or_size  pad (SHIFT) or size (CROP); ignored for NONE. */
+ *   pad_or_size  pad (SHIFT) or size (CROP); ignored for NONE.
+ * Stream ordering.  The sample kernels (this call, _ex, _curl, _views, _fused) are launched with programmatic stream
+ * serialization (option "sample_pdl", default on): when the previous kernel of the stream is itself a sample kernel,
+ * the read-only start of the next one -- the draws, the ring / refs / bank reads, its first bulk copies -- overlaps the
+ * tail of the previous one; every store, and every access to the ring's schedule counters, waits for the previous
+ * kernel to complete (griddepcontrol.wait).  After any other kernel or copy the launch is serialized as usual. */
 int augcl_ring_sample(augcl_ring* ring, const int64_t* idx, int B, float* out_obs, float* out_next,
                       float* out_act, float* out_rew, float* out_nd, int aug_mode,
                       const int32_t* off_obs, const int32_t* off_next, int pad_or_size,
