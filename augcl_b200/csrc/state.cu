@@ -10,7 +10,7 @@ std::atomic<int> g_sample_stages{0};   // 0 = auto (4 when a CTA gets few units,
 std::atomic<int> g_sample_ctas_per_sm{6};
 std::atomic<int> g_sample_pdl{1};
 std::atomic<int> g_sample_band{1};
-std::atomic<int> g_sample_fused_min_batch{256};   // augcl_ring_sample*: batches >= this use the fused.cu kernel (0 = never)
+std::atomic<int> g_sample_fused_min_batch{384};   // augcl_ring_sample*: batches >= this use the fused.cu kernel (0 = never)
 extern std::atomic<int> g_fused_ctas_per_sm;   // fused.cu
 extern std::atomic<int> g_fused_fast_mask;
 extern std::atomic<int> g_fused_stages;
