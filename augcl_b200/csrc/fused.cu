@@ -30,9 +30,7 @@ std::atomic<int> g_fused_ctas_per_sm{0};   // 0 = auto
 std::atomic<int> g_fused_stages{0};      // 0 = auto
 std::atomic<int> g_fused_batch{0};       // units the producer warp decodes side by side (0 = auto)
 std::atomic<int> g_fused_interleave{-1}; // obs / next_obs units alternate in ticket order (-1 = auto: conv chains only)
-std::atomic<int> g_fused_ahead{-1};      // producer fetches the next pass's draws before it issues the current one (-1 = auto)
 std::atomic<int> g_fused_skip{0};        // TIMING EXPERIMENTS ONLY (wrong results): 1 = no conv arithmetic, 2 = no tile stores, 4 = no direct obs stores
-std::atomic<int> g_fused_wait_hint{0};   // ns a waiting warp may stay suspended per mbarrier.try_wait (0 = default)
 std::atomic<int> g_fused_band{0};        // 0 = auto (non-conv chains: 14 or 7 rows)
 std::atomic<int> g_fused_fast_mask{1};   // 0: always the float HSV path (A/B and the exhaustive equivalence test)
 
@@ -61,7 +59,7 @@ struct FusedParams {
   int plane_stage, bank_stage, stage_bytes, tile_rs, stages;
   uint32_t* sched;          // unit schedule: {next ticket, CTAs done}
   int normalize;
-  int batch, wait_hint, interleave, ahead, skip;
+  int batch, interleave, skip;
   double rcp_bands, rcp_k, rcp_B;   // exact small-divisor division in the producer warp (udiv_small)
 };
 
@@ -809,10 +807,8 @@ extern "C" int augcl_ring_sample_fused(augcl_ring* r, const augcl_fused_desc* d,
   // conv chains: pairs (an obs band for the B-warps + a next_obs band) so every pass feeds both roles; other chains: one
   p.batch = g_fused_batch.load() > 0 ? g_fused_batch.load() : (has_conv ? 2 : 1);
   if (p.batch > p.stages) p.batch = p.stages;
-  p.wait_hint = g_fused_wait_hint.load();
   p.skip = g_fused_skip.load();
   p.interleave = g_fused_interleave.load() >= 0 ? g_fused_interleave.load() : ((has_conv || B <= 512) ? 1 : 0);
-  p.ahead = g_fused_ahead.load() >= 0 ? g_fused_ahead.load() : 1;
   if (smem > 200 * 1024) AUGCL_FAIL(AUGCL_ERR_UNSUPPORTED, "%s: geometry needs %zu B of shared memory", who, smem);
 
   DeviceGuard g(r->device);

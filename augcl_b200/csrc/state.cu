@@ -15,10 +15,8 @@ extern std::atomic<int> g_fused_ctas_per_sm;   // fused.cu
 extern std::atomic<int> g_fused_fast_mask;
 extern std::atomic<int> g_fused_stages;
 extern std::atomic<int> g_fused_batch;
-extern std::atomic<int> g_fused_wait_hint;
 extern std::atomic<int> g_fused_skip;
 extern std::atomic<int> g_fused_interleave;
-extern std::atomic<int> g_fused_ahead;
 extern std::atomic<int> g_fused_band;
 extern std::atomic<int> g_bil_tma;
 extern std::atomic<int> g_conv_part;
@@ -119,7 +117,9 @@ int augcl_set_option(const char* key, const char* value) {
     AUGCL_REQUIRE(v >= 0 && v <= 16, "fused_ctas_per_sm must be in [0,16] (0 = auto)");
     g_fused_ctas_per_sm = v; return AUGCL_OK;
   }
-  if (!strcmp(key, "fused_cost_obs") || !strcmp(key, "fused_cost_next") || !strcmp(key, "fused_dynamic")) return AUGCL_OK;   // retired (round-1 static schedule)
+  if (!strcmp(key, "fused_cost_obs") || !strcmp(key, "fused_cost_next") || !strcmp(key, "fused_dynamic") ||
+      !strcmp(key, "fused_ahead") || !strcmp(key, "fused_wait_hint"))
+    return AUGCL_OK;   // retired switches of earlier schedules: accepted, ignored
   if (!strcmp(key, "fused_stages")) {
     int v = atoi(value);
     AUGCL_REQUIRE(v >= 0 && v <= 4, "fused_stages must be in [0,4] (0 = auto)");
@@ -131,13 +131,7 @@ int augcl_set_option(const char* key, const char* value) {
     g_fused_batch = v; return AUGCL_OK;
   }
   if (!strcmp(key, "fused_interleave")) { g_fused_interleave = atoi(value); return AUGCL_OK; }   // -1 = auto
-  if (!strcmp(key, "fused_ahead")) { g_fused_ahead = atoi(value); return AUGCL_OK; }             // -1 = auto
   if (!strcmp(key, "fused_skip")) { g_fused_skip = atoi(value); return AUGCL_OK; }   // timing experiments only
-  if (!strcmp(key, "fused_wait_hint")) {
-    const int v = atoi(value);
-    AUGCL_REQUIRE(v >= 0 && v <= 1000000, "fused_wait_hint must be in [0,1000000] ns (0 = default)");
-    g_fused_wait_hint = v; return AUGCL_OK;
-  }
   if (!strcmp(key, "fused_band")) {
     int v = atoi(value);
     AUGCL_REQUIRE(v >= 0 && v <= 14, "fused_band must be in [0,14] (0 = auto)");

@@ -70,8 +70,15 @@ int64_t augcl_launch_count(void);
  * `nanoseconds` (<= 50 ms; it waits on the GPU's clock only).  bench.py puts it in front of the timed region so that every
  * timed launch is already queued when the GPU reaches the first one.  Not counted by augcl_launch_count. */
 int augcl_stream_delay(uint64_t nanoseconds, augcl_stream stream);
-/* Runtime switches, for A/B measurement: "staging" = "tma" (default; cp.async.bulk + mbarrier
- * pipeline through shared memory) | "generic" (one thread per output element, no staging). */
+/* Runtime switches, for A/B measurement (csrc/state.cu holds the table; integers are passed as decimal strings, 0 = auto
+ * where a count is meant).  "staging" = "tma" (default; cp.async.bulk + mbarrier pipeline through shared memory) |
+ * "generic" (one thread per output element, no staging).  Sample kernels: "sample_stages", "sample_ctas_per_sm",
+ * "sample_pdl" (programmatic dependent launch, default 1), "sample_band", "sample_fused_min_batch" (batches from here up
+ * run on the fused sampler's copy kernel; default 384).  Fused sampler: "fused_stages" (ring depth, <= 4), "fused_batch"
+ * (units the producer warp decodes side by side), "fused_ctas_per_sm", "fused_band" (rows per unit, non-conv chains),
+ * "fused_interleave" (obs / next_obs units alternate; -1 auto), "fused_fast_mask" (byte-domain splice mask, default 1),
+ * "fused_skip" (TIMING EXPERIMENTS ONLY -- switches parts of the conv chain off, results are wrong).  Stand-alone kernels:
+ * "conv_part", "bilinear_tma". */
 int augcl_set_option(const char* key, const char* value);
 
 /* ------------------------------------------------------------------------------------------
