@@ -77,6 +77,86 @@ __global__ void __launch_bounds__(256) cutout_kernel(const float* __restrict__ i
   }
 }
 
+// ---- 16-byte versions (h*w % 4 == 0, w % 4 == 0 where rows matter, 16-byte aligned tensors): same arithmetic per pixel ----
+__device__ __forceinline__ float gray_q(float v) { return (float)((int)(v * 255.0f) & 255); }   // x*255 -> uint8 (wraps) -> float
+
+// thread = 4 pixels of the three channels of one frame: 3 LDG.128 + 3 STG.128
+__global__ void __launch_bounds__(256) grayscale_vec_kernel(const float4* __restrict__ in, float4* __restrict__ out, int k, int hw4,
+                                                            int chunks, const uint8_t* __restrict__ mask) {
+  const int chunk = blockIdx.x % chunks;
+  const int frame = blockIdx.x / chunks;          // sample * k + f
+  const int p4 = chunk * 256 + threadIdx.x;
+  if (p4 >= hw4) return;
+  const int64_t o = (int64_t)frame * 3 * hw4 + p4;
+  const float4 r4 = __ldg(in + o), g4 = __ldg(in + o + hw4), b4 = __ldg(in + o + 2 * (int64_t)hw4);
+  float r[4] = {gray_q(r4.x), gray_q(r4.y), gray_q(r4.z), gray_q(r4.w)};
+  float g[4] = {gray_q(g4.x), gray_q(g4.y), gray_q(g4.z), gray_q(g4.w)};
+  float b[4] = {gray_q(b4.x), gray_q(b4.y), gray_q(b4.z), gray_q(b4.w)};
+  if (mask[frame / k]) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float y = (float)((int)((r[j] * 0.2989f + g[j] * 0.587f) + b[j] * 0.114f) & 255);
+      r[j] = g[j] = b[j] = y;
+    }
+  }
+  out[o] = make_float4(div255(r[0]), div255(r[1]), div255(r[2]), div255(r[3]));
+  out[o + hw4] = make_float4(div255(g[0]), div255(g[1]), div255(g[2]), div255(g[3]));
+  out[o + 2 * (int64_t)hw4] = make_float4(div255(b[0]), div255(b[1]), div255(b[2]), div255(b[3]));
+}
+
+// row-preserving permutations on whole 16-byte groups: identity, column flip (random_flip) and the half turn (rot90 by 2);
+// planes drawn a quarter turn (rot90 by 1 / 3, a transposition) take the scalar gather of permute_kernel, plane by plane
+__global__ void __launch_bounds__(256) permute_rows_vec_kernel(const float4* __restrict__ in, float4* __restrict__ out, int planes,
+                                                               int c, int h, int wq, const int32_t* __restrict__ flag, int mode) {
+  const int n4 = h * wq;
+  for (int plane = blockIdx.x; plane < planes; plane += gridDim.x) {
+    const int f = flag[plane / c];
+    const bool fc = mode == 0 ? f != 0 : f == 2, fr = mode == 1 && f == 2;
+    const float4* src = in + (int64_t)plane * n4;
+    float4* dst = out + (int64_t)plane * n4;
+    if (mode == 1 && (f & 1)) {   // h == w here
+      const int w = wq * 4;
+      const float* s1 = reinterpret_cast<const float*>(src);
+      float* d1 = reinterpret_cast<float*>(dst);
+      for (int e = threadIdx.x; e < h * w; e += 256) {
+        const int i = e / w, j = e - i * w;
+        // torch.rot90(x, r, [2, 3]):  r=1: out[i][j] = x[j][w-1-i];  r=3: x[h-1-j][i]
+        d1[e] = f == 1 ? __ldg(s1 + j * w + (w - 1 - i)) : __ldg(s1 + (h - 1 - j) * w + i);
+      }
+      continue;
+    }
+    for (int e = threadIdx.x; e < n4; e += 256) {
+      const int i = e / wq, q = e - i * wq;
+      const float4 v = __ldg(src + (fr ? h - 1 - i : i) * wq + (fc ? wq - 1 - q : q));
+      dst[e] = fc ? make_float4(v.w, v.z, v.y, v.x) : v;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) cutout_vec_kernel(const float4* __restrict__ in, float4* __restrict__ out, int planes, int c,
+                                                         int h, int wq, const int32_t* __restrict__ box,
+                                                         const float* __restrict__ colors) {
+  const int n4 = h * wq;
+  for (int plane = blockIdx.x; plane < planes; plane += gridDim.x) {
+    const int i = plane / c;
+    const int w1 = box[2 * i], h1 = box[2 * i + 1];
+    const float col = colors[plane];
+    const float4* src = in + (int64_t)plane * n4;
+    float4* dst = out + (int64_t)plane * n4;
+    for (int e = threadIdx.x; e < n4; e += 256) {
+      const int r = e / wq, q0 = (e - r * wq) * 4;
+      float4 v = __ldg(src + e);
+      if (r >= h1 && r < 2 * h1) {
+        if (q0 >= w1 && q0 < 2 * w1) v.x = col;
+        if (q0 + 1 >= w1 && q0 + 1 < 2 * w1) v.y = col;
+        if (q0 + 2 >= w1 && q0 + 2 < 2 * w1) v.z = col;
+        if (q0 + 3 >= w1 && q0 + 3 < 2 * w1) v.w = col;
+      }
+      dst[e] = v;
+    }
+  }
+}
+
 static int check_args(const char* who, const float* in, float* out, int n, int c, int h, int w, const void* draw) {
   AUGCL_REQUIRE(in && out && draw, "%s: NULL pointer", who);
   AUGCL_REQUIRE(in != out, "%s: in and out must not alias", who);
@@ -205,7 +285,17 @@ int augcl_random_grayscale(const float* in, float* out, int n, int c, int h, int
                            augcl_stream stream) {
   if (int rc = check_args("augcl_random_grayscale", in, out, n, c, h, w, mask)) return rc;
   AUGCL_REQUIRE(c % 3 == 0, "augcl_random_grayscale: c=%d is not a multiple of 3", c);
-  const int hw = h * w, chunks = (hw + 255) / 256, k = c / 3;
+  const int hw = h * w, k = c / 3;
+  if ((hw & 3) == 0 && aligned(in, 16) && aligned(out, 16)) {
+    const int hw4 = hw / 4, chunks4 = (hw4 + 255) / 256;
+    const int64_t grid4 = (int64_t)n * k * chunks4;
+    AUGCL_REQUIRE(grid4 < (1ll << 31), "augcl_random_grayscale: batch too large");
+    grayscale_vec_kernel<<<(unsigned)grid4, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<const float4*>(in), reinterpret_cast<float4*>(out),
+                                                                            k, hw4, chunks4, mask);
+    AUGCL_LAUNCHED();
+    return AUGCL_OK;
+  }
+  const int chunks = (hw + 255) / 256;
   const int64_t grid = (int64_t)n * k * chunks;
   AUGCL_REQUIRE(grid < (1ll << 31), "augcl_random_grayscale: batch too large");
   grayscale_kernel<<<(unsigned)grid, 256, 0, (cudaStream_t)stream>>>(in, out, k, hw, chunks, mask);
@@ -218,6 +308,12 @@ static int launch_permute(const char* who, const float* in, float* out, int n, i
   if (int rc = check_args(who, in, out, n, c, h, w, flag)) return rc;
   const int planes = n * c;
   const int grid = planes < kNumSMs * 8 ? planes : kNumSMs * 8;
+  if ((w & 3) == 0 && aligned(in, 16) && aligned(out, 16)) {
+    permute_rows_vec_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<const float4*>(in), reinterpret_cast<float4*>(out),
+                                                                  planes, c, h, w / 4, flag, mode);
+    AUGCL_LAUNCHED();
+    return AUGCL_OK;
+  }
   permute_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(in, out, planes, c, h, w, flag, mode);
   AUGCL_LAUNCHED();
   return AUGCL_OK;
@@ -240,6 +336,12 @@ int augcl_random_cutout_color(const float* in, float* out, int n, int c, int h, 
   AUGCL_REQUIRE(colors, "augcl_random_cutout_color: colors is NULL");
   const int planes = n * c;
   const int grid = planes < kNumSMs * 8 ? planes : kNumSMs * 8;
+  if ((w & 3) == 0 && aligned(in, 16) && aligned(out, 16)) {
+    cutout_vec_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<const float4*>(in), reinterpret_cast<float4*>(out), planes, c,
+                                                            h, w / 4, box, colors);
+    AUGCL_LAUNCHED();
+    return AUGCL_OK;
+  }
   cutout_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(in, out, planes, c, h, w, box, colors);
   AUGCL_LAUNCHED();
   return AUGCL_OK;
