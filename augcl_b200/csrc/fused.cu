@@ -802,7 +802,8 @@ extern "C" int augcl_ring_sample_fused(augcl_ring* r, const augcl_fused_desc* d,
   const size_t budget = (228 * 1024) / (has_conv ? 3 : 4) - 1024;   // 3 (conv) / 4 CTAs per SM
   while (p.stages > 1 && kFHeader + (size_t)p.stages * p.stage_bytes + tile_bytes > budget) --p.stages;
   const size_t smem = kFHeader + (size_t)p.stages * p.stage_bytes + tile_bytes;
-  p.sched = r->sched;
+  p.sched = sched_for(r, (cudaStream_t)stream);
+  if (!p.sched) AUGCL_FAIL(AUGCL_ERR_UNSUPPORTED, "%s: a ring can be sampled from at most %d streams", who, kSchedSlots);
   p.rcp_bands = 1.0 / (double)p.bands; p.rcp_k = 1.0 / (double)p.k; p.rcp_B = 1.0 / (double)B;
   // conv chains: pairs (an obs band for the B-warps + a next_obs band) so every pass feeds both roles; other chains: one
   p.batch = g_fused_batch.load() > 0 ? g_fused_batch.load() : (has_conv ? 2 : 1);

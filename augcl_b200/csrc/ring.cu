@@ -308,8 +308,10 @@ static int ring_create_impl(const char* who, augcl_ring** out, int device, int64
   if (e == cudaSuccess) e = cudaMalloc(&r->act, fbytes * action_dim);
   if (e == cudaSuccess) e = cudaMalloc(&r->rew, fbytes);
   if (e == cudaSuccess) e = cudaMalloc(&r->nd, fbytes);
-  if (e == cudaSuccess) e = cudaMalloc(&r->sched, 64);
-  if (e == cudaSuccess) e = cudaMemset(r->sched, 0, 64);
+  if (e == cudaSuccess) e = cudaMalloc(&r->sched, 64 * kSchedSlots);
+  if (e == cudaSuccess) e = cudaMemset(r->sched, 0, 64 * kSchedSlots);
+  r->n_sched = 0;
+  r->sched_lock.clear();
   if (e == cudaSuccess) {
     cudaMemPoolProps props{};
     props.allocType = cudaMemAllocationTypePinned;

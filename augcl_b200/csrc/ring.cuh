@@ -24,7 +24,11 @@ struct augcl_ring {
   int64_t bytes;
   // "v2" (de-duplicated) layout: obs = frame pool [pool][cpf][H][W] u8, next = NULL,
   // refs[capacity][2][k] = pool slot of every frame of (obs, next_obs)
-  uint32_t* sched;   // {ticket, done} counters of the fused sampler's dynamic unit schedule (zero between launches)
+  uint32_t* sched;   // kSchedSlots x {ticket, done, ..} (64 B each): counters of the fused sampler's unit schedule, one set per
+                     // stream the ring is sampled from (zero between launches); sched_streams[i] owns slot i
+  cudaStream_t sched_streams[16];
+  int n_sched;
+  std::atomic_flag sched_lock;
   cudaMemPool_t scratch_pool;   // stream-ordered scratch for staged HOST draws; never trimmed (the default pool gives its
                                 // memory back at every synchronize: ~0.5 ms per cudaMallocAsync + ~0.8 ms per sync after)
   int dedup;
@@ -33,6 +37,19 @@ struct augcl_ring {
 };
 
 namespace augcl {
+
+constexpr int kSchedSlots = 16;
+// Counter set of `stream` on this ring (launches of one stream are ordered, so they can share one; two streams must not).
+// Returns nullptr when more than kSchedSlots distinct streams have sampled the ring.
+inline uint32_t* sched_for(augcl_ring* r, cudaStream_t stream) {
+  while (r->sched_lock.test_and_set(std::memory_order_acquire)) {}
+  int slot = -1;
+  for (int i = 0; i < r->n_sched; ++i)
+    if (r->sched_streams[i] == stream) { slot = i; break; }
+  if (slot < 0 && r->n_sched < kSchedSlots) { slot = r->n_sched; r->sched_streams[r->n_sched++] = stream; }
+  r->sched_lock.clear(std::memory_order_release);
+  return slot < 0 ? nullptr : r->sched + 16 * slot;
+}
 
 constexpr int kMaxViews = 8;
 

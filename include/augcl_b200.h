@@ -24,9 +24,12 @@
  *     calls, which switch to the ring's device for the duration of the call.
  *   - threading: the stateless augmentation entry points may be called from any thread on any
  *     stream.  A ring handle is single-writer like the reference's ReplayBuffer (one Python
- *     thread, src/train.py): calls on ONE ring must be issued in order on ONE stream at a time
- *     (its sample kernels share schedule counters and stream-ordered scratch); different rings
- *     are independent.  CUDA-graph capture of ring calls is supported (tests/test_gpu_graph.py).
+ *     thread, src/train.py): put / fill calls on ONE ring are issued in order on one stream.
+ *     SAMPLING one ring from several streams at once is supported (up to 16 streams per ring:
+ *     the fused sampler keeps one set of schedule counters per stream, AUGCL_ERR_UNSUPPORTED
+ *     beyond that; tests/test_gpu_fused.py); the caller orders samples after the puts they
+ *     should see.  Different rings are independent.  CUDA-graph capture of ring calls is
+ *     supported (tests/test_gpu_graph.py).
  */
 #ifndef AUGCL_B200_H_
 #define AUGCL_B200_H_

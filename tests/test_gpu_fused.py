@@ -316,6 +316,28 @@ def test_fused_repeated_launches_are_bit_identical(U, A, chain, B):
         A.set_background_bank(None)
 
 
+def test_two_streams_sample_one_ring_concurrently(U, A):
+    """One set of schedule counters per (ring, stream): launches of the fused sampler that overlap on two streams each
+    process exactly their own units (round 1 had ONE counter per ring and documented the race instead)."""
+    cap, S, k, B = 20_000, 84, 3, 1024
+    buf = U.ReplayBuffer((3 * k, S, S), (6,), cap, B)
+    buf.fill_synthetic(seed=29)
+    g = torch.Generator().manual_seed(4)
+    draws = [(torch.randint(0, cap, (B,), generator=g).numpy(), {"obs": torch.randint(0, 9, (B, 2), generator=g).numpy()}) for _ in range(2)]
+    ref = [buf.sample_fused(idxs=i, offsets=o, data_aug="", want=("obs_shift", "next_obs")) for i, o in draws]
+    ref = [{key: r[key].clone() for key in ("obs_shift", "next_obs")} for r in ref]
+    torch.cuda.synchronize()
+    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    for rep in range(6):
+        outs = []
+        for st, (i, o) in zip(streams, draws):
+            with torch.cuda.stream(st):
+                outs.append(buf.sample_fused(idxs=i, offsets=o, data_aug="", want=("obs_shift", "next_obs")))
+        torch.cuda.synchronize()
+        for got, want in zip(outs, ref):
+            assert torch.equal(got["obs_shift"], want["obs_shift"]) and torch.equal(got["next_obs"], want["next_obs"]), rep
+
+
 def test_in_kernel_conv_weights_equal_explicit_weights(U, A):
     """desc.conv_weights == NULL: the 81 N(0,1) weights per sample are drawn inside the fused kernel (by the B-warps) and
     are the values augcl_rng_fill_normal(out, B*81, seed, conv_subsequence) writes -- AugCL's update is ONE launch."""
