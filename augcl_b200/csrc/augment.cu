@@ -13,6 +13,7 @@
 #include "pixel.cuh"
 
 namespace augcl {
+extern std::atomic<int> g_sample_pdl;   // state.cu: programmatic dependent launch on / off
 std::atomic<int> g_conv_part{1};  // random_conv: part-of-frame items (0 = 12-row bands, double-buffered)
 std::atomic<int> g_bil_tma{1};   // bilinear shift: double-buffered cp.async.bulk tiles (0 = single tile, LDG fill)
 
@@ -29,6 +30,10 @@ __global__ void __launch_bounds__(256) window_copy_vec_kernel(const float* __res
   constexpr int UNR = 4;   // 16 independent loads in flight per thread before the first store
   const int wq = WQ ? WQ : (Wo >> 2);
   const int nvec = Ho * wq;
+  // programmatic launch: this grid's CTAs become resident while the previous kernel of the stream drains (its output may be
+  // our input: nothing is read before the wait), and the next kernel's CTAs while this one does
+  pdl_wait();
+  pdl_launch_dependents();
   for (int plane = blockIdx.x; plane < planes; plane += gridDim.x) {
     const int i = plane / c;
     const int dy = offsets[2 * i] - pad, dx = offsets[2 * i + 1] - pad;
@@ -198,6 +203,8 @@ __global__ void __launch_bounds__(256) shift_bilinear_smem_kernel(const float* _
     mbar_init(&bars[1], 1);
     mbar_fence_init();
   }
+  pdl_wait();                 // launched programmatically: nothing is read before the previous kernel has completed
+  pdl_launch_dependents();
   const int Hp = h + 2 * pad, Wp = w + 2 * pad;
   const float sc = (float)(2.0 / (double)Hp);
   const int nchunk = 256 / w, rows_per = (((h + nchunk - 1) / nchunk) + 3) & ~3;
@@ -637,6 +644,8 @@ __global__ void __launch_bounds__(256) overlay_vec_kernel(const float4* __restri
                                                           int k, int hw4, int chunks, const void* __restrict__ bank,
                                                           int64_t bank_len, const int64_t* __restrict__ bank_idx,
                                                           float oma, float alpha) {
+  pdl_wait();                 // launched programmatically: nothing is read before the previous kernel has completed
+  pdl_launch_dependents();
   const int chunk = blockIdx.x % chunks;
   const int ic = blockIdx.x / chunks;
   const int i = ic / 3, ch = ic - 3 * i;
@@ -704,6 +713,8 @@ __global__ void __launch_bounds__(256) splice_vec_kernel(const float4* __restric
                                                          int n, int hw4, int chunks, const void* __restrict__ bank,
                                                          int64_t bank_len, const int64_t* __restrict__ bank_idx,
                                                          SpliceThr thr) {
+  pdl_wait();
+  pdl_launch_dependents();
   const int chunk = blockIdx.x % chunks;
   const int frame = blockIdx.x / chunks;     // row j of x.reshape(n*k, 3, h, w)
   const int p4 = chunk * 256 + threadIdx.x;
@@ -767,10 +778,10 @@ static int launch_window_copy(const float* in, float* out, int n, int c, int H, 
   const int planes = n * c;
   if (g_staging.load() == 0 && (Wo & 3) == 0 && aligned(out, 16)) {
     const int grid = planes < kNumSMs * 8 ? planes : kNumSMs * 8;
-    if (Wo == 84)
-      window_copy_vec_kernel<21><<<grid, 256, 0, st>>>(in, out, planes, c, H, W, Ho, Wo, offsets, pad);
-    else
-      window_copy_vec_kernel<0><<<grid, 256, 0, st>>>(in, out, planes, c, H, W, Ho, Wo, offsets, pad);
+    const bool pdl = g_sample_pdl.load() != 0;
+    const cudaError_t le = Wo == 84 ? launch_pdl(window_copy_vec_kernel<21>, grid, 256, 0, st, pdl, in, out, planes, c, H, W, Ho, Wo, offsets, pad)
+                                    : launch_pdl(window_copy_vec_kernel<0>, grid, 256, 0, st, pdl, in, out, planes, c, H, W, Ho, Wo, offsets, pad);
+    if (le != cudaSuccess) AUGCL_FAIL(AUGCL_ERR_CUDA, "window copy: launch failed: %s", cudaGetErrorString(le));
   } else {
     const int64_t total = (int64_t)planes * Ho * Wo;
     window_copy_generic_kernel<<<grid_for(total, 256, 16), 256, 0, st>>>(in, out, total, c, H, W, Ho, Wo, offsets, pad);
@@ -821,8 +832,8 @@ int augcl_random_shift(const float* in, float* out, int n, int c, int h, int w, 
     }
     const int per_sm = (int)((228 * 1024) / (smem + 1024));
     const int cap = kNumSMs * (per_sm < 1 ? 1 : (per_sm > 8 ? 8 : per_sm));
-    shift_bilinear_smem_kernel<<<planes < cap ? planes : cap, 256, smem, st>>>(
-        in, out, planes, c, h, w, pad, offsets, base, vec);
+    launch_pdl(shift_bilinear_smem_kernel, (unsigned)(planes < cap ? planes : cap), 256, smem, st, g_sample_pdl.load() != 0, in, out, planes, c,
+               h, w, pad, offsets, base, vec);
     AUGCL_LAUNCHED();
     return AUGCL_OK;
   }
@@ -883,7 +894,10 @@ int augcl_random_conv(const float* in, float* out, int n, int c, int h, int w, c
       per_sm = per_sm < 1 ? 1 : per_sm;
       const int64_t items = (int64_t)frames * parts;
       const int grid = (int)(items < kNumSMs * per_sm ? items : kNumSMs * per_sm);
-      random_conv_part_kernel<<<grid, threads, smem3, (cudaStream_t)stream>>>(in, out, frames, k, h, w, weights, parts, R);
+      // (no programmatic launch here: measured 22.5 -> 24.3 us at batch 128 with it -- waiting successor CTAs hold 45 KB tiles)
+      const cudaError_t le = launch_pdl(random_conv_part_kernel, grid, threads, smem3, (cudaStream_t)stream, false, in, out,
+                                        frames, k, h, w, weights, parts, R);
+      if (le != cudaSuccess) AUGCL_FAIL(AUGCL_ERR_CUDA, "augcl_random_conv: launch failed: %s", cudaGetErrorString(le));
       AUGCL_LAUNCHED();
       return AUGCL_OK;
     }
@@ -932,7 +946,7 @@ int augcl_random_overlay(const float* in, float* out, int n, int c, int h, int w
     AUGCL_REQUIRE(grid64 < (1ll << 31), "augcl_random_overlay: batch too large");
     const unsigned grid = (unsigned)grid64;
     const int k = c / 3;
-#define AUGCL_OV(U8, KK) overlay_vec_kernel<U8, KK><<<grid, 256, 0, st>>>((const float4*)in, (float4*)out, k, hw4, chunks, bank, bank_len, bank_idx, oma, alpha)
+#define AUGCL_OV(U8, KK) launch_pdl(overlay_vec_kernel<U8, KK>, grid, 256, 0, st, g_sample_pdl.load() != 0, (const float4*)in, (float4*)out, k, hw4, chunks, bank, bank_len, bank_idx, oma, alpha)
     if (u8) { if (k == 3) AUGCL_OV(true, 3); else AUGCL_OV(true, 0); }
     else    { if (k == 3) AUGCL_OV(false, 3); else AUGCL_OV(false, 0); }
 #undef AUGCL_OV
@@ -967,9 +981,9 @@ int augcl_splice(const float* in, float* out, int n, int c, int h, int w, const 
     AUGCL_REQUIRE(grid64 < (1ll << 31), "augcl_splice: batch too large");
     const unsigned grid = (unsigned)grid64;
     if (u8)
-      splice_vec_kernel<true><<<grid, 256, 0, st>>>((const float4*)in, (float4*)out, n, hw4, chunks, bank, bank_len, bank_idx, thr);
+      launch_pdl(splice_vec_kernel<true>, grid, 256, 0, st, g_sample_pdl.load() != 0, (const float4*)in, (float4*)out, n, hw4, chunks, bank, bank_len, bank_idx, thr);
     else
-      splice_vec_kernel<false><<<grid, 256, 0, st>>>((const float4*)in, (float4*)out, n, hw4, chunks, bank, bank_len, bank_idx, thr);
+      launch_pdl(splice_vec_kernel<false>, grid, 256, 0, st, g_sample_pdl.load() != 0, (const float4*)in, (float4*)out, n, hw4, chunks, bank, bank_len, bank_idx, thr);
   } else {
     const int64_t nwork = frames * hw;
     const int grid = grid_for(nwork, 256, 16);
