@@ -48,9 +48,13 @@ def main():
     name = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     kr = list(csv.reader(io.StringIO(name)))
     kname = kr[2][kr[0].index("Kernel Name")]
-    m = re.match(r"(?:void )?(\w+)<([^>]*)>", kname)
-    base, targs = m.group(1), [a.strip() for a in m.group(2).split(",")]
-    pat = "%d%sI" % (len(base), base) + "".join("L[ib]%sE" % {"true": "1", "false": "0"}.get(a, a) for a in targs) + "E"  
+    m = re.match(r"(?:void )?(?:\w+::)*(\w+)<([^>]*)>", kname)
+    if m:
+        base, targs = m.group(1), [a.strip() for a in m.group(2).split(",")]
+        pat = "%d%sI" % (len(base), base) + "".join("L[ib]%sE" % {"true": "1", "false": "0"}.get(a, a) for a in targs) + "E"
+    else:   # not a template
+        base = re.match(r"(?:void )?(?:\w+::)*(\w+)", kname).group(1)
+        pat = "%d%sE" % (len(base), base)
     # bools are printed as 0/1 by ncu: try both encodings
     cands = [pat]
     sl = []
