@@ -837,8 +837,9 @@ class ReplayBuffer(object):
         for chunk in chunks:
             start, end = persist.parse_chunk_name(chunk)
             payload = persist.load_chunk(os.path.join(save_dir, chunk), LazyFrames)
-            assert self.idx == start, \
-                f"self.idx: {self.idx} DNE start: {start} for save_dir: {save_dir}. Current chunk is {chunk}. Chucks: {chunks}."
+            assert self.idx == start, (     # same condition and exception type as src/utils.py:188-190
+                f"ReplayBuffer.load: chunk {chunk} of {save_dir} starts at slot {start} but the write cursor is at {self.idx} "
+                f"(chunks must be contiguous and loaded in order; found {chunks})")
             pairs = payload[0]
             n = len(pairs)
             if start + n > self.capacity:
