@@ -7,12 +7,12 @@
 // which in the unfused form costs four kernels and 2.2 MB of HBM traffic per sample; fused, every u8 frame is read
 // once and only the final f32 tensors are written (952 560 B per sample for AugCL's splice-conv at 9x84x84).
 //
-// Work unit = a band of kFBand rows of one RGB frame (3 u8 planes) of one (tensor, sample).  The units of a launch
-// are laid out obs-first and split over the persistent CTAs by COST (an obs unit writes several tensors and may
-// convolve; a next_obs unit is a plain copy), contiguously, so a CTA walks consecutive bands of the same frame and
-// re-reads its halo rows out of L2.  Per unit, one lane starts <= 6 bulk copies (cp.async.bulk, SASS UBLKCP): the
-// hull of source rows of the 3 planes and, for splice / overlay, the matching rows of the 3 background planes;
-// they land in a 2-deep stage ring guarded by mbarriers while the CTA works on the previous unit.
+// Work unit = a band of rows (kFBand for conv chains, else p.band) of one RGB frame (3 u8 planes) of one (tensor, sample).
+// Units are handed out by ticket (guided self-scheduling on a counter in the ring handle, one set per stream) to
+// persistent, warp-specialised CTAs: a producer warp decodes units and starts <= 6 bulk copies per unit (cp.async.bulk,
+// SASS UBLKCP: the hull of source rows of the 3 planes and, for splice / overlay, the matching rows of the 3 background
+// planes) into a ring of stages; A-warps run the elementwise phase out of a stage; conv chains hand an f32 tile over to
+// B-warps.  All hand-overs are mbarriers (see "CTA roles" below).
 //   phase A (elementwise): thread = 4 pixels x 3 channels of one tile row.  Plain word = 1 LDS.32; shifted word =
 //     2 LDS.32 + funnel shift + PRMT replicate selector (as in ring_sample_band_kernel); HSV mask / overlay in
 //     registers; direct outputs are STG.128; the conv input goes to an f32 tile in shared memory.
@@ -34,9 +34,9 @@ std::atomic<int> g_fused_skip{0};        // TIMING EXPERIMENTS ONLY (wrong resul
 std::atomic<int> g_fused_band{0};        // 0 = auto (non-conv chains: 14 or 7 rows)
 std::atomic<int> g_fused_fast_mask{1};   // 0: always the float HSV path (A/B and the exhaustive equivalence test)
 
-constexpr int kFHeader = 1664;   // mbarriers, per-stage flags and metas, tile metas, conv weights (per stage and per tile)
-constexpr int kFBand = 12;        // conv chains: 12 rows + 2 halo rows = 14 tile rows = two rounds of 7 rows
-constexpr int kFBandNoConv = 14;  // every other chain: 14 rows = two full rounds, 84 = 6 bands
+constexpr int kFHeader = 1664;   // mbarriers, per-stage flags, tile metas, the unit-meta ring, conv weights per tile
+constexpr int kFBand = 12;        // conv chains: 12 rows + 2 halo rows = 14 tile rows = 294 items = two rounds of 160 A-threads
+constexpr int kFBandNoConv = 14;  // every other chain: 84 = 6 bands
 
 struct FusedParams {
   SampleParams sp;          // stores, draw sources, scalar gather (sp.out unused)
