@@ -559,96 +559,132 @@ ring_sample_fused_kernel(const __grid_constant__ FusedParams p, const __grid_con
       if (tcount >= 2) mbar_wait(&tempty[t], (uint32_t)((tcount >> 1) - 1) & 1u);   // the B-warps have left tile t
       if (tid == 0) { TileMeta tm; tm.o_aug = m.o_aug; tm.r0 = m.r0; tm.rows = m.rows; tm.valid = 1; tm.sample = m.sample; tmeta[t] = tm; }
     }
-    for (int pr = pr0, q4 = q0; pr < trows;) {
-      const int r = clampi(m.r0 + pr - hal, 0, H - 1);
-      const bool own = (!CONV || (pr >= 1 && pr <= m.rows)) && !(p.skip & 4);   // halo rows only feed the conv tile
-      const size_t oo = (size_t)r * W + 4 * q4;              // offset inside plane 0; planes are H*W apart
-      uint32_t Aw[3], Ow[3];
-      if (aug_sh) {
-        load_shift(r, q4, Aw);
-        if (own && m.o_shift) store3(m.o_shift, oo, Aw);
-        if (own && m.o_plain) { load_plain(r, q4, Ow); store3(m.o_plain, oo, Ow); }
-      } else {
-        load_plain(r, q4, Aw);
-        if (own && m.o_plain) store3(m.o_plain, oo, Aw);
-        if (own && m.o_shift) { load_shift(r, q4, Ow); store3(m.o_shift, oo, Ow); }
-      }
-      float v[3][4];
-      if (PRE == kPreSpliceFast) {
-        // default thresholds (hue = sat = 0): the HSV test of pixel.cuh:hsv_gt only compares, and v -> v/255 is strictly
-        // increasing, so mask and select run on the raw bytes, four pixels per instruction (splice_keep_bytes);
-        // tests/: all 2^24 colours against the float path.
-        const int ga = m.gkoff + r * W + 4 * q4;
-        const uint32_t keep = splice_keep_bytes(Aw[0], Aw[1], Aw[2], p.thr_k, p.thr_c7);
-#pragma unroll
-        for (int ci = 0; ci < 3; ++ci) {
-          const uint32_t gw = *reinterpret_cast<const uint32_t*>(gb + ci * p.bank_stage + ga);
-          const float4 t4 = bytes_to_float4((Aw[ci] & keep) | (gw & ~keep));
-          // splice returns (x/255 or bg/255) * 255; as conv input the raw byte is the same value to 1 ulp
-          v[ci][0] = CONV ? t4.x : div255(t4.x) * 255.0f; v[ci][1] = CONV ? t4.y : div255(t4.y) * 255.0f;
-          v[ci][2] = CONV ? t4.z : div255(t4.z) * 255.0f; v[ci][3] = CONV ? t4.w : div255(t4.w) * 255.0f;
+    // one row of one 4-pixel group: the direct outputs of the row (plain / shifted) are stored, v = the chain's value
+    // before the conv (conv chains) or the augmented output (other chains)
+    auto row_values = [&](int pr, int q4, float (&v)[3][4], size_t& oo_out) {
+        const int r = clampi(m.r0 + pr - hal, 0, H - 1);
+        const bool own = (!CONV || (pr >= 1 && pr <= m.rows)) && !(p.skip & 4);   // halo rows only feed the conv tile
+        const size_t oo = (size_t)r * W + 4 * q4;              // offset inside plane 0; planes are H*W apart
+        uint32_t Aw[3], Ow[3];
+        if (aug_sh) {
+          load_shift(r, q4, Aw);
+          if (own && m.o_shift) store3(m.o_shift, oo, Aw);
+          if (own && m.o_plain) { load_plain(r, q4, Ow); store3(m.o_plain, oo, Ow); }
+        } else {
+          load_plain(r, q4, Aw);
+          if (own && m.o_plain) store3(m.o_plain, oo, Aw);
+          if (own && m.o_shift) { load_shift(r, q4, Ow); store3(m.o_shift, oo, Ow); }
         }
-      } else {
-        float a[3][4];
-#pragma unroll
-        for (int ci = 0; ci < 3; ++ci) {
-          const float4 t4 = bytes_to_float4(Aw[ci]);
-          a[ci][0] = t4.x; a[ci][1] = t4.y; a[ci][2] = t4.z; a[ci][3] = t4.w;
-        }
-        if (kBank) {
-          float g[3][4];
+        if (PRE == kPreSpliceFast) {
+          // default thresholds (hue = sat = 0): the HSV test of pixel.cuh:hsv_gt only compares, and v -> v/255 is strictly
+          // increasing, so mask and select run on the raw bytes, four pixels per instruction (splice_keep_bytes);
+          // tests/: all 2^24 colours against the float path.
           const int ga = m.gkoff + r * W + 4 * q4;
+          const uint32_t keep = splice_keep_bytes(Aw[0], Aw[1], Aw[2], p.thr_k, p.thr_c7);
 #pragma unroll
           for (int ci = 0; ci < 3; ++ci) {
-            const float4 g4 = bytes_to_float4(*reinterpret_cast<const uint32_t*>(gb + ci * p.bank_stage + ga));
-            g[ci][0] = g4.x; g[ci][1] = g4.y; g[ci][2] = g4.z; g[ci][3] = g4.w;
-          }
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            if (PRE == kPreOverlay) {
-#pragma unroll
-              for (int ci = 0; ci < 3; ++ci) v[ci][j] = overlay_px(a[ci][j], div255(g[ci][j]), p.oma, p.alpha);
-            } else {
-              const bool keep = splice_keep(div255(a[0][j]), div255(a[1][j]), div255(a[2][j]), p.thr);
-#pragma unroll
-              for (int ci = 0; ci < 3; ++ci) {
-                const float sel = keep ? a[ci][j] : g[ci][j];
-                v[ci][j] = CONV ? sel : div255(sel) * 255.0f;
-              }
-            }
+            const uint32_t gw = *reinterpret_cast<const uint32_t*>(gb + ci * p.bank_stage + ga);
+            const float4 t4 = bytes_to_float4((Aw[ci] & keep) | (gw & ~keep));
+            // splice returns (x/255 or bg/255) * 255; as conv input the raw byte is the same value to 1 ulp
+            v[ci][0] = CONV ? t4.x : div255(t4.x) * 255.0f; v[ci][1] = CONV ? t4.y : div255(t4.y) * 255.0f;
+            v[ci][2] = CONV ? t4.z : div255(t4.z) * 255.0f; v[ci][3] = CONV ? t4.w : div255(t4.w) * 255.0f;
           }
         } else {
-#pragma unroll
-          for (int ci = 0; ci < 3; ++ci)
-#pragma unroll
-            for (int j = 0; j < 4; ++j) v[ci][j] = a[ci][j];
-        }
-      }
-      if (CONV) {
-        // tile row pr -> lane .x of row pair pr (pr < kFPairs) and / or lane .y of row pair pr - kFHalf (pr >= kFHalf);
-        // pixels 4q4 .. 4q4+3 are columns c' = 4q4+1 .. 4q4+4: A0[q4].hi, A1[q4].lo, A1[q4].hi, A0[q4+1].lo
-        auto put = [&](float* tb) {
+          float a[3][4];
 #pragma unroll
           for (int ci = 0; ci < 3; ++ci) {
-            float* tp = tb + ci * kFPairs * TROW;
-            tp[2] = v[ci][0]; tp[TA1] = v[ci][1]; tp[TA1 + 2] = v[ci][2]; tp[4] = v[ci][3];
-            if (q4 == 0) tp[0] = v[ci][0];              // column -1: replicate
-            if (q4 == nq - 1) tp[6] = v[ci][3];         // column W
+            const float4 t4 = bytes_to_float4(Aw[ci]);
+            a[ci][0] = t4.x; a[ci][1] = t4.y; a[ci][2] = t4.z; a[ci][3] = t4.w;
           }
-        };
-        // every tile row has one home (branch-free); tile rows kFHalf, kFHalf + 1 are also lane .y of row pairs 0, 1
-        if (!(p.skip & 2)) {
-          put(tile + (pr < kFPairs ? pr * TROW : (pr - kFHalf) * TROW + 1) + 4 * q4);
-          if (pr >= kFHalf && pr < kFPairs) put(tile + (pr - kFHalf) * TROW + 4 * q4 + 1);
+          if (kBank) {
+            float g[3][4];
+            const int ga = m.gkoff + r * W + 4 * q4;
+#pragma unroll
+            for (int ci = 0; ci < 3; ++ci) {
+              const float4 g4 = bytes_to_float4(*reinterpret_cast<const uint32_t*>(gb + ci * p.bank_stage + ga));
+              g[ci][0] = g4.x; g[ci][1] = g4.y; g[ci][2] = g4.z; g[ci][3] = g4.w;
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              if (PRE == kPreOverlay) {
+#pragma unroll
+                for (int ci = 0; ci < 3; ++ci) v[ci][j] = overlay_px(a[ci][j], div255(g[ci][j]), p.oma, p.alpha);
+              } else {
+                const bool keep = splice_keep(div255(a[0][j]), div255(a[1][j]), div255(a[2][j]), p.thr);
+#pragma unroll
+                for (int ci = 0; ci < 3; ++ci) {
+                  const float sel = keep ? a[ci][j] : g[ci][j];
+                  v[ci][j] = CONV ? sel : div255(sel) * 255.0f;
+                }
+              }
+            }
+          } else {
+#pragma unroll
+            for (int ci = 0; ci < 3; ++ci)
+#pragma unroll
+              for (int j = 0; j < 4; ++j) v[ci][j] = a[ci][j];
+          }
         }
-      } else {
+      oo_out = oo;
+    };
+    if (!CONV) {
+      for (int pr = pr0, q4 = q0; pr < trows;) {
+        float v[3][4];
+        size_t oo;
+        row_values(pr, q4, v, oo);
 #pragma unroll
         for (int ci = 0; ci < 3; ++ci)
           st_global_f4(reinterpret_cast<float4*>(m.o_aug + oo + ci * HW),
                        fin4<NORM>(make_float4(v[ci][0], v[ci][1], v[ci][2], v[ci][3])));
+        q4 += dq; pr += dpr;
+        if (q4 >= nq) { q4 -= nq; ++pr; }
       }
-      q4 += dq; pr += dpr;
-      if (q4 >= nq) { q4 -= nq; ++pr; }
+    } else {
+      // Conv chains.  An item is a 4-pixel group of TWO tile rows that share a row pair of the tile -- (g, g + kFHalf) for
+      // g < kFHalf -- so the thread holds both lanes of every float2 and stores whole 16- and 8-byte pieces (A1[q4]; the
+      // halves of A0[q4], A0[q4+1]): 3 stores per channel for two rows where single rows need 8 four-byte stores that
+      // conflict 4-way (the tile stores were 13 % of the kernel in the timing experiments).  The last two tile rows
+      // (item row kFHalf) are lane .y of row pairs kFHalf, kFHalf + 1, whose lane .x -- tile rows kFHalf, kFHalf + 1 -- is
+      // stored a second time by the items that computed them as lane .y of pairs 0, 1.
+      auto put = [&](float* tb, const float (&v)[3][4], int q4) {   // one lane (.x or .y) of a row pair, four-byte stores
+#pragma unroll
+        for (int ci = 0; ci < 3; ++ci) {
+          float* tp = tb + ci * kFPairs * TROW;
+          tp[2] = v[ci][0]; tp[TA1] = v[ci][1]; tp[TA1 + 2] = v[ci][2]; tp[4] = v[ci][3];
+          if (q4 == 0) tp[0] = v[ci][0];              // column -1: replicate
+          if (q4 == nq - 1) tp[6] = v[ci][3];         // column W
+        }
+      };
+      const int nitem = (kFHalf + 1) * nq;
+      for (int it = tid; it < nitem; it += NTA) {
+        const int g = it / nq, q4 = it - g * nq;
+        const int r1 = g < kFHalf ? g : 2 * kFHalf, r2 = g < kFHalf ? g + kFHalf : 2 * kFHalf + 1;   // tile rows of the item
+        float vlo[3][4], v[3][4];
+        size_t oo;
+        if (r1 < trows) row_values(r1, q4, vlo, oo);
+        if (r2 < trows) row_values(r2, q4, v, oo);
+        if (p.skip & 2) continue;
+        float* tb = tile + 4 * q4;
+        if (g < kFHalf) {
+          if (r2 < trows) {          // both lanes of row pair g
+#pragma unroll
+            for (int ci = 0; ci < 3; ++ci) {
+              float* tp = tb + (ci * kFPairs + g) * TROW;
+              *reinterpret_cast<float2*>(tp + 2) = make_float2(vlo[ci][0], v[ci][0]);
+              *reinterpret_cast<float4*>(tp + TA1) = make_float4(vlo[ci][1], v[ci][1], vlo[ci][2], v[ci][2]);
+              *reinterpret_cast<float2*>(tp + 4) = make_float2(vlo[ci][3], v[ci][3]);
+              if (q4 == 0) *reinterpret_cast<float2*>(tp) = make_float2(vlo[ci][0], v[ci][0]);
+              if (q4 == nq - 1) *reinterpret_cast<float2*>(tp + 6) = make_float2(vlo[ci][3], v[ci][3]);
+            }
+            if (g < 2) put(tb + (g + kFHalf) * TROW, v, q4);      // tile row kFHalf + g is also lane .x of pair kFHalf + g
+          } else if (r1 < trows) {   // a short band: lane .x only
+            put(tb + g * TROW, vlo, q4);
+          }
+        } else {                     // tile rows 2 kFHalf, 2 kFHalf + 1: lane .y of pairs kFHalf, kFHalf + 1
+          if (r1 < trows) put(tb + kFHalf * TROW + 1, vlo, q4);
+          if (r2 < trows) put(tb + (kFHalf + 1) * TROW + 1, v, q4);
+        }
+      }
     }
     if (CONV && p.weights != nullptr && tid < 81) {   // -> [(ci*9 + ky*3 + kx)*4 + co], scaled for conv_sigmoid
       const int co = tid / 27, tap = tid - co * 27;
