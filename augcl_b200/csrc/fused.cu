@@ -833,7 +833,7 @@ extern "C" int augcl_ring_sample_fused(augcl_ring* r, const augcl_fused_desc* d,
   p.tile_rs = tile_row_floats(r->W);
   const size_t tile_bytes = has_conv ? 2 * 3 * (size_t)kFPairs * p.tile_rs * sizeof(float) : 0;   // two tiles
   // stage ring depth: the producer warp runs this many units ahead of the A-warps (scripts/bench_fused.py --opts)
-  p.stages = g_fused_stages.load() > 0 ? g_fused_stages.load() : 3;
+  p.stages = g_fused_stages.load() > 0 ? g_fused_stages.load() : ((has_conv && B >= 512) ? 4 : 3);   // measured (r03h sweep)
   if (p.stages > kFMaxStages) p.stages = kFMaxStages;
   const size_t budget = (228 * 1024) / (has_conv ? 3 : 4) - 1024;   // 3 (conv) / 4 CTAs per SM
   while (p.stages > 1 && kFHeader + (size_t)p.stages * p.stage_bytes + tile_bytes > budget) --p.stages;
