@@ -704,7 +704,7 @@ def main():
                                  "start event, see `timing`).  Consecutive launches overlap: with programmatic dependent launch "
                                  "the read-only start of launch n+1 (draws, first bulk copies) runs during the tail of launch n; "
                                  "every store waits for launch n to complete.  One launch alone: timing.isolated_launch_ms",
-                         "traffic_note": "ncu --set full, one isolated launch (profiles/r01_ncu_ring_sample.csv): 16.2 MB read = the "
+                         "traffic_note": "ncu --set full, one isolated launch (profiles/r02_ncu_ring_sample.csv): 16.2 MB read = the "
                                          "launch's u8 inputs exactly, 8.3 MB written -- the other 57 MB of its 65 MB f32 output are "
                                          "still dirty lines in the 126 MB L2 when the kernel ends and reach DRAM during later "
                                          "launches; no re-reads (traffic below the algorithmic bytes, not above)"},
@@ -712,6 +712,11 @@ def main():
         }
         if sweep is not None:
             line["batch_sweep"] = sweep
+            line["batch_sweep_note"] = ("K launches back to back per batch size, fresh indices, rotating outputs; frac = algorithmic bytes / time / "
+                                        "the measured COPY bandwidth (MEASURED_PEAKS.json).  At batch 128 consecutive launches overlap through "
+                                        "programmatic dependent launch and most of a launch's 65 MB output is still dirty in the 126 MB L2 "
+                                        "when the next one starts, so frac can read slightly above 1.0 there (a pure write stream reaches "
+                                        "~6.8 TB/s on this part, the copy figure is 6.55)")
         if world == 1 and not args.no_sweep:
             line["fused_configs"] = fused_configs(res)
             line["dedup_ring"] = dedup_ring(res)
