@@ -338,6 +338,40 @@ def test_two_streams_sample_one_ring_concurrently(U, A):
             assert torch.equal(got["obs_shift"], want["obs_shift"]) and torch.equal(got["next_obs"], want["next_obs"]), rep
 
 
+@pytest.mark.parametrize("H,W,k,pad,B", [(8, 8, 1, 2, 5), (12, 16, 2, 3, 7), (64, 48, 2, 4, 40), (128, 128, 1, 4, 9), (16, 128, 3, 2, 12),
+                                         (52, 8, 2, 1, 6)])
+def test_fused_geometries_equal_the_unfused_chain(U, A, H, W, k, pad, B):
+    """The generic-width instantiations: non-square frames, the narrowest / widest supported rows, bands shorter than a
+    tile, on every chain: all five image outputs against the unfused product kernels (themselves oracle-checked)."""
+    buf = U.ReplayBuffer((3 * k, H, W), (4,), 300, B)
+    buf.fill_synthetic(seed=H * 7 + W)
+    A.set_background_bank(torch.randint(0, 256, (13, 3, H, W), dtype=torch.uint8, device="cuda"))
+    try:
+        g = torch.Generator().manual_seed(H + W)
+        idxs = torch.randint(0, 300, (B,), generator=g).numpy()
+        off = {"obs": torch.randint(0, 2 * pad + 1, (B, 2), generator=g).numpy(),
+               "next_obs": torch.randint(0, 2 * pad + 1, (B, 2), generator=g).numpy()}
+        rows = torch.randint(0, 13, (B,), generator=g).numpy()
+        wt = torch.randn((B, 3, 3, 3, 3), generator=g)
+        obs, _, _, nxt, _ = buf.sample(idxs=idxs)
+        sh = A.random_shift(obs, pad, offsets=off["obs"])
+        nsh = A.random_shift(nxt, pad, offsets=off["next_obs"])
+        fns = {"splice": lambda x: A.splice(x, bank_idx=rows), "CS_splice": lambda x: A.CS_splice(x, bank_idx=rows),
+               "overlay": lambda x: A.random_overlay(x, bank_idx=rows), "conv": lambda x: A.random_conv(x, weights=wt)}
+        for chain in ["splice-conv", "overlay", "conv", "CS_splice-conv", "splice", "overlay-conv"]:
+            for aug_input in ["plain", "shift"]:
+                out = buf.sample_fused(idxs=idxs, pad=pad, data_aug=chain, aug_input=aug_input, offsets=off, bank_idx=rows, weights=wt,
+                                       want=("obs", "obs_shift", "obs_aug", "next_obs", "next_obs_shift"))
+                assert torch.equal(out["obs"], obs) and torch.equal(out["next_obs"], nxt), (chain, aug_input)
+                assert torch.equal(out["obs_shift"], sh) and torch.equal(out["next_obs_shift"], nsh), (chain, aug_input)
+                x = sh if aug_input == "shift" else obs
+                for key in chain.split("-"):
+                    x = fns[key](x)
+                assert (out["obs_aug"] - x).abs().max().item() / 255.0 <= TOL_NORM, (chain, aug_input)
+    finally:
+        A.set_background_bank(None)
+
+
 def test_in_kernel_conv_weights_equal_explicit_weights(U, A):
     """desc.conv_weights == NULL: the 81 N(0,1) weights per sample are drawn inside the fused kernel (by the B-warps) and
     are the values augcl_rng_fill_normal(out, B*81, seed, conv_subsequence) writes -- AugCL's update is ONE launch."""
