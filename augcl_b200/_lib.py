@@ -57,6 +57,7 @@ SIGNATURES = {
     "augcl_ring_get": (_i, [_p, _i64, _i64, _p, _p, _p, _p, _p, _p]),
     "augcl_ring_fill_synthetic": (_i, [_p, _i64, _u64, _p]),
     "augcl_ring_sample": (_i, [_p, _p, _i, _p, _p, _p, _p, _p, _i, _p, _p, _i, _i, _p]),
+    "augcl_ring_sample_noalloc": (_i, [_p, _p, _i, _p, _p, _p, _p, _p, _i, _p, _p, _i, _i, _p]),
     "augcl_ring_sample_ex": (_i, [_p, _i, _p, _i64, _i, _p, _p, _p, _p, _p, _i, _i, _p, _p, _i, _i, _u64, _u64, _p]),
     "augcl_ring_sample_curl": (_i, [_p, _i, _p, _i64, _i, _p, _p, _p, _p, _p, _p, _i, _p, _p, _p, _i, _i, _u64, _u64, _p]),
     "augcl_ring_sample_views": (_i, [_p, _i, _p, _i64, _i, _i, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _u64, _u64, _p]),

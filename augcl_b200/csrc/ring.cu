@@ -737,4 +737,76 @@ int augcl_ring_sample_views(augcl_ring* r, int idx_src, const int64_t* idx, int6
                      nullptr, pad_or_size, normalize, seed, subsequence, (cudaStream_t)stream, n_views, view_src, outs, offs);
 }
 
+// ------------------------------------------------------------------------------------------------
+// augcl_ring_sample_noalloc: augcl_ring_sample_ex for HOST draws without any allocation (no counterpart in the
+// reference).  augcl_ring_sample_ex stages host indices / offsets of
+// batches beyond the inline limit through stream-ordered scratch (cudaMallocFromPoolAsync above); here that scratch is
+// a file-scope device array of fixed size, so the call is usable where allocation is forbidden.
+// Layout: [idx int64 kNoAllocMaxBatch][obs offsets int32 2*kNoAllocMaxBatch][next_obs offsets int32 2*kNoAllocMaxBatch].
+// ------------------------------------------------------------------------------------------------
+constexpr int kNoAllocMaxBatch = AUGCL_NOALLOC_MAX_BATCH;
+static __device__ __align__(256) unsigned char g_noalloc_scratch[(size_t)kNoAllocMaxBatch * 24];
+
+// Device address of the array on the CURRENT device (the symbol's name is only a host-side stand-in): resolved once
+// per device with that device current, remembered afterwards.
+static int noalloc_scratch_ptr(int device, unsigned char** out) {
+  static std::atomic<unsigned char*> cache[64];
+  AUGCL_REQUIRE(device >= 0 && device < 64, "augcl_ring_sample_noalloc: device %d outside [0, 64)", device);
+  unsigned char* ptr = cache[device].load(std::memory_order_acquire);
+  if (!ptr) {
+    void* sym = nullptr;
+    AUGCL_CUDA(cudaGetSymbolAddress(&sym, g_noalloc_scratch));
+    ptr = static_cast<unsigned char*>(sym);
+    cache[device].store(ptr, std::memory_order_release);
+  }
+  *out = ptr;
+  return AUGCL_OK;
+}
+
+int augcl_ring_sample_noalloc(augcl_ring* r, const int64_t* idx, int B, float* out_obs, float* out_next, float* out_act,
+                              float* out_rew, float* out_nd, int aug_mode, const int32_t* off_obs, const int32_t* off_next,
+                              int pad_or_size, int normalize, augcl_stream stream) {
+  const char* who = "augcl_ring_sample_noalloc";
+  AUGCL_REQUIRE(r, "%s: ring is NULL", who);
+  AUGCL_REQUIRE(idx, "%s: idx is NULL", who);
+  AUGCL_REQUIRE(B > 0, "%s: B must be positive (got %d)", who, B);
+  if (B > kNoAllocMaxBatch)
+    AUGCL_FAIL(AUGCL_ERR_UNSUPPORTED, "%s: batch %d exceeds the fixed scratch (AUGCL_NOALLOC_MAX_BATCH = %d)", who, B,
+               kNoAllocMaxBatch);
+  AUGCL_REQUIRE(aug_mode == AUGCL_AUG_NONE || aug_mode == AUGCL_AUG_SHIFT || aug_mode == AUGCL_AUG_SHIFT_OBS,
+                "%s: aug_mode must be NONE, SHIFT or SHIFT_OBS (got %d)", who, aug_mode);
+  // the host draws are validated like augcl_ring_sample_ex's (the reference raises IndexError)
+  for (int b = 0; b < B; ++b)
+    AUGCL_REQUIRE(idx[b] >= 0 && idx[b] < r->capacity, "%s: index %lld (position %d) out of range [0, %lld)", who,
+                  (long long)idx[b], b, (long long)r->capacity);
+  const int32_t* off[2] = {off_obs, aug_mode == AUGCL_AUG_SHIFT ? off_next : nullptr};
+  if (aug_mode != AUGCL_AUG_NONE) {
+    AUGCL_REQUIRE(pad_or_size >= 0 && pad_or_size <= 63, "%s: pad %d outside [0, 63]", who, pad_or_size);
+    for (int t = 0; t < 2; ++t)
+      if (off[t])
+        for (int e = 0; e < 2 * B; ++e)
+          AUGCL_REQUIRE(off[t][e] >= 0 && off[t][e] <= 2 * pad_or_size, "%s: offset %d (tensor %d, element %d) outside [0, %d]",
+                        who, off[t][e], t, e, 2 * pad_or_size);
+  }
+  DeviceGuard g(r->device);
+  AUGCL_CUDA(g.err);
+  unsigned char* sp = nullptr;
+  if (int rc = noalloc_scratch_ptr(r->device, &sp)) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t ib = (size_t)kNoAllocMaxBatch * 8;
+  // every byte the kernel reads is rewritten here: nothing in the array has to start at zero
+  AUGCL_CUDA(cudaMemcpyAsync(sp, idx, (size_t)B * 8, cudaMemcpyHostToDevice, st));
+  const int32_t* d_off[2] = {nullptr, nullptr};
+  if (aug_mode != AUGCL_AUG_NONE)
+    for (int t = 0; t < 2; ++t)
+      if (off[t]) {
+        unsigned char* dst = sp + ib + (size_t)t * kNoAllocMaxBatch * 8;
+        AUGCL_CUDA(cudaMemcpyAsync(dst, off[t], (size_t)B * 8, cudaMemcpyHostToDevice, st));
+        d_off[t] = reinterpret_cast<const int32_t*>(dst);
+      }
+  // DEVICE draws from here on: the same kernels as augcl_ring_sample, no scratch, no allocation
+  return sample_impl(who, r, AUGCL_SRC_DEVICE, reinterpret_cast<const int64_t*>(sp), 0, B, out_obs, out_next, out_act, out_rew,
+                     out_nd, aug_mode, AUGCL_SRC_DEVICE, d_off[0], d_off[1], pad_or_size, normalize, 0, 0, st);
+}
+
 }  // extern "C"

@@ -262,6 +262,24 @@ typedef struct augcl_fused_desc {
 
 int augcl_ring_sample_fused(augcl_ring* ring, const augcl_fused_desc* desc, augcl_stream stream);
 
+/* No counterpart in the reference: added for callers that must not allocate
+ * (code under CUDA-graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * augcl_ring_sample_ex with HOST indices / offsets stages batches beyond its inline limit through stream-ordered
+ * scratch (cudaMallocFromPoolAsync); this variant stages them through a fixed file-scope device array instead
+ * (24 bytes x AUGCL_NOALLOC_MAX_BATCH = 384 KiB, held by every GPU that loads the library until exit) and calls no
+ * cudaMalloc / cudaFree / allocating routine.  Same outputs as augcl_ring_sample / _ex for the same draws.
+ *   idx          HOST int64[B], each in [0, capacity) (AUGCL_ERR_BAD_ARG otherwise)
+ *   off_obs / off_next   HOST int32[B,2] shift offsets in [0, 2*pad], NULL = identity for that tensor
+ *   aug_mode     AUGCL_AUG_NONE, AUGCL_AUG_SHIFT or AUGCL_AUG_SHIFT_OBS; outputs as for augcl_ring_sample
+ *   B > AUGCL_NOALLOC_MAX_BATCH is rejected with AUGCL_ERR_UNSUPPORTED.
+ * All calls (on any ring of a device) share the one array, which keeps the last call's draws; every byte a call reads
+ * is rewritten by that call, nothing needs clearing.  Calls that overlap on the GPU (different streams) RACE on it:
+ * issue them on one stream, or order them with events. */
+#define AUGCL_NOALLOC_MAX_BATCH 16384
+int augcl_ring_sample_noalloc(augcl_ring* ring, const int64_t* idx, int B, float* out_obs, float* out_next,
+                              float* out_act, float* out_rew, float* out_nd, int aug_mode, const int32_t* off_obs,
+                              const int32_t* off_next, int pad_or_size, int normalize, augcl_stream stream);
+
 /* ------------------------------------------------------------------------------------------
  * Stand-alone augmentations on f32 NCHW batches (in and out must not alias).
  * ------------------------------------------------------------------------------------------ */
