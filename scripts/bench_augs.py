@@ -39,7 +39,11 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--batches", default="128,256,2048")
     ap.add_argument("--only", default="")
+    ap.add_argument("--opts", default="", help="augcl_set_option pairs, e.g. conv_part=-1")
     a = ap.parse_args()
+    for kv in filter(None, a.opts.split(",")):
+        key, val = kv.split("=")
+        L.set_option(key, val)
     dev = torch.device("cuda", 0)
     g = torch.Generator().manual_seed(0)
     bank = torch.randint(0, 256, (4096, 3, S, S), generator=g, dtype=torch.uint8).to(dev)
