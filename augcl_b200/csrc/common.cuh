@@ -162,6 +162,21 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
       "r"(parity)
       : "memory");
 }
+// elect.sync over `mask` (every thread of `mask`, and only those, must execute it): true in exactly one of them.  Code
+// under the returned predicate is single-threaded BY CONSTRUCTION for ptxas, so instructions that take uniform-register
+// operands (UBLKCP) get plain R2UR moves instead of a divergence-safe loop (ELECT / R2UR / BRA.U.ANY per instruction).
+__device__ __forceinline__ bool elect_in(uint32_t mask) {
+  uint32_t leader;
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "elect.sync _|p, %1;\n"
+      "selp.u32 %0, 1, 0, p;\n"
+      "}\n"
+      : "=r"(leader)
+      : "r"(mask));
+  return leader != 0;
+}
 // global -> shared bulk copy; dst/src 16-B aligned, bytes a multiple of 16; completes on `bar`.
 __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
   asm volatile(

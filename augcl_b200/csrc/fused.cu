@@ -374,7 +374,7 @@ ring_sample_fused_kernel(const __grid_constant__ FusedParams p, const __grid_con
           more = false;
           break;
         }
-        if (lane == i) {
+        if (lane == i && elect_in(1u << i)) {   // (single lane, and ptxas knows it: no uniformisation loop around each UBLKCP)
           mbar_expect_tx(&full[s], 3 * (sbytes + gbytes));   // P % 16 == 0: the three planes share lead and length
           uint8_t* sb = stage + (size_t)s * p.stage_bytes;
 #pragma unroll
