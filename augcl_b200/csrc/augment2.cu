@@ -107,7 +107,9 @@ __global__ void __launch_bounds__(256) grayscale_vec_kernel(const float4* __rest
 // row-preserving permutations on whole 16-byte groups: identity, column flip (random_flip) and the half turn (rot90 by 2);
 // planes drawn a quarter turn (rot90 by 1 / 3, a transposition) take the scalar gather of permute_kernel, plane by plane
 __global__ void __launch_bounds__(256) permute_rows_vec_kernel(const float4* __restrict__ in, float4* __restrict__ out, int planes,
-                                                               int c, int h, int wq, const int32_t* __restrict__ flag, int mode) {
+                                                               int c, int h, int wq, const int32_t* __restrict__ flag, int mode,
+                                                               int use_tile) {
+  extern __shared__ __align__(16) float ptile[];   // quarter turns: the plane, row stride w + 1 (conflict-free column reads)
   const int n4 = h * wq;
   for (int plane = blockIdx.x; plane < planes; plane += gridDim.x) {
     const int f = flag[plane / c];
@@ -118,6 +120,33 @@ __global__ void __launch_bounds__(256) permute_rows_vec_kernel(const float4* __r
       const int w = wq * 4;
       const float* s1 = reinterpret_cast<const float*>(src);
       float* d1 = reinterpret_cast<float*>(dst);
+      if (use_tile) {
+        // transpose through shared memory: coalesced 16-byte reads in, coalesced 16-byte writes out, the transposed access
+        // (a column of the tile per output row) happens on the padded tile
+        const int ts = w + 1;
+        __syncthreads();                       // the previous plane's reads of the tile are done
+        for (int e = threadIdx.x; e < n4; e += 256) {
+          const int i = e / wq, q = e - i * wq;
+          const float4 v = __ldg(src + e);
+          float* t = ptile + i * ts + 4 * q;
+          t[0] = v.x; t[1] = v.y; t[2] = v.z; t[3] = v.w;
+        }
+        __syncthreads();
+        for (int e = threadIdx.x; e < n4; e += 256) {
+          const int i = e / wq, j = (e - i * wq) * 4;
+          // torch.rot90(x, r, [2, 3]):  r=1: out[i][j] = x[j][w-1-i];  r=3: x[h-1-j][i]
+          float4 o;
+          if (f == 1) {
+            const float* t = ptile + j * ts + (w - 1 - i);
+            o = make_float4(t[0], t[ts], t[2 * ts], t[3 * ts]);
+          } else {
+            const float* t = ptile + (h - 1 - j) * ts + i;
+            o = make_float4(t[0], t[-ts], t[-2 * ts], t[-3 * ts]);
+          }
+          dst[e] = o;
+        }
+        continue;
+      }
       for (int e = threadIdx.x; e < h * w; e += 256) {
         const int i = e / w, j = e - i * w;
         // torch.rot90(x, r, [2, 3]):  r=1: out[i][j] = x[j][w-1-i];  r=3: x[h-1-j][i]
@@ -309,8 +338,9 @@ static int launch_permute(const char* who, const float* in, float* out, int n, i
   const int planes = n * c;
   const int grid = planes < kNumSMs * 8 ? planes : kNumSMs * 8;
   if ((w & 3) == 0 && aligned(in, 16) && aligned(out, 16)) {
-    permute_rows_vec_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<const float4*>(in), reinterpret_cast<float4*>(out),
-                                                                  planes, c, h, w / 4, flag, mode);
+    const size_t tile = (mode == 1 && (size_t)h * (w + 1) * 4 <= 48 * 1024) ? (size_t)h * (w + 1) * 4 : 0;   // quarter turns only
+    permute_rows_vec_kernel<<<grid, 256, tile, (cudaStream_t)stream>>>(reinterpret_cast<const float4*>(in), reinterpret_cast<float4*>(out),
+                                                                     planes, c, h, w / 4, flag, mode, tile ? 1 : 0);
     AUGCL_LAUNCHED();
     return AUGCL_OK;
   }
