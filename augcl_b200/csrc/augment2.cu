@@ -251,33 +251,34 @@ __device__ __forceinline__ void hue_px(float& r, float& g, float& b, float hf) {
   b = i == 0 ? pp : i == 1 ? pp : i == 2 ? t : i == 3 ? v : i == 4 ? v : q;
 }
 
-__global__ void __launch_bounds__(256) color_jitter_kernel(float* __restrict__ imgs, const int32_t* __restrict__ sel, int hw,
+__global__ void __launch_bounds__(512, 2) color_jitter_kernel(float* __restrict__ imgs, const int32_t* __restrict__ sel, int hw,
                                                            JitterParams P) {
   extern __shared__ __align__(16) float jsm[];     // [3][hw]
-  __shared__ float s_red[8];
+  __shared__ float s_red[16];
+  const int NT = blockDim.x;     // 512: two CTAs (85 KB frame each at 84x84) = 32 warps per SM behind the divisions of the hue step
   float* fr = imgs + (int64_t)sel[blockIdx.x] * 3 * hw;
   const int tid = threadIdx.x;
-  for (int e = tid; e < 3 * hw; e += 256) jsm[e] = fr[e];
+  for (int e = tid; e < 3 * hw; e += NT) jsm[e] = fr[e];
   __syncthreads();
   for (int step = 0; step < 4; ++step) {
     const int op = P.order[step];
     if (!((P.enabled >> op) & 1)) continue;
     if (op == 1) {
       float part = 0.0f;
-      for (int px = tid; px < hw; px += 256) part += lum(jsm[px], jsm[hw + px], jsm[2 * hw + px]);
+      for (int px = tid; px < hw; px += NT) part += lum(jsm[px], jsm[hw + px], jsm[2 * hw + px]);
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
       if ((tid & 31) == 0) s_red[tid >> 5] = part;
       __syncthreads();
       float tot = 0.0f;
 #pragma unroll
-      for (int j = 0; j < 8; ++j) tot += s_red[j];
+      for (int j = 0; j < 16; ++j) tot += (j < (NT >> 5)) ? s_red[j] : 0.0f;
       const float other = P.omr[1] * __fdiv_rn(tot, (float)hw);
-      for (int e = tid; e < 3 * hw; e += 256) jsm[e] = clamp01(P.ratio[1] * jsm[e] + other);
+      for (int e = tid; e < 3 * hw; e += NT) jsm[e] = clamp01(P.ratio[1] * jsm[e] + other);
     } else if (op == 0) {
-      for (int e = tid; e < 3 * hw; e += 256) jsm[e] = clamp01(P.ratio[0] * jsm[e] + P.omr[0] * 0.0f);
+      for (int e = tid; e < 3 * hw; e += NT) jsm[e] = clamp01(P.ratio[0] * jsm[e] + P.omr[0] * 0.0f);
     } else {
-      for (int px = tid; px < hw; px += 256) {
+      for (int px = tid; px < hw; px += NT) {
         float r = jsm[px], g = jsm[hw + px], b = jsm[2 * hw + px];
         if (op == 2) {
           const float y = P.omr[2] * lum(r, g, b);
@@ -290,7 +291,7 @@ __global__ void __launch_bounds__(256) color_jitter_kernel(float* __restrict__ i
     }
     __syncthreads();
   }
-  for (int e = tid; e < 3 * hw; e += 256) fr[e] = jsm[e];
+  for (int e = tid; e < 3 * hw; e += NT) fr[e] = jsm[e];
 }
 }  // namespace augcl
 
@@ -405,7 +406,7 @@ int augcl_color_jitter(float* imgs, int frames, int h, int w, const int32_t* sel
   const size_t smem = (size_t)3 * h * w * sizeof(float);
   if (smem > 200 * 1024) AUGCL_FAIL(AUGCL_ERR_UNSUPPORTED, "augcl_color_jitter: %dx%d frame does not fit shared memory", h, w);
   if (int rc = ensure_dyn_smem(reinterpret_cast<const void*>(color_jitter_kernel), 200 * 1024)) return rc;
-  color_jitter_kernel<<<n_sel, 256, smem, (cudaStream_t)stream>>>(imgs, sel, h * w, P);
+  color_jitter_kernel<<<n_sel, 512, smem, (cudaStream_t)stream>>>(imgs, sel, h * w, P);
   AUGCL_LAUNCHED();
   return AUGCL_OK;
 }
