@@ -153,7 +153,11 @@ int augcl_ring_fill_synthetic(augcl_ring* ring, int64_t count, uint64_t seed, au
  * serialization (option "sample_pdl", default on): when the previous kernel of the stream is itself a sample kernel,
  * the read-only start of the next one -- the draws, the ring / refs / bank reads, its first bulk copies -- overlaps the
  * tail of the previous one; every store, and every access to the ring's schedule counters, waits for the previous
- * kernel to complete (griddepcontrol.wait).  After any other kernel or copy the launch is serialized as usual. */
+ * kernel to complete (griddepcontrol.wait).  After any other kernel or copy the launch is serialized as usual: a grid can
+ * only start early behind a predecessor that executed griddepcontrol.launch_dependents, and the only kernels that do are
+ * this library's (sample and stand-alone augmentation kernels), which write nothing but their float outputs -- never the
+ * ring, the refs table, the background bank or a draw array.  Draws or ring data written by any other kernel right before
+ * the call are therefore complete and visible (tests/test_gpu_replay_parity.py). */
 int augcl_ring_sample(augcl_ring* ring, const int64_t* idx, int B, float* out_obs, float* out_next,
                       float* out_act, float* out_rew, float* out_nd, int aug_mode,
                       const int32_t* off_obs, const int32_t* off_next, int pad_or_size,

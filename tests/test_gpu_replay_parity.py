@@ -431,3 +431,23 @@ def test_recycled_output_sets_behave_like_fresh_tensors(U):
     plain.fill_synthetic(seed=2)
     i = rng.randint(0, 256, 8)
     assert all(torch.equal(x, y) for x, y in zip(buf.sample(idxs=i), plain.sample(idxs=i)))
+
+
+def test_device_draws_written_just_before_the_launch_are_seen(U):
+    """The sample kernels read their draws and start their first bulk copies BEFORE griddepcontrol.wait (programmatic launch).
+    That is only allowed to overlap kernels that released their successor early -- this library's own kernels, which never
+    write draws or ring data.  A torch kernel that writes the index / offset tensors, or the ring fill, immediately before the
+    launch (no synchronize in between) must be fully visible: same result as the host-draw call."""
+    S, k, cap = 84, 3, 4000
+    for B in (128, 512):           # plane kernel / band-of-frames kernel
+        buf = U.ReplayBuffer((3 * k, S, S), (6,), cap, B)
+        for rep in range(4):
+            buf.fill_synthetic(seed=100 + rep)                                      # kernels, not synchronized
+            base = torch.arange(B, device="cuda", dtype=torch.int64)
+            idx_dev = (base * 7919 + 13 * rep) % cap                                  # written by torch kernels on the same stream
+            off_dev = ((base.view(B, 1) * 3 + torch.tensor([rep, 2 * rep + 1], device="cuda")) % 9).to(torch.int32)
+            got = buf.sample_drq(pad=4, idxs=idx_dev, offsets={"obs": off_dev, "next_obs": off_dev})
+            idx_h, off_h = idx_dev.cpu().numpy(), off_dev.cpu().numpy()
+            want = buf.sample_drq(pad=4, idxs=idx_h, offsets={"obs": off_h, "next_obs": off_h})
+            for g, w in zip(got, want):
+                assert torch.equal(g, w), (B, rep)
