@@ -418,10 +418,10 @@ __global__ void __launch_bounds__(kConvThreads, 6) random_conv_kernel(const floa
 __global__ void __launch_bounds__(kConvThreads, 7) random_conv_tma_kernel(const float* __restrict__ in, float* __restrict__ out,
                                                                           int frames, int k, int h, int w,
                                                                           const float* __restrict__ weights, int bands, int RS) {
-  extern __shared__ __align__(128) float csm[];
-  uint64_t* bars = reinterpret_cast<uint64_t*>(csm);       // 2 mbarriers (16 B), padded to 16 floats
-  float* wsm = csm + 16;                                   // [27][4]
-  float* tiles = csm + 16 + 27 * 4;                        // [2][3][kBand+2][RS]   (124 floats in: 16-B aligned)
+  extern __shared__ __align__(128) float ctsm[];
+  uint64_t* bars = reinterpret_cast<uint64_t*>(ctsm);      // 2 mbarriers (16 B), padded to 16 floats
+  float* wsm = ctsm + 16;                                  // [27][4]
+  float* tiles = ctsm + 16 + 27 * 4;                        // [2][3][kBand+2][RS]   (124 floats in: 16-B aligned)
   const int tile_floats = 3 * (kBand + 2) * RS;
   const int tid = threadIdx.x;
   const int nq = w >> 2;
@@ -662,7 +662,7 @@ __global__ void __launch_bounds__(256) overlay_vec_kernel(const float4* __restri
     g = __ldg(reinterpret_cast<const float4*>(bank) + boff);
   }
   const int64_t base = ((int64_t)i * 3 * k + ch) * hw4 + p4;
-  if (K > 0) {   // frame_stack known at compile time: all K loads are issued before the first use
+  if constexpr (K > 0) {   // frame_stack known at compile time: all K loads are issued before the first use
     float4 x[K > 0 ? K : 1];
 #pragma unroll
     for (int f = 0; f < K; ++f) x[f] = __ldg(in + base + (int64_t)f * 3 * hw4);
@@ -670,13 +670,13 @@ __global__ void __launch_bounds__(256) overlay_vec_kernel(const float4* __restri
     for (int f = 0; f < K; ++f)
       out[base + (int64_t)f * 3 * hw4] = make_float4(overlay_px(x[f].x, g.x, oma, alpha), overlay_px(x[f].y, g.y, oma, alpha),
                                                     overlay_px(x[f].z, g.z, oma, alpha), overlay_px(x[f].w, g.w, oma, alpha));
-    return;
-  }
-  for (int f = 0; f < k; ++f) {
-    const int64_t o = base + (int64_t)f * 3 * hw4;
-    const float4 x = __ldg(in + o);
-    out[o] = make_float4(overlay_px(x.x, g.x, oma, alpha), overlay_px(x.y, g.y, oma, alpha),
-                         overlay_px(x.z, g.z, oma, alpha), overlay_px(x.w, g.w, oma, alpha));
+  } else {
+    for (int f = 0; f < k; ++f) {
+      const int64_t o = base + (int64_t)f * 3 * hw4;
+      const float4 x = __ldg(in + o);
+      out[o] = make_float4(overlay_px(x.x, g.x, oma, alpha), overlay_px(x.y, g.y, oma, alpha),
+                           overlay_px(x.z, g.z, oma, alpha), overlay_px(x.w, g.w, oma, alpha));
+    }
   }
 }
 
