@@ -154,10 +154,21 @@ __global__ void __launch_bounds__(256) permute_rows_vec_kernel(const float4* __r
       }
       continue;
     }
-    for (int e = threadIdx.x; e < n4; e += 256) {
-      const int i = e / wq, q = e - i * wq;
-      const float4 v = __ldg(src + (fr ? h - 1 - i : i) * wq + (fc ? wq - 1 - q : q));
-      dst[e] = fc ? make_float4(v.w, v.z, v.y, v.x) : v;
+    for (int e0 = threadIdx.x; e0 < n4; e0 += 4 * 256) {   // four independent loads in flight per thread before the first store
+      float4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int e = e0 + u * 256;
+        if (e < n4) {
+          const int i = e / wq, q = e - i * wq;
+          v[u] = __ldg(src + (fr ? h - 1 - i : i) * wq + (fc ? wq - 1 - q : q));
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int e = e0 + u * 256;
+        if (e < n4) dst[e] = fc ? make_float4(v[u].w, v[u].z, v[u].y, v[u].x) : v[u];
+      }
     }
   }
 }
