@@ -143,6 +143,38 @@ def test_reference_update_runs_on_the_dropin(dropin, algo, S, kw):
     dropin.aug.set_background_bank(None)
 
 
+@pytest.mark.parametrize("algo,kw", [("augcl", dict(data_aug="splice-conv")), ("drq", {}), ("svea", dict(data_aug="overlay"))])
+def test_train_loop_pattern_add_then_update(dropin, algo, kw):
+    """src/train.py:251-256 in miniature: every step adds one transition (frames shared with the previous step, like
+    FrameStack) and runs one update() of the unmodified reference agent on the drop-in buffer -- 40 steps across the
+    staging flushes, the wrap-around of the write cursor, the recycled output sets and back-to-back sample launches."""
+    torch.manual_seed(1)
+    np.random.seed(1)
+    dropin.aug.seed(9)
+    dropin.aug.set_background_bank(None)
+    args = _args(algo, **kw)
+    buf = _fill(dropin.utils, 84, args.batch_size, cap=256)
+    start = buf.idx
+    agent = dropin.make_agent(obs_shape=(9, 84, 84), action_shape=(4,), args=args)
+    rng = np.random.RandomState(5)
+    frames = [rng.randint(0, 256, (3, 84, 84)).astype(np.uint8) for _ in range(3)]
+    log = _Log()
+    for step in range(40):
+        frames.append(rng.randint(0, 256, (3, 84, 84)).astype(np.uint8))
+        buf.add(dropin.utils.LazyFrames(frames[-4:-1]), rng.uniform(-1, 1, 4).astype(np.float32), float(rng.rand()),
+                dropin.utils.LazyFrames(frames[-3:]), False)
+        agent.update(buf, log, step)
+    torch.cuda.synchronize()
+    assert buf.idx == (start + 40) % 256 and buf.full          # 249 + 40: the write cursor wrapped around the ring
+    for k, v in log.rows.items():
+        assert math.isfinite(v), f"{algo}: {k} = {v}"
+    # the last transition added is what the ring returns for its slot
+    obs, _, _, nxt, _ = buf.sample(idxs=np.array([buf.idx - 1]))
+    assert torch.equal(obs[0].cpu(), torch.from_numpy(np.concatenate(frames[-4:-1])).float())
+    assert torch.equal(nxt[0].cpu(), torch.from_numpy(np.concatenate(frames[-3:])).float())
+    dropin.aug.set_background_bank(None)
+
+
 def test_apply_aug_kwargs_by_name_and_input_aliasing(dropin):
     """RAD.apply_aug passes --aug_params by keyword (rad.py:18-22); SVEA augments obs.clone() (svea.py:49) and AugCL
     reuses obs after random_shift (augcl.py:70-71): neither call may mutate its input."""
